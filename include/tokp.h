@@ -1,0 +1,155 @@
+/* tokp - C ABI of the B200-native key-point FD-derivative + iLQR path.
+ *
+ * The reference (DMackRus/TrajOptKP) has no FFI layer: the path sits behind C++ classes
+ * (include/Differentiator.h:17-24, include/KeyPointGenerator.h:56-110, include/Optimiser/Optimiser.h:49-242,
+ *  include/Optimiser/iLQR.h, include/MuJoCoHelper.h:118-123).  Each entry point below names the reference
+ * method whose body it replaces; the C++ shim classes in trajoptkp_b200/host/ keep those class
+ * signatures and call only these functions.  All pointers are HOST pointers owned by the caller;
+ * all matrices are column-major with leading dimension = rows (Eigen's default layout).
+ * Every function returns TOKP_OK (0) or an error code; tokp_last_error() gives the message.
+ * There is no CPU fallback: without a CUDA device every compute entry point returns TOKP_ERR_CUDA.
+ */
+#ifndef TOKP_H_
+#define TOKP_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct tokp_model tokp_model; /* compiled mjModel equivalent (host + device copy)            */
+typedef struct tokp_traj tokp_traj;   /* batch of B trajectories: device arena + iLQR state          */
+
+enum {
+  TOKP_OK = 0,
+  TOKP_ERR_ARG = 1,         /* bad argument / size                                                    */
+  TOKP_ERR_MODEL = 2,       /* MJCF outside the supported subset, parse error                         */
+  TOKP_ERR_CUDA = 3,        /* CUDA runtime error or no device                                        */
+  TOKP_ERR_UNSUPPORTED = 4, /* feature outside the hot-path scope (e.g. non-zero applied forces)      */
+  TOKP_ERR_STATE = 5        /* call sequence error (e.g. derivatives before a rollout)                */
+};
+
+/* object types for tokp_model_name2id (mj_name2id equivalents used by MuJoCoHelper.cpp:36-438) */
+enum { TOKP_OBJ_BODY = 1, TOKP_OBJ_JOINT = 3, TOKP_OBJ_GEOM = 5, TOKP_OBJ_SITE = 6, TOKP_OBJ_ACTUATOR = 19 };
+
+/* task kinds: which MT::Residuals override runs on the device
+ * (src/ModelTranslator/Acrobot.cpp:26-55, Walker.cpp:59-90) */
+enum { TOKP_TASK_ACROBOT = 0, TOKP_TASK_WALKER = 1 };
+
+/* key-point methods (include/KeyPointGenerator.h:34-43) */
+enum {
+  TOKP_KP_SET_INTERVAL = 0,
+  TOKP_KP_ADAPTIVE_JERK = 1,
+  TOKP_KP_ADAPTIVE_ACCEL = 2,
+  TOKP_KP_ITERATIVE_ERROR = 3,
+  TOKP_KP_VELOCITY_CHANGE = 4
+};
+
+/* mjSTAGE_* as used by mj_stepSkip (Differentiator.cpp:118,253,357) */
+enum { TOKP_STAGE_NONE = 0, TOKP_STAGE_POS = 1, TOKP_STAGE_VEL = 2 };
+
+/* What ModelTranslator::InitModelTranslator derives from the task YAML
+ * (src/ModelTranslator/ModelTranslator.cpp:18-96, stateVectorList include/StdInclude.h:110-188):
+ * the optimiser state is [pos(n); vel(n)], controls u(m). */
+typedef struct tokp_task_desc {
+  int kind;                             /* TOKP_TASK_*                                                */
+  int n;                                /* optimiser DoFs (current_state_vector.dof)                  */
+  int m;                                /* controls (num_ctrl)                                        */
+  const int* qpos_adr;                  /* [n] qpos address of each state position                    */
+  const int* dof_adr;                   /* [n] dof address (ModelTranslator::StateIndexToQposIndex)   */
+  const int* ctrl_adr;                  /* [m] actuator index of each control                         */
+  int num_resid;                        /* residual_list.size()                                       */
+  const double* resid_target;           /* [num_resid] residual_list[i].target[0]                     */
+  const double* resid_weight;           /* [num_resid]                                                */
+  const double* resid_weight_terminal;  /* [num_resid]                                                */
+  int kp_method;                        /* TOKP_KP_*                                                  */
+  int min_N, max_N;
+  const double* jerk_thresholds;        /* [n]                                                        */
+  const double* velchange_thresholds;   /* [n]                                                        */
+  double iterative_error_threshold;
+} tokp_task_desc;
+
+const char* tokp_last_error(void);
+const char* tokp_version(void);
+
+/* ---- model (MuJoCoHelper::InitSimulator, src/PhysicsSimulators/MuJoCoHelper.cpp:877-923) ---------- */
+int tokp_model_compile(const char* mjcf_path, double timestep, tokp_model** out);
+int tokp_model_compile_string(const char* mjcf_xml, const char* base_dir, double timestep, tokp_model** out);
+void tokp_model_destroy(tokp_model* m);
+/* dims = [nq, nv, nu, nbody, njnt, ngeom, npair, nmeshvert, maxcontact, maxefc, treedepth] */
+int tokp_model_dims(const tokp_model* m, int dims[11]);
+int tokp_model_name2id(const tokp_model* m, int objtype, const char* name); /* -1 when absent        */
+/* serialised model blob; returns the size in bytes (call with buf = NULL to query) or -1 */
+int64_t tokp_model_blob(const tokp_model* m, void* buf, int64_t cap);
+/* copy a named real / int field (names: trajoptkp_b200/csrc/model.h); returns count, -count if cap too small, -1e6 unknown */
+int tokp_model_get_real(const tokp_model* m, const char* field, double* out, int cap);
+int tokp_model_get_int(const tokp_model* m, const char* field, int32_t* out, int cap);
+/* doubles per snapshot: [time | qpos nq | qvel nv | qacc nv | qacc_warmstart nv | qfrc_applied nv |
+ * xfrc_applied 6*nbody | ctrl nu] - the 8 fields of MuJoCoHelper::CpMjData (MuJoCoHelper.cpp:732-741) */
+int tokp_snapshot_size(const tokp_model* m);
+
+/* ---- trajectory batch (Optimiser storage include/Optimiser/Optimiser.h:194-211; iLQR::Resize iLQR.cpp:37-200;
+ *      saved_systems_state_list / fd_data include/MuJoCoHelper.h:118-123) --------------------------------- */
+int tokp_traj_create(const tokp_model* m, const tokp_task_desc* task, int horizon, int batch, tokp_traj** out);
+void tokp_traj_destroy(tokp_traj* tr);
+/* per-trajectory residual targets (LoadTaskFromFile, src/FileHandler/FileHandler.cpp:471-578) */
+int tokp_traj_set_targets(tokp_traj* tr, int b, const double* resid_target);
+int tokp_traj_set_keypoint_method(tokp_traj* tr, int kp_method, int min_N, int max_N, const double* jerk_thr,
+                                  const double* vel_thr, double iter_thr);
+/* saved_systems_state_list[t] of trajectory b */
+int tokp_traj_set_snapshot(tokp_traj* tr, int b, int t, const double* snapshot);
+int tokp_traj_get_snapshot(tokp_traj* tr, int b, int t, double* snapshot);
+
+/* batched plain stepping of `count` independent worlds: mj_step / mj_stepSkip(NONE) applied `nsteps` times.
+ * solver_iterations < 0 selects the model's options (100, 1e-8). status[count] receives per-world warning bits. */
+int tokp_step_worlds(const tokp_model* m, const double* snapshots_in, double* snapshots_out, int count, int nsteps,
+                     int solver_iterations, double solver_tolerance, int* status);
+
+/* iLQR::RolloutTrajectory (iLQR.cpp:202-254) for all B trajectories: snapshot0[B][S], U[B][T][m] -> cost[B] */
+int tokp_rollout(tokp_traj* tr, const double* snapshot0, const double* U, double* cost);
+/* KeypointGenerator::GenerateKeyPoints (KeyPointGenerator.cpp:76-135) on the nominal X_old; optional outputs:
+ * counts[B][T], indices[B][T][2n] (row lists, in reference order, duplicates kept), pct[B][n] */
+int tokp_keypoints(tokp_traj* tr, int* counts, int* indices, double* pct);
+/* override the device key-point rows of trajectory b (tests / Optimiser::SmoothDerivativesAtContact) */
+int tokp_traj_set_keypoints(tokp_traj* tr, int b, const int* counts, const int* indices);
+/* Optimiser::ComputeDynamicsDerivativesAtKeypoints (Optimiser.cpp:239-323): ONE batched launch over all
+ * (b, t, column, +-eps) worlds of the current key-points; FD solver options (5 iterations, tol 0) */
+int tokp_dynamics_derivs(tokp_traj* tr, int central_diff, double eps);
+/* Differentiator::DynamicsDerivatives (Differentiator.cpp:8-462) exact drop-in for one (b, t, cols):
+ * writes columns {c, c+n} of A (lda) and {c | c<m} of B (ldb), leaves the others untouched */
+int tokp_dynamics_derivs_cols(tokp_traj* tr, int b, int t, const int* cols, int ncols, int central_diff, double eps,
+                              double* A, int lda, double* B, int ldb);
+/* KeypointGenerator::InterpolateDerivatives (KeyPointGenerator.cpp:840-954) */
+int tokp_interpolate(tokp_traj* tr);
+/* Optimiser::ComputeCostDerivatives (Optimiser.cpp:197-236): residual FD (Differentiator.cpp:464-663) for
+ * t = 0..T and Gauss-Newton l_x, l_xx, l_u, l_uu (ModelTranslator.cpp:552-583), terminal at T-1 */
+int tokp_cost_derivs(tokp_traj* tr, int central_diff, double eps);
+/* Optimiser::GenerateDerivatives (Optimiser.cpp:80-108): the four calls above in order */
+int tokp_generate_derivatives(tokp_traj* tr);
+/* iLQR::BackwardsPassQuuRegularisation (iLQR.cpp:535-634): lambda[B] in; ok[B], delta_J[B] out */
+int tokp_backward_pass(tokp_traj* tr, const double* lambda, int* ok, double* delta_J);
+/* iLQR::ForwardsPassParallel (iLQR.cpp:824-934) batched over alphas: costs[B][nalpha] */
+int tokp_forward_pass(tokp_traj* tr, const double* alphas, int nalpha, double* costs);
+/* Optimiser::SaveBestRollout + iLQR::UpdateNominal (Optimiser.cpp:440-468, iLQR.cpp:936-948) */
+int tokp_accept(tokp_traj* tr, int b, int alpha_idx);
+/* iLQR::Optimise (iLQR.cpp:269-410) for all B trajectories in lock-step: U_out[B][T][m], stats[B][8] =
+ * {initial_cost, final_cost, iterations, lambda, avg_pct_derivs, derivs_ms, bp_ms, fp_ms} (device-timed totals) */
+int tokp_optimise(tokp_traj* tr, const double* snapshot0, const double* U_init, int max_iterations, int min_iterations,
+                  const double* lambda_init, double* U_out, double* stats);
+
+/* named device-array readback (A, B, X_old, U_old, resid, r_x, r_u, l_x, l_xx, l_u, l_uu, K, k) for trajectory b;
+ * returns count, -count if cap too small, -1e6 unknown */
+int tokp_traj_get(tokp_traj* tr, int b, const char* name, double* out, int cap);
+int tokp_traj_set(tokp_traj* tr, int b, const char* name, const double* in, int count);
+/* counters of the last tokp_dynamics_derivs: [worlds, jacobians_x1e6, kernel_launches, 0] */
+int tokp_traj_counters(tokp_traj* tr, int64_t out[4]);
+/* CUDA-event time of the last derivative / backward / forward phase, ms (time_get_derivs_ms etc., iLQR.cpp:418-505) */
+int tokp_timers(tokp_traj* tr, double ms[3]);
+/* total number of kernels this library launched since load */
+int64_t tokp_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TOKP_H_ */

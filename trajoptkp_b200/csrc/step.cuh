@@ -1,0 +1,208 @@
+// Batched fp64 rigid-body step for sm_100a: one *group* of G lanes (G = 8, 16 or 32; G = 32 is
+// warp-per-world) advances one world.  All mjData-equivalent state of the world lives in the
+// group's shared-memory workspace; model arrays are read-only global (L1/L2 resident).
+//
+// Replaces MuJoCo's mj_step / mj_stepSkip on the reference path
+// (src/Differentiator/Differentiator.cpp:69,118,155,253,276,357,377; src/Optimiser/iLQR.cpp:222,914).
+// Pipeline order follows mj_forwardSkip: kinematics, comPos, crb, factorM, collision, makeConstraint |
+// comVel, passive, referenceConstraint, rne | actuation, acceleration, Newton constraint solver | Euler.
+// Lane mapping: tree stages are level-synchronous over bodies, everything else is strided over
+// dofs / constraint rows / matrix entries; reductions are xor-butterflies inside the group, so every
+// lane of a group holds bit-identical scalars and control flow is uniform per group.
+#pragma once
+#include <cuda_runtime.h>
+
+#include "device_model.h"
+
+namespace tk {
+
+#define TK_DEV __device__ __forceinline__
+constexpr double kMinVal = 1e-15;
+constexpr double kPi = 3.14159265358979323846;
+constexpr double kMinImp = 0.0001, kMaxImp = 0.9999;
+enum { JNT_FREE = 0, JNT_BALL = 1, JNT_SLIDE = 2, JNT_HINGE = 3 };
+enum { GEOM_PLANE = 0, GEOM_SPHERE = 2, GEOM_CAPSULE = 3, GEOM_CYLINDER = 5, GEOM_BOX = 6, GEOM_MESH = 7 };
+enum { ROW_LIMIT = 0, ROW_FRICTIONLESS = 1, ROW_PYRAMIDAL = 2 };
+// status bits (per world)
+enum { ST_BAD_QPOS = 1, ST_BAD_QVEL = 2, ST_BAD_QACC = 4, ST_OVERFLOW = 8, ST_UNSUPPORTED = 32 };
+
+// ---- group of G lanes -----------------------------------------------------------------------------
+template <int G>
+struct Grp {
+  unsigned mask;
+  int gl;  // lane index inside the group
+  TK_DEV Grp() {
+    int lane = threadIdx.x & 31;
+    gl = lane % G;
+    mask = (G == 32) ? 0xffffffffu : (((1u << G) - 1u) << (lane - gl));
+  }
+  TK_DEV void sync() const { __syncwarp(mask); }
+  TK_DEV double sum(double v) const {
+#pragma unroll
+    for (int off = G / 2; off > 0; off >>= 1) v += __shfl_xor_sync(mask, v, off, G);
+    return v;
+  }
+  TK_DEV int any(int p) const { return __any_sync(mask, p); }
+};
+
+// ---- small vector helpers ---------------------------------------------------------------------------
+TK_DEV double dot3(const double* a, const double* b) { return a[0] * b[0] + a[1] * b[1] + a[2] * b[2]; }
+TK_DEV void cross3(double* r, const double* a, const double* b) {
+  double x = a[1] * b[2] - a[2] * b[1], y = a[2] * b[0] - a[0] * b[2], z = a[0] * b[1] - a[1] * b[0];
+  r[0] = x; r[1] = y; r[2] = z;
+}
+TK_DEV double normalize3(double* a) {
+  double n = sqrt(dot3(a, a));
+  if (n < kMinVal) { a[0] = 1.0; a[1] = 0.0; a[2] = 0.0; }
+  else { double inv = 1.0 / n; a[0] *= inv; a[1] *= inv; a[2] *= inv; }
+  return n;
+}
+TK_DEV void normalize4(double* q) {
+  double n = sqrt(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
+  if (n < kMinVal) { q[0] = 1.0; q[1] = 0.0; q[2] = 0.0; q[3] = 0.0; }
+  else if (fabs(n - 1.0) > kMinVal) { double inv = 1.0 / n; q[0] *= inv; q[1] *= inv; q[2] *= inv; q[3] *= inv; }
+}
+TK_DEV void mul_quat(double* r, const double* a, const double* b) {
+  double w = a[0] * b[0] - a[1] * b[1] - a[2] * b[2] - a[3] * b[3];
+  double x = a[0] * b[1] + a[1] * b[0] + a[2] * b[3] - a[3] * b[2];
+  double y = a[0] * b[2] - a[1] * b[3] + a[2] * b[0] + a[3] * b[1];
+  double z = a[0] * b[3] + a[1] * b[2] - a[2] * b[1] + a[3] * b[0];
+  r[0] = w; r[1] = x; r[2] = y; r[3] = z;
+}
+TK_DEV void quat2mat(double* m, const double* q) {
+  double q00 = q[0] * q[0], q01 = q[0] * q[1], q02 = q[0] * q[2], q03 = q[0] * q[3];
+  double q11 = q[1] * q[1], q12 = q[1] * q[2], q13 = q[1] * q[3];
+  double q22 = q[2] * q[2], q23 = q[2] * q[3], q33 = q[3] * q[3];
+  m[0] = q00 + q11 - q22 - q33; m[4] = q00 - q11 + q22 - q33; m[8] = q00 - q11 - q22 + q33;
+  m[1] = 2.0 * (q12 - q03); m[2] = 2.0 * (q13 + q02);
+  m[3] = 2.0 * (q12 + q03); m[5] = 2.0 * (q23 - q01);
+  m[6] = 2.0 * (q13 - q02); m[7] = 2.0 * (q23 + q01);
+}
+TK_DEV void mat_vec3(double* r, const double* m, const double* v) {
+  double x = m[0] * v[0] + m[1] * v[1] + m[2] * v[2];
+  double y = m[3] * v[0] + m[4] * v[1] + m[5] * v[2];
+  double z = m[6] * v[0] + m[7] * v[1] + m[8] * v[2];
+  r[0] = x; r[1] = y; r[2] = z;
+}
+TK_DEV void rot_vec_quat(double* r, const double* v, const double* q) {
+  if (q[0] == 1.0 && q[1] == 0.0 && q[2] == 0.0 && q[3] == 0.0) { r[0] = v[0]; r[1] = v[1]; r[2] = v[2]; return; }
+  double m[9];
+  quat2mat(m, q);
+  mat_vec3(r, m, v);
+}
+TK_DEV void axis_angle2quat(double* q, const double* axis, double angle) {
+  if (angle == 0.0) { q[0] = 1.0; q[1] = 0.0; q[2] = 0.0; q[3] = 0.0; return; }
+  double s, c;
+  sincos(angle * 0.5, &s, &c);
+  q[0] = c; q[1] = axis[0] * s; q[2] = axis[1] * s; q[3] = axis[2] * s;
+}
+TK_DEV void quat_integrate(double* q, const double* vel, double scale) {
+  double tmp[3] = {vel[0], vel[1], vel[2]};
+  double angle = scale * normalize3(tmp);
+  double qrot[4], res[4];
+  axis_angle2quat(qrot, tmp, angle);
+  normalize4(q);
+  mul_quat(res, q, qrot);
+  q[0] = res[0]; q[1] = res[1]; q[2] = res[2]; q[3] = res[3];
+}
+TK_DEV void sub_quat(double* res, const double* qa, const double* qb) {
+  double qneg[4] = {qa[0], -qa[1], -qa[2], -qa[3]}, qdif[4];
+  mul_quat(qdif, qneg, qb);
+  double axis[3] = {qdif[1], qdif[2], qdif[3]};
+  double s = normalize3(axis);
+  double speed = 2.0 * atan2(s, qdif[0]);
+  if (speed > kPi) speed -= 2.0 * kPi;
+  res[0] = axis[0] * speed; res[1] = axis[1] * speed; res[2] = axis[2] * speed;
+}
+// spatial inertia (10 numbers) times motion vector [rot; lin]
+TK_DEV void mul_inert_vec(double* res, const double* i, const double* v) {
+  res[0] = i[0] * v[0] + i[3] * v[1] + i[4] * v[2] - i[8] * v[4] + i[7] * v[5];
+  res[1] = i[3] * v[0] + i[1] * v[1] + i[5] * v[2] + i[8] * v[3] - i[6] * v[5];
+  res[2] = i[4] * v[0] + i[5] * v[1] + i[2] * v[2] - i[7] * v[3] + i[6] * v[4];
+  res[3] = i[8] * v[1] - i[7] * v[2] + i[9] * v[3];
+  res[4] = i[6] * v[2] - i[8] * v[0] + i[9] * v[4];
+  res[5] = i[7] * v[0] - i[6] * v[1] + i[9] * v[5];
+}
+TK_DEV void cross_motion(double* res, const double* vel, const double* v) {
+  double a[3], b[3], c[3];
+  cross3(a, vel, v);
+  cross3(b, vel, v + 3);
+  cross3(c, vel + 3, v);
+  res[0] = a[0]; res[1] = a[1]; res[2] = a[2];
+  res[3] = b[0] + c[0]; res[4] = b[1] + c[1]; res[5] = b[2] + c[2];
+}
+TK_DEV void cross_force(double* res, const double* vel, const double* f) {
+  double a[3], b[3], c[3];
+  cross3(a, vel, f);
+  cross3(b, vel + 3, f + 3);
+  cross3(c, vel, f + 3);
+  res[0] = a[0] + b[0]; res[1] = a[1] + b[1]; res[2] = a[2] + b[2];
+  res[3] = c[0]; res[4] = c[1]; res[5] = c[2];
+}
+TK_DEV bool in_mask(unsigned lo, unsigned hi, int bit) { return bit < 32 ? ((lo >> bit) & 1u) : ((hi >> (bit - 32)) & 1u); }
+TK_DEV bool bad_value(double x) { return !(fabs(x) <= 1e10); }
+
+// ---- per-world workspace (shared memory) ---------------------------------------------------------
+struct WS {
+  // state
+  double *qpos, *qvel, *qacc, *warm, *ctrl;
+  // position stage
+  double *xpos, *xquat, *xmat, *xipos, *ximat, *xanchor, *xaxis, *gxpos, *gxmat;
+  double *rootcom, *cinert, *crb, *cdof, *cdof_dot;
+  double *M, *LD, *LDinv, *H, *Hinv;  // Hinv: diag inverse for the Euler factor
+  // contacts
+  double *con_dist, *con_pos, *con_frame;
+  int *con_pair;
+  // constraint rows
+  double *J, *efc_pos, *efc_margin, *efc_D, *efc_aref, *efc_K, *efc_B, *efc_imp, *jar, *jv, *quad, *efc_force;
+  int *row_type, *row_id, *row_sub, *cnt;  // cnt: scratch counters (max(njnt, npair) + 2)
+  // velocity / acceleration stage
+  double *cvel, *cacc, *cfrc;
+  double *frc_passive, *frc_bias, *frc_act, *frc_smooth, *acc_smooth, *frc_con, *Ma, *Mv, *grad, *Mgrad, *search, *tmpv;
+  int ncon, nefc;
+};
+
+__host__ __device__ inline int ws_doubles(const DM& m) {
+  int nb = m.nbody, nv = m.nv, ne = m.maxefc, nc = m.maxcontact;
+  int n = 0;
+  n += m.nq + 3 * nv + m.nu;
+  n += nb * (3 + 4 + 9 + 3 + 9) + 6 * m.njnt + 12 * m.ngeom;
+  n += 3 * nb + 20 * nb + 12 * nv;
+  n += 3 * nv * nv + 2 * nv;
+  n += nc * 13;
+  n += ne * nv + ne * 13;
+  n += 18 * nb;
+  n += 12 * nv;
+  // int region (counted in doubles, rounded up)
+  int ints = nc + 3 * ne + (m.njnt > m.npair ? m.njnt : m.npair) + 4;
+  n += (ints + 1) / 2;
+  return n;
+}
+
+TK_DEV void ws_init(WS& w, double* base, const DM& m) {
+  int nb = m.nbody, nv = m.nv, ne = m.maxefc, nc = m.maxcontact;
+  double* p = base;
+  auto take = [&](int n) { double* r = p; p += n; return r; };
+  w.qpos = take(m.nq); w.qvel = take(nv); w.qacc = take(nv); w.warm = take(nv); w.ctrl = take(m.nu);
+  w.xpos = take(3 * nb); w.xquat = take(4 * nb); w.xmat = take(9 * nb); w.xipos = take(3 * nb); w.ximat = take(9 * nb);
+  w.xanchor = take(3 * m.njnt); w.xaxis = take(3 * m.njnt); w.gxpos = take(3 * m.ngeom); w.gxmat = take(9 * m.ngeom);
+  w.rootcom = take(3 * nb); w.cinert = take(10 * nb); w.crb = take(10 * nb); w.cdof = take(6 * nv); w.cdof_dot = take(6 * nv);
+  w.M = take(nv * nv); w.LD = take(nv * nv); w.H = take(nv * nv); w.LDinv = take(nv); w.Hinv = take(nv);
+  w.con_dist = take(nc); w.con_pos = take(3 * nc); w.con_frame = take(9 * nc);
+  w.J = take(ne * nv);
+  w.efc_pos = take(ne); w.efc_margin = take(ne); w.efc_D = take(ne); w.efc_aref = take(ne); w.efc_K = take(ne);
+  w.efc_B = take(ne); w.efc_imp = take(ne); w.jar = take(ne); w.jv = take(ne); w.quad = take(3 * ne); w.efc_force = take(ne);
+  w.cvel = take(6 * nb); w.cacc = take(6 * nb); w.cfrc = take(6 * nb);
+  w.frc_passive = take(nv); w.frc_bias = take(nv); w.frc_act = take(nv); w.frc_smooth = take(nv); w.acc_smooth = take(nv);
+  w.frc_con = take(nv); w.Ma = take(nv); w.Mv = take(nv); w.grad = take(nv); w.Mgrad = take(nv); w.search = take(nv);
+  w.tmpv = take(nv);
+  int* ip = reinterpret_cast<int*>(p);
+  w.con_pair = ip; ip += nc;
+  w.row_type = ip; ip += ne;
+  w.row_id = ip; ip += ne;
+  w.row_sub = ip; ip += ne;
+  w.cnt = ip;
+  w.ncon = 0; w.nefc = 0;
+}
+
+}  // namespace tk

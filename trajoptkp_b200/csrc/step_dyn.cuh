@@ -1,0 +1,422 @@
+// Velocity / acceleration stages, Newton constraint solver with exact line search and the
+// semi-implicit Euler update of the batched step (MuJoCo: mj_fwdVelocity, mj_fwdActuation,
+// mj_fwdAcceleration, mj_fwdConstraint/mj_solNewton, mj_EulerSkip).
+#pragma once
+#include "step_con.cuh"
+
+namespace tk {
+
+// mj_comVel (level-synchronous)
+template <int G>
+TK_DEV void com_vel(const DM& m, WS& w, const Grp<G>& g) {
+  if (g.gl == 0) for (int k = 0; k < 6; k++) w.cvel[k] = 0.0;
+  g.sync();
+  for (int depth = 1; depth <= m.treedepth; depth++) {
+    for (int i = 1 + g.gl; i < m.nbody; i += G) {
+      if (m.body_depth[i] != depth) continue;
+      double cv[6];
+      for (int k = 0; k < 6; k++) cv[k] = w.cvel[6 * m.body_parentid[i] + k];
+      int bda = m.body_dofadr[i], dn = m.body_dofnum[i];
+      int j = 0;
+      while (j < dn) {
+        int dj = bda + j;
+        if (m.jnt_type[m.dof_jntid[dj]] == JNT_FREE) {
+          for (int k = 0; k < 18; k++) w.cdof_dot[6 * dj + k] = 0.0;
+          for (int k = 0; k < 3; k++)
+            for (int c = 0; c < 6; c++) cv[c] += w.cdof[6 * (dj + k) + c] * w.qvel[dj + k];
+          dj += 3;
+          for (int k = 0; k < 3; k++) cross_motion(&w.cdof_dot[6 * (dj + k)], cv, &w.cdof[6 * (dj + k)]);
+          for (int k = 0; k < 3; k++)
+            for (int c = 0; c < 6; c++) cv[c] += w.cdof[6 * (dj + k) + c] * w.qvel[dj + k];
+          j += 6;
+        } else {
+          cross_motion(&w.cdof_dot[6 * dj], cv, &w.cdof[6 * dj]);
+          for (int c = 0; c < 6; c++) cv[c] += w.cdof[6 * dj + c] * w.qvel[dj];
+          j += 1;
+        }
+      }
+      for (int k = 0; k < 6; k++) w.cvel[6 * i + k] = cv[k];
+    }
+    g.sync();
+  }
+}
+
+// mj_passive (damping + gravity compensation) and mj_rne(flg_acc = 0)
+template <int G>
+TK_DEV void passive_and_bias(const DM& m, WS& w, const Grp<G>& g) {
+  int nv = m.nv;
+  for (int i = g.gl; i < nv; i += G) {
+    double f = -m.dof_damping[i] * w.qvel[i];
+    if (m.any_gravcomp) {
+      for (int b = 1; b < m.nbody; b++) {
+        double gc = m.body_gravcomp[b];
+        if (gc == 0.0) continue;
+        double col[3];
+        jac_col(m, w, col, &w.xipos[3 * b], b, i);
+        double s = m.body_mass[b] * gc;
+        f += col[0] * (-m.gravity[0] * s) + col[1] * (-m.gravity[1] * s) + col[2] * (-m.gravity[2] * s);
+      }
+    }
+    w.frc_passive[i] = f;
+  }
+  // cacc: level-synchronous down the tree
+  if (g.gl == 0) {
+    w.cacc[0] = w.cacc[1] = w.cacc[2] = 0.0;
+    w.cacc[3] = -m.gravity[0]; w.cacc[4] = -m.gravity[1]; w.cacc[5] = -m.gravity[2];
+    for (int k = 0; k < 6; k++) w.cfrc[k] = 0.0;
+  }
+  g.sync();
+  for (int depth = 1; depth <= m.treedepth; depth++) {
+    for (int i = 1 + g.gl; i < m.nbody; i += G) {
+      if (m.body_depth[i] != depth) continue;
+      int bda = m.body_dofadr[i];
+      double t[6] = {0, 0, 0, 0, 0, 0};
+      for (int j = 0; j < m.body_dofnum[i]; j++)
+        for (int c = 0; c < 6; c++) t[c] += w.cdof_dot[6 * (bda + j) + c] * w.qvel[bda + j];
+      double ca[6];
+      for (int c = 0; c < 6; c++) { ca[c] = w.cacc[6 * m.body_parentid[i] + c] + t[c]; w.cacc[6 * i + c] = ca[c]; }
+      double t1[6], t2[6], t3[6];
+      mul_inert_vec(t1, &w.cinert[10 * i], ca);
+      mul_inert_vec(t2, &w.cinert[10 * i], &w.cvel[6 * i]);
+      cross_force(t3, &w.cvel[6 * i], t2);
+      for (int c = 0; c < 6; c++) w.cfrc[6 * i + c] = t1[c] + t3[c];
+    }
+    g.sync();
+  }
+  // bias[i] = cdof_i . (sum of body forces over the subtree of the dof's body)
+  for (int i = g.gl; i < nv; i += G) {
+    int b = m.dof_bodyid[i];
+    unsigned lo = m.body_subtreemask_lo[b], hi = m.body_subtreemask_hi[b];
+    double f[6] = {0, 0, 0, 0, 0, 0};
+    for (int j = m.nbody - 1; j >= b; j--) {
+      if (!in_mask(lo, hi, j)) continue;
+      for (int c = 0; c < 6; c++) f[c] += w.cfrc[6 * j + c];
+    }
+    const double* cd = &w.cdof[6 * i];
+    w.frc_bias[i] = cd[0] * f[0] + cd[1] * f[1] + cd[2] * f[2] + cd[3] * f[3] + cd[4] * f[4] + cd[5] * f[5];
+  }
+  g.sync();
+}
+
+// mj_fwdActuation + mj_fwdAcceleration
+template <int G>
+TK_DEV void actuation_acceleration(const DM& m, WS& w, const Grp<G>& g) {
+  int nv = m.nv;
+  for (int i = g.gl; i < nv; i += G) {
+    double fa = 0.0;
+    for (int a = 0; a < m.nu; a++) {
+      if (m.actuator_dofadr[a] != i) continue;
+      double ctrl = w.ctrl[a];
+      if (m.actuator_ctrllimited[a]) ctrl = fmin(fmax(ctrl, m.actuator_ctrlrange[2 * a]), m.actuator_ctrlrange[2 * a + 1]);
+      double gear = m.actuator_gear[a];
+      double force = m.actuator_gainprm[a] * ctrl;
+      if (m.actuator_biastype[a] == 1) {
+        int qa = m.jnt_qposadr[m.actuator_trnid[a]];
+        force += m.actuator_biasprm[3 * a] + m.actuator_biasprm[3 * a + 1] * (gear * w.qpos[qa]) +
+                 m.actuator_biasprm[3 * a + 2] * (gear * w.qvel[i]);
+      }
+      if (m.actuator_forcelimited[a]) force = fmin(fmax(force, m.actuator_forcerange[2 * a]), m.actuator_forcerange[2 * a + 1]);
+      fa += gear * force;
+    }
+    w.frc_act[i] = fa;
+    double fs = w.frc_passive[i] - w.frc_bias[i] + fa;
+    w.frc_smooth[i] = fs;
+    w.acc_smooth[i] = fs;
+  }
+  g.sync();
+  solve_ldl(m, w.LD, w.LDinv, w.acc_smooth, g);
+}
+
+// ---- Newton solver --------------------------------------------------------------------------------
+struct Pnt { double alpha, cost, d0, d1; };
+
+// cost of the active rows at jar (s(jar)); optionally writes forces
+template <int G>
+TK_DEV double constraint_cost(const WS& w, const double* jar, const Grp<G>& g) {
+  double c = 0.0;
+  for (int r = g.gl; r < w.nefc; r += G) {
+    double x = jar[r];
+    if (x < 0.0) c += 0.5 * w.efc_D[r] * x * x;
+  }
+  return g.sum(c);
+}
+
+template <int G>
+TK_DEV Pnt primal_eval(const WS& w, const Grp<G>& g, const double qg[3], double alpha, int& lsiter) {
+  lsiter++;
+  double q0 = 0.0, q1 = 0.0, q2 = 0.0;
+  for (int r = g.gl; r < w.nefc; r += G) {
+    double x = w.jar[r] + alpha * w.jv[r];
+    if (x < 0.0) { q0 += w.quad[3 * r]; q1 += w.quad[3 * r + 1]; q2 += w.quad[3 * r + 2]; }
+  }
+  q0 = g.sum(q0) + qg[0]; q1 = g.sum(q1) + qg[1]; q2 = g.sum(q2) + qg[2];
+  Pnt p;
+  p.alpha = alpha;
+  p.cost = alpha * alpha * q2 + alpha * q1 + q0;
+  p.d0 = 2.0 * alpha * q2 + q1;
+  p.d1 = 2.0 * q2;
+  if (p.d1 <= 0.0) p.d1 = kMinVal;
+  return p;
+}
+
+template <int G>
+TK_DEV int update_bracket(const WS& w, const Grp<G>& g, const double qg[3], Pnt& p, const Pnt cand[3], Pnt& pnext, int& lsiter) {
+  int flag = 0;
+  for (int i = 0; i < 3; i++) {
+    if (p.d0 < 0.0 && cand[i].d0 < 0.0 && p.d0 < cand[i].d0) { p = cand[i]; flag = 1; }
+    else if (p.d0 > 0.0 && cand[i].d0 > 0.0 && p.d0 > cand[i].d0) { p = cand[i]; flag = 2; }
+  }
+  if (flag) pnext = primal_eval(w, g, qg, p.alpha - p.d0 / p.d1, lsiter);
+  return flag;
+}
+
+// exact line search along w.search (PrimalSearch); returns the step
+template <int G>
+TK_DEV double primal_search(const DM& m, WS& w, const Grp<G>& g, double gauss, double tolerance) {
+  int nv = m.nv;
+  double sn = 0.0;
+  for (int i = g.gl; i < nv; i += G) sn += w.search[i] * w.search[i];
+  double snorm = sqrt(g.sum(sn));
+  if (snorm < kMinVal) return 0.0;
+  double scale = 1.0 / (m.meaninertia * (double)max(1, nv));
+  double gtol = tolerance * m.ls_tolerance * snorm / scale;
+  mul_M(m, w, w.Mv, w.search, g);
+  for (int r = g.gl; r < w.nefc; r += G) {
+    double s = 0.0;
+    for (int i = 0; i < nv; i++) s += w.J[r * nv + i] * w.search[i];
+    w.jv[r] = s;
+    double DJ0 = w.efc_D[r] * w.jar[r];
+    w.quad[3 * r] = 0.5 * w.jar[r] * DJ0;
+    w.quad[3 * r + 1] = s * DJ0;
+    w.quad[3 * r + 2] = 0.5 * s * w.efc_D[r] * s;
+  }
+  g.sync();
+  double a = 0.0, b = 0.0, c = 0.0;
+  for (int i = g.gl; i < nv; i += G) {
+    a += w.search[i] * w.Ma[i];
+    b += w.frc_smooth[i] * w.search[i];
+    c += w.search[i] * w.Mv[i];
+  }
+  double qg[3] = {gauss, g.sum(a) - g.sum(b), 0.5 * g.sum(c)};
+  int lsiter = 0;
+  Pnt p0 = primal_eval(w, g, qg, 0.0, lsiter);
+  Pnt p1 = primal_eval(w, g, qg, p0.alpha - p0.d0 / p0.d1, lsiter);
+  if (p0.cost < p1.cost) p1 = p0;
+  if (fabs(p1.d0) < gtol) return p1.alpha;
+  double dir = (p1.d0 < 0.0) ? 1.0 : -1.0;
+  int p2update = 0;
+  Pnt p2 = p1;
+  while (p1.d0 * dir <= -gtol && lsiter < m.ls_iterations) {
+    p2 = p1;
+    p2update = 1;
+    p1 = primal_eval(w, g, qg, p1.alpha - p1.d0 / p1.d1, lsiter);
+    if (fabs(p1.d0) < gtol) return p1.alpha;
+  }
+  if (lsiter >= m.ls_iterations) return p1.alpha;
+  if (!p2update) return p1.alpha;
+  Pnt p2next = p1;
+  Pnt p1next = primal_eval(w, g, qg, p1.alpha - p1.d0 / p1.d1, lsiter);
+  while (lsiter < m.ls_iterations) {
+    Pnt pmid = primal_eval(w, g, qg, 0.5 * (p1.alpha + p2.alpha), lsiter);
+    Pnt cand[3] = {p1next, p2next, pmid};
+    double bestcost = 0.0;
+    int bestind = -1;
+    for (int i = 0; i < 3; i++)
+      if (fabs(cand[i].d0) < gtol && (bestind == -1 || cand[i].cost < bestcost)) { bestcost = cand[i].cost; bestind = i; }
+    if (bestind >= 0) return cand[bestind].alpha;
+    int b1 = update_bracket(w, g, qg, p1, cand, p1next, lsiter);
+    int b2 = update_bracket(w, g, qg, p2, cand, p2next, lsiter);
+    if (!b1 && !b2) return pmid.alpha;
+  }
+  if (p1.cost <= p2.cost && p1.cost < p0.cost) return p1.alpha;
+  if (p2.cost <= p1.cost && p2.cost < p0.cost) return p2.alpha;
+  return 0.0;
+}
+
+// in-place dense Cholesky (lower) of the nv x nv matrix in w.H, right-looking, lanes over the trailing block
+template <int G>
+TK_DEV void chol_factor(double* H, int n, const Grp<G>& g) {
+  for (int j = 0; j < n; j++) {
+    double d = H[j * n + j];
+    if (d < kMinVal) d = kMinVal;
+    d = sqrt(d);
+    double inv = 1.0 / d;
+    g.sync();
+    for (int i = j + g.gl; i < n; i += G) H[i * n + j] = (i == j) ? d : H[i * n + j] * inv;
+    g.sync();
+    int rem = n - j - 1;
+    for (int e = g.gl; e < rem * rem; e += G) {
+      int i = j + 1 + e / rem, k = j + 1 + e % rem;
+      if (k <= i) H[i * n + k] -= H[i * n + j] * H[k * n + j];
+    }
+    g.sync();
+  }
+}
+
+// x = inv(L L') b  (column-oriented substitutions, lanes over the remaining rows)
+template <int G>
+TK_DEV void chol_solve(const double* L, int n, double* x, const double* b, const Grp<G>& g) {
+  for (int i = g.gl; i < n; i += G) x[i] = b[i];
+  g.sync();
+  for (int j = 0; j < n; j++) {
+    double xj = x[j] / L[j * n + j];
+    g.sync();
+    if (g.gl == 0) x[j] = xj;
+    for (int i = j + 1 + g.gl; i < n; i += G) x[i] -= L[i * n + j] * xj;
+    g.sync();
+  }
+  for (int j = n - 1; j >= 0; j--) {
+    double xj = x[j] / L[j * n + j];
+    g.sync();
+    if (g.gl == 0) x[j] = xj;
+    for (int i = g.gl; i < j; i += G) x[i] -= L[j * n + i] * xj;
+    g.sync();
+  }
+}
+
+// mj_fwdConstraint with the Newton solver
+template <int G>
+TK_DEV void fwd_constraint(const DM& m, WS& w, const Grp<G>& g, int iterations, double tolerance) {
+  int nv = m.nv, nefc = w.nefc;
+  if (nefc == 0) {
+    for (int i = g.gl; i < nv; i += G) { w.qacc[i] = w.acc_smooth[i]; w.warm[i] = w.acc_smooth[i]; w.frc_con[i] = 0.0; }
+    g.sync();
+    return;
+  }
+  // warm start: keep qacc_warmstart only if it costs less than qacc_smooth
+  for (int r = g.gl; r < nefc; r += G) {
+    double s1 = 0.0, s2 = 0.0;
+    for (int i = 0; i < nv; i++) { s1 += w.J[r * nv + i] * w.warm[i]; s2 += w.J[r * nv + i] * w.acc_smooth[i]; }
+    w.jar[r] = s1 - w.efc_aref[r];
+    w.jv[r] = s2 - w.efc_aref[r];
+  }
+  mul_M(m, w, w.Ma, w.warm, g);
+  g.sync();
+  double cw = constraint_cost(w, w.jar, g);
+  double gs = 0.0;
+  for (int i = g.gl; i < nv; i += G) gs += (w.Ma[i] - w.frc_smooth[i]) * (w.warm[i] - w.acc_smooth[i]);
+  cw += 0.5 * g.sum(gs);
+  double cs = constraint_cost(w, w.jv, g);
+  bool use_smooth = cw > cs;
+  g.sync();
+  for (int i = g.gl; i < nv; i += G) w.qacc[i] = use_smooth ? w.acc_smooth[i] : w.warm[i];
+  if (use_smooth) {
+    for (int r = g.gl; r < nefc; r += G) w.jar[r] = w.jv[r];
+    g.sync();
+    mul_M(m, w, w.Ma, w.qacc, g);
+  }
+  g.sync();
+
+  double cost = 0.0, gauss = 0.0;
+  auto update = [&]() {
+    // forces, cost, qfrc_constraint, gradient, Hessian, Newton direction
+    double c = 0.0;
+    for (int r = g.gl; r < nefc; r += G) {
+      double x = w.jar[r];
+      if (x < 0.0) { c += 0.5 * w.efc_D[r] * x * x; w.efc_force[r] = -w.efc_D[r] * x; }
+      else w.efc_force[r] = 0.0;
+    }
+    c = g.sum(c);
+    g.sync();
+    double gsum = 0.0;
+    for (int i = g.gl; i < nv; i += G) {
+      double fc = 0.0;
+      for (int r = 0; r < nefc; r++) fc += w.J[r * nv + i] * w.efc_force[r];
+      w.frc_con[i] = fc;
+      w.grad[i] = w.Ma[i] - w.frc_smooth[i] - fc;
+      gsum += (w.Ma[i] - w.frc_smooth[i]) * (w.qacc[i] - w.acc_smooth[i]);
+    }
+    gauss = 0.5 * g.sum(gsum);
+    cost = c + gauss;
+    for (int e = g.gl; e < nv * nv; e += G) {
+      int i = e / nv, j = e - i * nv;
+      if (j > i) continue;
+      double h = w.M[e];
+      for (int r = 0; r < nefc; r++)
+        if (w.efc_force[r] != 0.0) h += w.efc_D[r] * w.J[r * nv + i] * w.J[r * nv + j];
+      w.H[e] = h;
+    }
+    g.sync();
+    chol_factor(w.H, nv, g);
+    chol_solve(w.H, nv, w.Mgrad, w.grad, g);
+    for (int i = g.gl; i < nv; i += G) w.search[i] = -w.Mgrad[i];
+    g.sync();
+  };
+
+  update();
+  double scale = 1.0 / (m.meaninertia * (double)max(1, nv));
+  int iter = 0;
+  while (iter < iterations) {
+    double alpha = primal_search(m, w, g, gauss, tolerance);
+    if (alpha == 0.0) break;
+    for (int i = g.gl; i < nv; i += G) { w.qacc[i] += alpha * w.search[i]; w.Ma[i] += alpha * w.Mv[i]; }
+    for (int r = g.gl; r < nefc; r += G) w.jar[r] += alpha * w.jv[r];
+    g.sync();
+    double oldcost = cost;
+    update();
+    double gn = 0.0;
+    for (int i = g.gl; i < nv; i += G) gn += w.grad[i] * w.grad[i];
+    double improvement = scale * (oldcost - cost);
+    double gradient = scale * sqrt(g.sum(gn));
+    iter++;
+    if (improvement < tolerance || gradient < tolerance) break;
+  }
+  for (int i = g.gl; i < nv; i += G) w.warm[i] = w.qacc[i];
+  g.sync();
+}
+
+// mj_EulerSkip + mj_advance
+template <int G>
+TK_DEV void euler(const DM& m, WS& w, const Grp<G>& g, double& time) {
+  int nv = m.nv;
+  double h = m.timestep;
+  if (m.any_damping) {
+    for (int e = g.gl; e < nv * nv; e += G) {
+      int i = e / nv;
+      w.H[e] = w.M[e] + ((e - i * nv) == i ? h * m.dof_damping[i] : 0.0);
+    }
+    g.sync();
+    factor_ldl(m, w.H, w.LD, w.Hinv, g);
+    for (int i = g.gl; i < nv; i += G) w.tmpv[i] = w.frc_smooth[i] + w.frc_con[i];
+    g.sync();
+    solve_ldl(m, w.LD, w.Hinv, w.tmpv, g);
+  } else {
+    for (int i = g.gl; i < nv; i += G) w.tmpv[i] = w.qacc[i];
+    g.sync();
+  }
+  for (int i = g.gl; i < nv; i += G) w.qvel[i] += w.tmpv[i] * h;
+  g.sync();
+  for (int j = g.gl; j < m.njnt; j += G) {
+    int pa = m.jnt_qposadr[j], va = m.jnt_dofadr[j];
+    if (m.jnt_type[j] == JNT_FREE) {
+      for (int k = 0; k < 3; k++) w.qpos[pa + k] += h * w.qvel[va + k];
+      quat_integrate(&w.qpos[pa + 3], &w.qvel[va + 3], h);
+    } else {
+      w.qpos[pa] += h * w.qvel[va];
+    }
+  }
+  time += h;
+  g.sync();
+}
+
+// one full step (mj_step).  `iterations`/`tolerance`: solver options of this launch.
+template <int G>
+TK_DEV void step(const DM& m, WS& w, const Grp<G>& g, int iterations, double tolerance, double& time, int& status) {
+  for (int i = g.gl; i < m.nq; i += G) if (bad_value(w.qpos[i])) status |= ST_BAD_QPOS;
+  for (int i = g.gl; i < m.nv; i += G) if (bad_value(w.qvel[i])) status |= ST_BAD_QVEL;
+  kinematics(m, w, g);
+  com_pos(m, w, g);
+  crb_factor(m, w, g);
+  factor_ldl(m, w.M, w.LD, w.LDinv, g);
+  collision(m, w, g, status);
+  make_constraint(m, w, g, status);
+  com_vel(m, w, g);
+  passive_and_bias(m, w, g);
+  reference_constraint(m, w, g);
+  actuation_acceleration(m, w, g);
+  fwd_constraint(m, w, g, iterations, tolerance);
+  for (int i = g.gl; i < m.nv; i += G) if (bad_value(w.qacc[i])) status |= ST_BAD_QACC;
+  euler(m, w, g, time);
+}
+
+}  // namespace tk

@@ -1,0 +1,185 @@
+// Device model upload + batched plain stepping (tokp_step_worlds).
+// Replaces mj_makeData/mj_step usage of MuJoCoHelper (src/PhysicsSimulators/MuJoCoHelper.cpp:877-923)
+// for batches of independent worlds.
+#include <cstring>
+#include <mutex>
+
+#include "step_dyn.cuh"
+#include "traj.h"
+
+namespace tokp {
+
+std::atomic<int64_t> g_launches{0};
+static std::mutex g_upload_mutex;
+
+void device_model_free(DeviceModel* dm) {
+  if (!dm) return;
+  if (dm->arena) cudaFree(dm->arena);
+  delete dm;
+}
+
+int lanes_for_model(const DM& dm) {
+  int k = dm.nv > dm.nbody ? dm.nv : dm.nbody;
+  if (k <= 10) return 8;
+  if (k <= 20) return 16;
+  return 32;
+}
+
+int ensure_device_model(const tokp_model* mc, const DM** out) {
+  tokp_model* m = const_cast<tokp_model*>(mc);
+  std::lock_guard<std::mutex> lock(g_upload_mutex);
+  if (m->dev) { *out = &m->dev->dm; return TOKP_OK; }
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+    set_error("no CUDA device available (tokp has no CPU fallback)");
+    return TOKP_ERR_CUDA;
+  }
+  const Model& h = m->host;
+  // pack every array into one host buffer (8-byte aligned), upload, then patch pointers
+  std::vector<uint8_t> buf;
+  auto add = [&](const void* p, size_t bytes) {
+    size_t off = buf.size();
+    buf.resize(off + ((bytes + 7) / 8) * 8 + 8);
+    if (bytes) std::memcpy(buf.data() + off, p, bytes);
+    return off;
+  };
+  struct Patch { size_t off; const void** dst; };
+  std::vector<Patch> patches;
+  auto* d = new DeviceModel();
+  DM& dm = d->dm;
+#define AI(name) patches.push_back({add(h.name.data(), h.name.size() * 4), (const void**)&dm.name});
+#define AR(name) patches.push_back({add(h.name.data(), h.name.size() * 8), (const void**)&dm.name});
+  AI(body_parentid) AI(body_rootid) AI(body_weldid) AI(body_jntadr) AI(body_jntnum) AI(body_dofadr) AI(body_dofnum)
+  AI(body_depth) AI(body_subtreemask_lo) AI(body_subtreemask_hi)
+  AI(jnt_type) AI(jnt_qposadr) AI(jnt_dofadr) AI(jnt_bodyid) AI(jnt_limited)
+  AI(dof_bodyid) AI(dof_jntid) AI(dof_parentid) AI(dof_ancmask_lo) AI(dof_ancmask_hi)
+  AI(geom_type) AI(geom_bodyid) AI(geom_condim) AI(geom_priority) AI(pair_geom1) AI(pair_geom2)
+  AI(actuator_trnid) AI(actuator_dofadr) AI(actuator_ctrllimited) AI(actuator_forcelimited) AI(actuator_biastype)
+  AR(qpos0) AR(body_pos) AR(body_quat) AR(body_ipos) AR(body_iquat) AR(body_mass) AR(body_inertia) AR(body_invweight0)
+  AR(body_gravcomp)
+  AR(jnt_pos) AR(jnt_axis) AR(jnt_range) AR(jnt_solref) AR(jnt_solimp) AR(jnt_margin)
+  AR(dof_armature) AR(dof_damping) AR(dof_invweight0)
+  AR(geom_size) AR(geom_pos) AR(geom_quat) AR(geom_friction) AR(geom_solref) AR(geom_solimp) AR(geom_margin) AR(geom_gap)
+  AR(geom_solmix) AR(geom_rbound)
+  AR(actuator_gear) AR(actuator_ctrlrange) AR(actuator_forcerange) AR(actuator_gainprm) AR(actuator_biasprm)
+#undef AI
+#undef AR
+  cudaError_t e = cudaMalloc(&d->arena, buf.size());
+  if (e == cudaSuccess) e = cudaMemcpy(d->arena, buf.data(), buf.size(), cudaMemcpyHostToDevice);
+  if (e != cudaSuccess) {
+    set_error(std::string("model upload: ") + cudaGetErrorString(e));
+    if (d->arena) cudaFree(d->arena);
+    delete d;
+    return TOKP_ERR_CUDA;
+  }
+  for (auto& p : patches) *p.dst = (const uint8_t*)d->arena + p.off;
+  dm.nq = h.nq(); dm.nv = h.nv(); dm.nu = h.nu(); dm.nbody = h.nbody(); dm.njnt = h.njnt(); dm.ngeom = h.ngeom();
+  dm.npair = h.npair(); dm.maxcontact = h.maxcontact() > 0 ? h.maxcontact() : 1; dm.maxefc = h.maxefc() > 0 ? h.maxefc() : 1;
+  dm.treedepth = h.dims[10];
+  dm.iterations = h.opt_int[0]; dm.ls_iterations = h.opt_int[1];
+  dm.timestep = h.opt_real[0];
+  dm.gravity[0] = h.opt_real[1]; dm.gravity[1] = h.opt_real[2]; dm.gravity[2] = h.opt_real[3];
+  dm.tolerance = h.opt_real[4]; dm.ls_tolerance = h.opt_real[5]; dm.meaninertia = h.opt_real[7];
+  dm.any_damping = 0; dm.any_gravcomp = 0;
+  for (double v : h.dof_damping) if (v > 0) dm.any_damping = 1;
+  for (double v : h.body_gravcomp) if (v != 0) dm.any_gravcomp = 1;
+  m->dev = d;
+  *out = &m->dev->dm;
+  return TOKP_OK;
+}
+
+// ---- tokp_step_worlds ---------------------------------------------------------------------------
+// in/out: host-layout snapshots [count][S] already on the device
+template <int G>
+__global__ void k_step_worlds(DM dm, const double* __restrict__ in, double* __restrict__ out, int* __restrict__ status,
+                              int count, int nsteps, int iterations, double tolerance, int S, int wsd) {
+  extern __shared__ double smem[];
+  constexpr int GPW = 32 / G;  // groups per warp
+  tk::Grp<G> g;
+  int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  int gidx = (blockIdx.x * (blockDim.x >> 5) + warp) * GPW + lane / G;  // world index
+  int slot = warp * GPW + lane / G;
+  if (gidx >= count) return;
+  tk::WS w;
+  tk::ws_init(w, smem + (size_t)slot * wsd, dm);
+  const double* s = in + (size_t)gidx * S;
+  int nq = dm.nq, nv = dm.nv;
+  double time = s[0];
+  for (int i = g.gl; i < nq; i += G) w.qpos[i] = s[1 + i];
+  for (int i = g.gl; i < nv; i += G) {
+    w.qvel[i] = s[1 + nq + i];
+    w.qacc[i] = s[1 + nq + nv + i];
+    w.warm[i] = s[1 + nq + 2 * nv + i];
+  }
+  for (int i = g.gl; i < dm.nu; i += G) w.ctrl[i] = s[S - dm.nu + i];
+  g.sync();
+  int st = 0;
+  for (int k = 0; k < nsteps; k++) tk::step<G>(dm, w, g, iterations, tolerance, time, st);
+  double* o = out + (size_t)gidx * S;
+  for (int i = g.gl; i < S; i += G) o[i] = 0.0;
+  g.sync();
+  if (g.gl == 0) o[0] = time;
+  for (int i = g.gl; i < nq; i += G) o[1 + i] = w.qpos[i];
+  for (int i = g.gl; i < nv; i += G) {
+    o[1 + nq + i] = w.qvel[i];
+    o[1 + nq + nv + i] = w.qacc[i];
+    o[1 + nq + 2 * nv + i] = w.warm[i];
+  }
+  for (int i = g.gl; i < dm.nu; i += G) o[S - dm.nu + i] = w.ctrl[i];
+  // OR-reduce the status bits across the group
+  int bits = 0;
+  for (int b = 0; b < 6; b++) if (g.any((st >> b) & 1)) bits |= (1 << b);
+  if (g.gl == 0) status[gidx] = bits;
+}
+
+}  // namespace tokp
+
+using namespace tokp;
+
+extern "C" int tokp_step_worlds(const tokp_model* m, const double* snapshots_in, double* snapshots_out, int count,
+                                int nsteps, int solver_iterations, double solver_tolerance, int* status) {
+  if (!m || !snapshots_in || !snapshots_out || count <= 0 || nsteps < 0) { set_error("tokp_step_worlds: bad argument"); return TOKP_ERR_ARG; }
+  const DM* dmp;
+  int rc = ensure_device_model(m, &dmp);
+  if (rc) return rc;
+  const DM& dm = *dmp;
+  int S = tokp_snapshot_size(m);
+  // applied forces must be zero (outside the hot-path scope)
+  for (int wi = 0; wi < count; wi++) {
+    const double* s = snapshots_in + (size_t)wi * S + 1 + dm.nq + 3 * dm.nv;
+    for (int i = 0; i < dm.nv + 6 * dm.nbody; i++)
+      if (s[i] != 0.0) { set_error("tokp_step_worlds: non-zero qfrc_applied/xfrc_applied unsupported"); return TOKP_ERR_UNSUPPORTED; }
+  }
+  double *d_in = nullptr, *d_out = nullptr;
+  int* d_st = nullptr;
+  size_t bytes = (size_t)count * S * sizeof(double);
+  TOKP_CUDA(cudaMalloc(&d_in, bytes));
+  TOKP_CUDA(cudaMalloc(&d_out, bytes));
+  TOKP_CUDA(cudaMalloc(&d_st, count * sizeof(int)));
+  TOKP_CUDA(cudaMemcpy(d_in, snapshots_in, bytes, cudaMemcpyHostToDevice));
+  int iters = solver_iterations < 0 ? dm.iterations : solver_iterations;
+  double tol = solver_iterations < 0 ? dm.tolerance : solver_tolerance;
+  int G = lanes_for_model(dm);
+  int wsd = tk::ws_doubles(dm);
+  int gpw = 32 / G;
+  int warps = 4;
+  while (warps > 1 && (size_t)warps * gpw * wsd * 8 > 200 * 1024) warps >>= 1;
+  size_t smem = (size_t)warps * gpw * wsd * 8;
+  if (smem > 227 * 1024) { set_error("model too large for the shared-memory workspace"); return TOKP_ERR_UNSUPPORTED; }
+  int worlds_per_block = warps * gpw;
+  int blocks = (count + worlds_per_block - 1) / worlds_per_block;
+#define LAUNCH(GG)                                                                                                  \
+  TOKP_CUDA(cudaFuncSetAttribute(k_step_worlds<GG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));       \
+  k_step_worlds<GG><<<blocks, warps * 32, smem>>>(dm, d_in, d_out, d_st, count, nsteps, iters, tol, S, wsd);
+  if (G == 8) { LAUNCH(8) } else if (G == 16) { LAUNCH(16) } else { LAUNCH(32) }
+#undef LAUNCH
+  g_launches++;
+  TOKP_CUDA(cudaGetLastError());
+  TOKP_CUDA(cudaDeviceSynchronize());
+  TOKP_CUDA(cudaMemcpy(snapshots_out, d_out, bytes, cudaMemcpyDeviceToHost));
+  if (status) TOKP_CUDA(cudaMemcpy(status, d_st, count * sizeof(int), cudaMemcpyDeviceToHost));
+  cudaFree(d_in); cudaFree(d_out); cudaFree(d_st);
+  return TOKP_OK;
+}
+
+extern "C" int64_t tokp_launch_count(void) { return g_launches.load(); }

@@ -1,0 +1,73 @@
+// Device arena of a trajectory batch + common CUDA helpers (internal).
+#pragma once
+#include <cuda_runtime.h>
+
+#include <atomic>
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include "device_model.h"
+#include "tokp_internal.h"
+
+namespace tokp {
+
+extern std::atomic<int64_t> g_launches;
+
+#define TOKP_CUDA(expr)                                                                         \
+  do {                                                                                          \
+    cudaError_t _e = (expr);                                                                    \
+    if (_e != cudaSuccess) {                                                                    \
+      tokp::set_error(std::string(#expr) + ": " + cudaGetErrorString(_e));                      \
+      return TOKP_ERR_CUDA;                                                                     \
+    }                                                                                           \
+  } while (0)
+
+// returns TOKP_OK or TOKP_ERR_CUDA; uploads on first use
+int ensure_device_model(const tokp_model* m, const DM** out);
+
+// number of lanes per world for a model (8, 16 or 32)
+int lanes_for_model(const DM& dm);
+
+// compact device snapshot: [time | qpos nq | qvel nv | qacc nv | warm nv | ctrl nu]
+inline int dsnap_size(const DM& dm) { return 1 + dm.nq + 3 * dm.nv + dm.nu; }
+
+struct TaskDev {
+  int kind, n, m, nr;
+  int kp_method, min_N, max_N;
+  double iter_thr;
+  const int *qpos_adr, *dof_adr, *ctrl_adr;           // device
+  const double *weight, *weight_terminal, *jerk_thr, *vel_thr, *ctrl_limits;  // device
+};
+
+}  // namespace tokp
+
+struct tokp_traj {
+  const tokp_model* model = nullptr;
+  DM dm;
+  tokp::TaskDev task;
+  int B = 0, T = 0, S = 0 /* host snapshot size */, SD = 0 /* device snapshot size */, W = 0 /* worlds per key-point */;
+  int n = 0, m = 0, nx = 0, nr = 0, G = 8;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  void* arena = nullptr;
+  size_t arena_bytes = 0;
+  // device arrays (all inside arena)
+  double *snap, *X, *U, *resid, *A, *Bm, *rx, *ru, *lx, *lxx, *lu, *luu, *K, *k, *target;
+  double *cand;       // [B][NA][T+1][SD] rollout buffers (zero-initialised, rows 0 and T never written)
+  double *cand_cost;  // [B][NA]
+  double *fd_out;     // [B][T][W][nq+nv]
+  unsigned long long* kp_mask;  // [B][T]
+  int* kp_flags;      // [B]: bit0 = velocity_change duplicate last row
+  int *kp_prev, *kp_next;  // [B][T][n]
+  int* status;        // [B][T][W]
+  double *cost, *deltaJ, *lambda_d;  // [B]
+  int* bp_ok;         // [B]
+  int* task_ints;     // qpos_adr | dof_adr | ctrl_adr
+  double* task_reals;
+  static const int NA = 6;
+  bool have_rollout = false;
+  double timers[3] = {0, 0, 0};
+  int64_t counters[4] = {0, 0, 0, 0};
+  std::vector<double> h_stage;  // host staging
+};

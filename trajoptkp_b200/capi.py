@@ -66,6 +66,8 @@ def lib():
     L.tokp_model_get_real.argtypes = [vp, C.c_char_p, _dp, C.c_int]
     L.tokp_model_get_int.argtypes = [vp, C.c_char_p, C.POINTER(C.c_int32), C.c_int]
     L.tokp_snapshot_size.argtypes = [vp]
+    L.tokp_step_worlds.argtypes = [vp, _dp, _dp, C.c_int, C.c_int, C.c_int, C.c_double, _ip]
+    L.tokp_launch_count.restype = C.c_int64
     if hasattr(L, "tokp_traj_create"):
         L.tokp_traj_create.argtypes = [vp, C.POINTER(TaskDesc), C.c_int, C.c_int, C.POINTER(vp)]
         L.tokp_traj_destroy.argtypes = [vp]
@@ -73,7 +75,6 @@ def lib():
         L.tokp_traj_set_keypoint_method.argtypes = [vp, C.c_int, C.c_int, C.c_int, _dp, _dp, C.c_double]
         L.tokp_traj_set_snapshot.argtypes = [vp, C.c_int, C.c_int, _dp]
         L.tokp_traj_get_snapshot.argtypes = [vp, C.c_int, C.c_int, _dp]
-        L.tokp_step_worlds.argtypes = [vp, _dp, _dp, C.c_int, C.c_int, C.c_int, C.c_double, _ip]
         L.tokp_rollout.argtypes = [vp, _dp, _dp, _dp]
         L.tokp_keypoints.argtypes = [vp, _ip, _ip, _dp]
         L.tokp_traj_set_keypoints.argtypes = [vp, C.c_int, _ip, _ip]
@@ -91,7 +92,6 @@ def lib():
         L.tokp_traj_set.argtypes = [vp, C.c_int, C.c_char_p, _dp, C.c_int]
         L.tokp_traj_counters.argtypes = [vp, C.POINTER(C.c_int64)]
         L.tokp_timers.argtypes = [vp, _dp]
-        L.tokp_launch_count.restype = C.c_int64
     _lib = L
     return L
 

@@ -167,3 +167,128 @@ class Model:
         nv = self.nv
         return dict(time=s[0], qpos=s[1:o], qvel=s[o:o + nv], qacc=s[o + nv:o + 2 * nv], warm=s[o + 2 * nv:o + 3 * nv],
                     ctrl=s[self.S - self.nu:])
+
+
+class Traj:
+    """Batch of B trajectories on the device (tokp_traj)."""
+
+    def __init__(self, task_cfg, horizon, batch=1):
+        self.tc, self.model, self.T, self.B = task_cfg, task_cfg.model, horizon, batch
+        self.n, self.m, self.nr = task_cfg.n, task_cfg.m, task_cfg.nr
+        self.nx = 2 * self.n
+        self._desc = task_cfg.desc()
+        h = C.c_void_p()
+        check(lib().tokp_traj_create(self.model.h, C.byref(self._desc), horizon, batch, C.byref(h)))
+        self.h = h
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().tokp_traj_destroy(self.h)
+            self.h = None
+
+    def set_targets(self, b, targets):
+        t = np.ascontiguousarray(targets, dtype=np.float64)
+        assert t.size == self.nr
+        check(lib().tokp_traj_set_targets(self.h, b, _d(t)))
+
+    def set_keypoint_method(self, method, min_N, max_N, jerk_thr=None, vel_thr=None, iter_thr=0.0):
+        j = None if jerk_thr is None else np.ascontiguousarray(jerk_thr, dtype=np.float64)
+        v = None if vel_thr is None else np.ascontiguousarray(vel_thr, dtype=np.float64)
+        check(lib().tokp_traj_set_keypoint_method(self.h, method, min_N, max_N, _d(j), _d(v), float(iter_thr)))
+
+    def set_snapshot(self, b, t, snap):
+        s = np.ascontiguousarray(snap, dtype=np.float64)
+        check(lib().tokp_traj_set_snapshot(self.h, b, t, _d(s)))
+
+    def get_snapshot(self, b, t):
+        s = np.zeros(self.model.S)
+        check(lib().tokp_traj_get_snapshot(self.h, b, t, _d(s)))
+        return s
+
+    def rollout(self, snap0, U):
+        s = np.ascontiguousarray(np.broadcast_to(np.asarray(snap0, dtype=np.float64), (self.B, self.model.S)))
+        U = np.ascontiguousarray(np.broadcast_to(np.asarray(U, dtype=np.float64), (self.B, self.T, self.m)))
+        cost = np.zeros(self.B)
+        check(lib().tokp_rollout(self.h, _d(s), _d(U), _d(cost)))
+        return cost
+
+    def keypoints(self):
+        counts = np.zeros((self.B, self.T), dtype=np.int32)
+        idx = np.zeros((self.B, self.T, 2 * self.n), dtype=np.int32)
+        pct = np.zeros((self.B, self.n))
+        check(lib().tokp_keypoints(self.h, _i(counts), _i(idx), _d(pct)))
+        rows = [[idx[b, t, :counts[b, t]].tolist() for t in range(self.T)] for b in range(self.B)]
+        return rows, pct
+
+    def set_keypoints(self, b, rows):
+        counts = np.array([len(r) for r in rows], dtype=np.int32)
+        idx = np.array([v for r in rows for v in r] + [0], dtype=np.int32)
+        check(lib().tokp_traj_set_keypoints(self.h, b, _i(counts), _i(idx)))
+
+    def dynamics_derivs(self, central=True, eps=1e-6):
+        check(lib().tokp_dynamics_derivs(self.h, int(central), eps))
+
+    def dynamics_derivs_cols(self, b, t, cols, central=True, eps=1e-6, A=None, B=None):
+        nx = self.nx
+        A = np.zeros((nx, nx), order="F") if A is None else A
+        Bm = np.zeros((nx, max(self.m, 1)), order="F") if B is None else B
+        cols = np.ascontiguousarray(cols, dtype=np.int32)
+        check(lib().tokp_dynamics_derivs_cols(self.h, b, t, _i(cols), len(cols), int(central), eps, _d(A), nx, _d(Bm), nx))
+        return A, Bm[:, :self.m]
+
+    def interpolate(self):
+        check(lib().tokp_interpolate(self.h))
+
+    def cost_derivs(self, central=True, eps=1e-6):
+        check(lib().tokp_cost_derivs(self.h, int(central), eps))
+
+    def generate_derivatives(self):
+        check(lib().tokp_generate_derivatives(self.h))
+
+    def backward_pass(self, lam):
+        lam = np.ascontiguousarray(np.broadcast_to(np.asarray(lam, dtype=np.float64), (self.B,)))
+        ok = np.zeros(self.B, dtype=np.int32)
+        dJ = np.zeros(self.B)
+        check(lib().tokp_backward_pass(self.h, _d(lam), _i(ok), _d(dJ)))
+        return ok, dJ
+
+    def forward_pass(self, alphas):
+        a = np.ascontiguousarray(alphas, dtype=np.float64)
+        costs = np.zeros((self.B, len(a)))
+        check(lib().tokp_forward_pass(self.h, _d(a), len(a), _d(costs)))
+        return costs
+
+    def accept(self, b, alpha_idx):
+        check(lib().tokp_accept(self.h, b, alpha_idx))
+
+    def optimise(self, snap0, U, max_it, min_it, lam=None):
+        s = np.ascontiguousarray(np.broadcast_to(np.asarray(snap0, dtype=np.float64), (self.B, self.model.S)))
+        U = np.ascontiguousarray(np.broadcast_to(np.asarray(U, dtype=np.float64), (self.B, self.T, self.m)))
+        lamv = None if lam is None else np.ascontiguousarray(np.broadcast_to(np.asarray(lam, dtype=np.float64), (self.B,)))
+        Uo = np.zeros((self.B, self.T, self.m))
+        stats = np.zeros((self.B, 8))
+        check(lib().tokp_optimise(self.h, _d(s), _d(U), max_it, min_it, _d(lamv), _d(Uo), _d(stats)))
+        return Uo, stats
+
+    def get(self, b, name):
+        c = lib().tokp_traj_get(self.h, b, name.encode(), None, 0)
+        if c <= -1000000:
+            raise KeyError(name)
+        out = np.zeros(-c if c < 0 else c)
+        got = lib().tokp_traj_get(self.h, b, name.encode(), _d(out), out.size)
+        assert got == out.size, (name, got)
+        return out
+
+    def set(self, b, name, arr):
+        a = np.ascontiguousarray(arr, dtype=np.float64).ravel()
+        check(lib().tokp_traj_set(self.h, b, name.encode(), _d(a), a.size))
+
+    def counters(self):
+        c = (C.c_int64 * 4)()
+        check(lib().tokp_traj_counters(self.h, c))
+        return list(c)
+
+    def timers(self):
+        t = np.zeros(3)
+        check(lib().tokp_timers(self.h, _d(t)))
+        return t

@@ -1,0 +1,271 @@
+// Batched finite-difference dynamics derivatives: every (trajectory b, key-point t, perturbed column, +-eps)
+// pair is one independent one-step world; one launch per iteration.
+// Replaces Optimiser::ComputeDynamicsDerivativesAtKeypoints + WorkerComputeDerivatives
+// (src/Optimiser/Optimiser.cpp:239-323) and the loop nest of Differentiator::DynamicsDerivatives
+// (src/Differentiator/Differentiator.cpp:8-462).  mj_stepSkip's stage reuse is an optimisation that does
+// not change results (a skipped stage would recompute identical values), so each world runs the full step.
+#include "step_dyn.cuh"
+#include "traj.h"
+
+namespace tokp {
+
+// world slot layout inside one key-point (W = 1 + 2m + 4n):
+//   0                      nominal
+//   1 + 2i + s             control i,  s = 0 (+eps) / 1 (-eps)
+//   1 + 2m + 2i + s        velocity i
+//   1 + 2m + 2n + 2i + s   position i
+struct FdArgs {
+  const double* snap;               // [B][T+1][SD]
+  double* fd_out;                   // [B][T][W][nq+nv]
+  int* status;                      // [B][T][W]: bit 30 = computed, low bits = step status
+  const unsigned long long* mask;   // [B][T]
+  const int* rows;                  // optional list of b*T+t rows (nullptr = all)
+  int nrows;
+  int B, T, SD, W, n, m;
+  const int *qpos_adr, *dof_adr, *ctrl_adr;
+  const double* ctrl_limits;
+  int central;
+  double eps;
+  int iterations;
+  double tolerance;
+};
+
+template <int G>
+__global__ void k_fd_worlds(DM dm, FdArgs a, int wsd) {
+  extern __shared__ double smem[];
+  constexpr int GPW = 32 / G;
+  tk::Grp<G> g;
+  int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  long long gidx = ((long long)blockIdx.x * (blockDim.x >> 5) + warp) * GPW + lane / G;
+  int slot_s = warp * GPW + lane / G;
+  long long total = (long long)a.nrows * a.W;
+  if (gidx >= total) return;
+  int rowi = (int)(gidx / a.W), slot = (int)(gidx - (long long)rowi * a.W);
+  int row = a.rows ? a.rows[rowi] : rowi;
+  int b = row / a.T, t = row - b * a.T;
+  unsigned long long mask = a.mask[row];
+  int* st_out = a.status + (size_t)row * a.W + slot;
+  if (mask == 0ull) { if (g.gl == 0) *st_out = 0; return; }
+  // decode
+  int kind = 0, col = 0, sgn = 0;
+  if (slot > 0) {
+    int s = slot - 1;
+    if (s < 2 * a.m) { kind = 1; col = s >> 1; sgn = s & 1; }
+    else if (s < 2 * a.m + 2 * a.n) { s -= 2 * a.m; kind = 2; col = s >> 1; sgn = s & 1; }
+    else { s -= 2 * a.m + 2 * a.n; kind = 3; col = s >> 1; sgn = s & 1; }
+    if (!((mask >> col) & 1ull)) { if (g.gl == 0) *st_out = 0; return; }
+  }
+  const double* s = a.snap + ((size_t)b * (a.T + 1) + t) * a.SD;
+  int nq = dm.nq, nv = dm.nv;
+  // control perturbations are clamp-aware (Differentiator.cpp:98-102,136-143); forward mode drops the minus
+  // side unless the plus side is infeasible
+  if (kind == 1) {
+    double u = s[1 + nq + 3 * nv + a.ctrl_adr[col]];
+    bool fwd_ok = !(u + a.eps > a.ctrl_limits[2 * col + 1]);
+    bool back_wanted = a.central || !fwd_ok;
+    bool back_ok = back_wanted && !(u - a.eps < a.ctrl_limits[2 * col]);
+    if ((sgn == 0 && !fwd_ok) || (sgn == 1 && !back_ok)) { if (g.gl == 0) *st_out = 0; return; }
+  } else if (kind >= 2 && sgn == 1 && !a.central) {
+    if (g.gl == 0) *st_out = 0;
+    return;
+  }
+  tk::WS w;
+  tk::ws_init(w, smem + (size_t)slot_s * wsd, dm);
+  double time = s[0];
+  for (int i = g.gl; i < nq; i += G) w.qpos[i] = s[1 + i];
+  for (int i = g.gl; i < nv; i += G) {
+    w.qvel[i] = s[1 + nq + i];
+    w.qacc[i] = s[1 + nq + nv + i];
+    w.warm[i] = s[1 + nq + 2 * nv + i];
+  }
+  for (int i = g.gl; i < dm.nu; i += G) w.ctrl[i] = s[1 + nq + 3 * nv + i];
+  g.sync();
+  if (g.gl == 0 && kind != 0) {
+    double e = sgn ? -a.eps : a.eps;
+    if (kind == 1) {
+      w.ctrl[a.ctrl_adr[col]] += e;
+    } else if (kind == 2) {
+      w.qvel[a.dof_adr[col]] += e;
+    } else {
+      // mj_integratePos(qpos, e_dof, +-eps)
+      int d = a.dof_adr[col];
+      int j = dm.dof_jntid[d];
+      int pa = dm.jnt_qposadr[j], va = dm.jnt_dofadr[j];
+      if (dm.jnt_type[j] == tk::JNT_FREE) {
+        int kk = d - va;
+        if (kk < 3) w.qpos[pa + kk] += e * 1.0;
+        else {
+          double vel[3] = {0.0, 0.0, 0.0};
+          vel[kk - 3] = 1.0;
+          tk::quat_integrate(&w.qpos[pa + 3], vel, e);
+        }
+      } else {
+        w.qpos[pa] += e * 1.0;
+      }
+    }
+  }
+  g.sync();
+  int st = 0;
+  tk::step<G>(dm, w, g, a.iterations, a.tolerance, time, st);
+  double* o = a.fd_out + ((size_t)row * a.W + slot) * (nq + nv);
+  for (int i = g.gl; i < nq; i += G) o[i] = w.qpos[i];
+  for (int i = g.gl; i < nv; i += G) o[nq + i] = w.qvel[i];
+  int bits = 0;
+  for (int k = 0; k < 6; k++) if (g.any((st >> k) & 1)) bits |= (1 << k);
+  if (g.gl == 0) *st_out = bits | (1 << 30);
+}
+
+// (q2 - q1)/h on the configuration manifold for one dof (mj_differentiatePos restricted to a dof)
+__device__ inline double diff_pos_dof(const DM& dm, const double* q1, const double* q2, double h, int d) {
+  int j = dm.dof_jntid[d];
+  int pa = dm.jnt_qposadr[j], va = dm.jnt_dofadr[j];
+  if (dm.jnt_type[j] == tk::JNT_FREE) {
+    int kk = d - va;
+    if (kk < 3) return (q2[pa + kk] - q1[pa + kk]) / h;
+    double v[3];
+    tk::sub_quat(v, q1 + pa + 3, q2 + pa + 3);
+    return v[kk - 3] / h;
+  }
+  return (q2[pa] - q1[pa]) / h;
+}
+
+// one thread per (row, kind, column, state row): differencing + scatter (Differentiator.cpp:167-222,286-321,386-457)
+__global__ void k_fd_assemble(DM dm, FdArgs a, double* __restrict__ A, double* __restrict__ Bm) {
+  int nx = 2 * a.n;
+  long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  long long per_row = (long long)(a.m + 2 * a.n) * nx;
+  long long total = (long long)a.nrows * per_row;
+  if (gid >= total) return;
+  int rowi = (int)(gid / per_row);
+  int rem = (int)(gid - (long long)rowi * per_row);
+  int c = rem / nx, j = rem - c * nx;
+  int row = a.rows ? a.rows[rowi] : rowi;
+  int kind, col;
+  if (c < a.m) { kind = 1; col = c; }
+  else if (c < a.m + a.n) { kind = 2; col = c - a.m; }
+  else { kind = 3; col = c - a.m - a.n; }
+  unsigned long long mask = a.mask[row];
+  if (!((mask >> col) & 1ull)) return;
+  int nq = dm.nq, nv = dm.nv, S2 = nq + nv;
+  int base = (kind == 1) ? 1 : (kind == 2 ? 1 + 2 * a.m : 1 + 2 * a.m + 2 * a.n);
+  int sp = base + 2 * col, sm = sp + 1;
+  const int* st = a.status + (size_t)row * a.W;
+  bool vp = (st[sp] >> 30) & 1, vm = (st[sm] >> 30) & 1;
+  if (!vp && !vm) return;
+  const double* out0 = a.fd_out + (size_t)row * a.W * S2;
+  const double *qa, *qb;
+  double h;
+  if (vp && vm) { qa = out0 + (size_t)sm * S2; qb = out0 + (size_t)sp * S2; h = 2 * a.eps; }
+  else if (vp) { qa = out0; qb = out0 + (size_t)sp * S2; h = a.eps; }
+  else { qa = out0 + (size_t)sm * S2; qb = out0; h = a.eps; }
+  double val;
+  if (j < a.n) val = diff_pos_dof(dm, qa, qb, h, a.dof_adr[j]);
+  else { int d = a.dof_adr[j - a.n]; val = (qb[nq + d] - qa[nq + d]) / h; }
+  if (kind == 1) Bm[(size_t)row * nx * a.m + (size_t)col * nx + j] = val;
+  else if (kind == 2) A[(size_t)row * nx * nx + (size_t)(col + a.n) * nx + j] = val;
+  else A[(size_t)row * nx * nx + (size_t)col * nx + j] = val;
+}
+
+// launch helper shared by tokp_dynamics_derivs / _cols / iterative_error
+int launch_fd(tokp_traj* tr, const unsigned long long* mask, const int* rows, int nrows, int central, double eps) {
+  const DM& dm = tr->dm;
+  FdArgs a;
+  a.snap = tr->snap; a.fd_out = tr->fd_out; a.status = tr->status; a.mask = mask; a.rows = rows; a.nrows = nrows;
+  a.B = tr->B; a.T = tr->T; a.SD = tr->SD; a.W = tr->W; a.n = tr->n; a.m = tr->m;
+  a.qpos_adr = tr->task.qpos_adr; a.dof_adr = tr->task.dof_adr; a.ctrl_adr = tr->task.ctrl_adr;
+  a.ctrl_limits = tr->task.ctrl_limits;
+  a.central = central; a.eps = eps;
+  a.iterations = 5; a.tolerance = 0.0;  // MuJoCoHelper::InitModelForFiniteDifferencing (MuJoCoHelper.cpp:925-931)
+  int G = tr->G, gpw = 32 / G;
+  int wsd = tk::ws_doubles(dm);
+  int warps = 4;
+  while (warps > 1 && (size_t)warps * gpw * wsd * 8 > 110 * 1024) warps >>= 1;
+  size_t smem = (size_t)warps * gpw * wsd * 8;
+  if (smem > 227 * 1024) { set_error("model too large for the shared-memory workspace"); return TOKP_ERR_UNSUPPORTED; }
+  long long worlds = (long long)nrows * tr->W;
+  int wpb = warps * gpw;
+  int blocks = (int)((worlds + wpb - 1) / wpb);
+  if (blocks < 1) return TOKP_OK;
+#define LAUNCH(GG)                                                                                             \
+  TOKP_CUDA(cudaFuncSetAttribute(k_fd_worlds<GG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));    \
+  k_fd_worlds<GG><<<blocks, warps * 32, smem, tr->stream>>>(dm, a, wsd);
+  if (G == 8) { LAUNCH(8) } else if (G == 16) { LAUNCH(16) } else { LAUNCH(32) }
+#undef LAUNCH
+  g_launches++;
+  long long tot = (long long)nrows * (tr->m + 2 * tr->n) * tr->nx;
+  k_fd_assemble<<<(int)((tot + 255) / 256), 256, 0, tr->stream>>>(dm, a, tr->A, tr->Bm);
+  g_launches++;
+  TOKP_CUDA(cudaGetLastError());
+  tr->counters[2] += 2;
+  return TOKP_OK;
+}
+
+}  // namespace tokp
+
+using namespace tokp;
+
+extern "C" int tokp_dynamics_derivs(tokp_traj* tr, int central_diff, double eps) {
+  if (!tr || !(eps > 0)) { set_error("tokp_dynamics_derivs: bad argument"); return TOKP_ERR_ARG; }
+  cudaEventRecord(tr->ev0, tr->stream);
+  int rc = launch_fd(tr, tr->kp_mask, nullptr, tr->B * tr->T, central_diff, eps);
+  if (rc) return rc;
+  cudaEventRecord(tr->ev1, tr->stream);
+  TOKP_CUDA(cudaStreamSynchronize(tr->stream));
+  float ms = 0;
+  cudaEventElapsedTime(&ms, tr->ev0, tr->ev1);
+  tr->timers[0] = ms;
+  // counters: worlds actually simulated and Jacobians (|C|/n per row)
+  std::vector<unsigned long long> hm((size_t)tr->B * tr->T);
+  TOKP_CUDA(cudaMemcpy(hm.data(), tr->kp_mask, hm.size() * 8, cudaMemcpyDeviceToHost));
+  long long worlds = 0, cols = 0;
+  for (auto mk : hm) {
+    if (!mk) continue;
+    int c = __builtin_popcountll(mk);
+    int cm = __builtin_popcountll(mk & ((tr->m >= 64) ? ~0ull : ((1ull << tr->m) - 1)));
+    worlds += 1 + 2 * cm + 4 * c;
+    cols += c;
+  }
+  tr->counters[0] = worlds;
+  tr->counters[1] = (int64_t)((double)cols / tr->n * 1e6);
+  return TOKP_OK;
+}
+
+extern "C" int tokp_dynamics_derivs_cols(tokp_traj* tr, int b, int t, const int* cols, int ncols, int central_diff,
+                                         double eps, double* A, int lda, double* B, int ldb) {
+  if (!tr || !cols || !A || !B || b < 0 || b >= tr->B || t < 0 || t >= tr->T || ncols < 0 || lda < tr->nx || ldb < tr->nx) {
+    set_error("tokp_dynamics_derivs_cols: bad argument");
+    return TOKP_ERR_ARG;
+  }
+  unsigned long long mk = 0;
+  for (int i = 0; i < ncols; i++) {
+    if (cols[i] < 0 || cols[i] >= tr->n) { set_error("tokp_dynamics_derivs_cols: column out of range"); return TOKP_ERR_ARG; }
+    mk |= 1ull << cols[i];
+  }
+  int row = b * tr->T + t;
+  // temporary one-row mask + row list live at the end of the status array's row (reuse small scratch allocations)
+  unsigned long long* d_mask;
+  int* d_row;
+  TOKP_CUDA(cudaMalloc(&d_mask, (size_t)tr->B * tr->T * 8));
+  TOKP_CUDA(cudaMalloc(&d_row, 4));
+  TOKP_CUDA(cudaMemsetAsync(d_mask, 0, (size_t)tr->B * tr->T * 8, tr->stream));
+  TOKP_CUDA(cudaMemcpyAsync(d_mask + row, &mk, 8, cudaMemcpyHostToDevice, tr->stream));
+  TOKP_CUDA(cudaMemcpyAsync(d_row, &row, 4, cudaMemcpyHostToDevice, tr->stream));
+  int rc = launch_fd(tr, d_mask, d_row, 1, central_diff, eps);
+  if (rc) { cudaFree(d_mask); cudaFree(d_row); return rc; }
+  int nx = tr->nx, m = tr->m, n = tr->n;
+  std::vector<double> hA((size_t)nx * nx), hB((size_t)nx * (m > 0 ? m : 1));
+  TOKP_CUDA(cudaMemcpyAsync(hA.data(), tr->A + (size_t)row * nx * nx, hA.size() * 8, cudaMemcpyDeviceToHost, tr->stream));
+  if (m > 0) TOKP_CUDA(cudaMemcpyAsync(hB.data(), tr->Bm + (size_t)row * nx * m, (size_t)nx * m * 8, cudaMemcpyDeviceToHost, tr->stream));
+  TOKP_CUDA(cudaStreamSynchronize(tr->stream));
+  cudaFree(d_mask);
+  cudaFree(d_row);
+  for (int i = 0; i < ncols; i++) {
+    int c = cols[i];
+    for (int j = 0; j < nx; j++) {
+      A[(size_t)c * lda + j] = hA[(size_t)c * nx + j];
+      A[(size_t)(c + n) * lda + j] = hA[(size_t)(c + n) * nx + j];
+      if (c < m) B[(size_t)c * ldb + j] = hB[(size_t)c * nx + j];
+    }
+  }
+  return TOKP_OK;
+}

@@ -1,0 +1,151 @@
+// Rollout kernels: nominal rollout and the alpha-batched closed-loop line-search rollouts, persistent over
+// the whole horizon in one launch.  Replaces iLQR::RolloutTrajectory (src/Optimiser/iLQR.cpp:202-254) and
+// iLQR::ForwardsPassParallel (:824-934) + Optimiser::SaveSystemStateToRolloutData (Optimiser.cpp:416-438).
+#include "step_dyn.cuh"
+#include "task_dev.cuh"
+#include "traj.h"
+
+namespace tokp {
+
+struct RollArgs {
+  double* snap;        // [B][T+1][SD] nominal snapshots
+  double* X;           // [B][T+1][nx]
+  double* U;           // [B][T][m]      U_old (written in nominal mode, read in forward mode)
+  double* resid;       // [B][T+1][nr]   (written in nominal mode)
+  const double* U_in;  // [B][T][m]      nominal mode: controls to apply
+  const double* K;     // [B][T][m*nx]
+  const double* k;     // [B][T][m]
+  const double* target;  // [B][nr]
+  double* cand;        // [B][NA][T+1][SD]
+  double* cost;        // nominal: [B]; forward: [B][NA]
+  const double* alphas;  // [NA]
+  int B, T, SD, NA, mode;  // mode 0 nominal, 1 forward pass
+  int iterations;
+  double tolerance;
+  TaskDev task;
+};
+
+template <int G>
+__global__ void k_rollout(DM dm, RollArgs a, int wsd) {
+  extern __shared__ double smem[];
+  tk::Grp<G> g;
+  int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // one world per warp (latency path): only the first group of each warp works
+  if (lane / G != 0) return;
+  int widx = blockIdx.x * (blockDim.x >> 5) + warp;
+  int nworlds = a.mode == 0 ? a.B : a.B * a.NA;
+  if (widx >= nworlds) return;
+  int b = a.mode == 0 ? widx : widx / a.NA;
+  int ai = a.mode == 0 ? 0 : widx - b * a.NA;
+  tk::WS w;
+  tk::ws_init(w, smem + (size_t)warp * wsd, dm);
+  const TaskDev& tk_ = a.task;
+  int nq = dm.nq, nv = dm.nv, nu = dm.nu, n = tk_.n, m = tk_.m, nx = 2 * n, nr = tk_.nr, T = a.T, SD = a.SD;
+  double* snapb = a.snap + (size_t)b * (T + 1) * SD;
+  const double* s = snapb;
+  double time = s[0];
+  for (int i = g.gl; i < nq; i += G) w.qpos[i] = s[1 + i];
+  for (int i = g.gl; i < nv; i += G) {
+    w.qvel[i] = s[1 + nq + i];
+    w.qacc[i] = s[1 + nq + nv + i];
+    w.warm[i] = s[1 + nq + 2 * nv + i];
+  }
+  for (int i = g.gl; i < nu; i += G) w.ctrl[i] = s[1 + nq + 3 * nv + i];
+  g.sync();
+  double* Xb = a.X + (size_t)b * (T + 1) * nx;
+  double* Ub = a.U + (size_t)b * T * m;
+  const double* tgt = a.target + (size_t)b * nr;
+  double cost = 0.0;
+  int st = 0;
+  double alpha = a.mode ? a.alphas[ai] : 0.0;
+  double* candb = a.cand + ((size_t)b * a.NA + ai) * (T + 1) * SD;
+  if (a.mode == 0) {
+    for (int i = g.gl; i < n; i += G) { Xb[i] = w.qpos[tk_.qpos_adr[i]]; Xb[n + i] = w.qvel[tk_.dof_adr[i]]; }
+  }
+  for (int t = 0; t < T; t++) {
+    if (a.mode == 0) {
+      for (int i = g.gl; i < m; i += G) w.ctrl[tk_.ctrl_adr[i]] = a.U_in[((size_t)b * T + t) * m + i];
+      g.sync();
+    } else {
+      // U_new = U_old[t] + alpha k[t] + K[t] (x - X_old[t]), clamped (iLQR.cpp:847-890)
+      const double* Kt = a.K + ((size_t)b * T + t) * m * nx;
+      const double* kt = a.k + ((size_t)b * T + t) * m;
+      const double* Xo = Xb + (size_t)t * nx;
+      for (int i = g.gl; i < m; i += G) {
+        double gsum = 0.0;
+        for (int c = 0; c < nx; c++) {
+          double xc = c < n ? w.qpos[tk_.qpos_adr[c]] : w.qvel[tk_.dof_adr[c - n]];
+          gsum += Kt[c * m + i] * (xc - Xo[c]);
+        }
+        double u = Ub[(size_t)t * m + i] + (alpha * kt[i]) + gsum;
+        if (u > tk_.ctrl_limits[2 * i + 1]) u = tk_.ctrl_limits[2 * i + 1];
+        if (u < tk_.ctrl_limits[2 * i]) u = tk_.ctrl_limits[2 * i];
+        w.tmpv[i] = u;
+      }
+      g.sync();
+      for (int i = g.gl; i < m; i += G) w.ctrl[tk_.ctrl_adr[i]] = w.tmpv[i];
+      g.sync();
+      // cost of (x_t, u_t) before the step (iLQR.cpp:896-912)
+      if (g.gl == 0) {
+        double r[kMaxResid];
+        task_residuals(tk_, w.qpos, w.qvel, w.ctrl, tgt, r);
+        cost = __dadd_rn(cost, task_cost(tk_, r, t == T - 1));
+      }
+    }
+    tk::step<G>(dm, w, g, a.iterations, a.tolerance, time, st);
+    if (a.mode == 0) {
+      // residuals / cost after the step, X_old, U_old, saved[t+1] (iLQR.cpp:222-246)
+      if (g.gl == 0) {
+        double r[kMaxResid];
+        task_residuals(tk_, w.qpos, w.qvel, w.ctrl, tgt, r);
+        double* rb = a.resid + ((size_t)b * (T + 1) + t) * nr;
+        for (int i = 0; i < nr; i++) rb[i] = r[i];
+        cost = __dadd_rn(cost, task_cost(tk_, r, t == T - 1));
+      }
+      double* Xn = Xb + (size_t)(t + 1) * nx;
+      for (int i = g.gl; i < n; i += G) { Xn[i] = w.qpos[tk_.qpos_adr[i]]; Xn[n + i] = w.qvel[tk_.dof_adr[i]]; }
+      for (int i = g.gl; i < m; i += G) Ub[(size_t)t * m + i] = w.ctrl[tk_.ctrl_adr[i]];
+    }
+    if (a.mode == 0 || t != 0) {
+      double* o = a.mode == 0 ? snapb + (size_t)(t + 1) * SD : candb + (size_t)t * SD;
+      if (g.gl == 0) o[0] = time;
+      for (int i = g.gl; i < nq; i += G) o[1 + i] = w.qpos[i];
+      for (int i = g.gl; i < nv; i += G) {
+        o[1 + nq + i] = w.qvel[i];
+        o[1 + nq + nv + i] = w.qacc[i];
+        o[1 + nq + 2 * nv + i] = w.warm[i];
+      }
+      for (int i = g.gl; i < nu; i += G) o[1 + nq + 3 * nv + i] = w.ctrl[i];
+    }
+    g.sync();
+  }
+  if (g.gl == 0) a.cost[a.mode == 0 ? b : b * a.NA + ai] = cost;
+}
+
+int launch_rollout(tokp_traj* tr, int mode, const double* d_Uin, const double* d_alphas, int nalpha) {
+  const DM& dm = tr->dm;
+  RollArgs a;
+  a.snap = tr->snap; a.X = tr->X; a.U = tr->U; a.resid = tr->resid; a.U_in = d_Uin; a.K = tr->K; a.k = tr->k;
+  a.target = tr->target; a.cand = tr->cand; a.cost = mode == 0 ? tr->cost : tr->cand_cost; a.alphas = d_alphas;
+  a.B = tr->B; a.T = tr->T; a.SD = tr->SD; a.NA = mode == 0 ? 1 : nalpha; a.mode = mode;
+  a.iterations = dm.iterations; a.tolerance = dm.tolerance;
+  a.task = tr->task;
+  if (mode == 1) a.NA = tokp_traj::NA;  // buffer stride; unused alpha slots are skipped by the grid size
+  int G = tr->G;
+  int wsd = tk::ws_doubles(dm);
+  int warps = 1;
+  size_t smem = (size_t)warps * wsd * 8;
+  if (smem > 227 * 1024) { set_error("model too large for the shared-memory workspace"); return TOKP_ERR_UNSUPPORTED; }
+  int nworlds = mode == 0 ? tr->B : tr->B * tokp_traj::NA;
+  int blocks = (nworlds + warps - 1) / warps;
+#define LAUNCH(GG)                                                                                           \
+  TOKP_CUDA(cudaFuncSetAttribute(k_rollout<GG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));    \
+  k_rollout<GG><<<blocks, warps * 32, smem, tr->stream>>>(dm, a, wsd);
+  if (G == 8) { LAUNCH(8) } else if (G == 16) { LAUNCH(16) } else { LAUNCH(32) }
+#undef LAUNCH
+  g_launches++;
+  TOKP_CUDA(cudaGetLastError());
+  return TOKP_OK;
+}
+
+}  // namespace tokp

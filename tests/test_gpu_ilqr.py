@@ -1,0 +1,149 @@
+"""GPU parity tests for key-points, interpolation, cost derivatives, the Riccati backward pass, the alpha-batched
+forward pass, acceptance (with the reference's index quirks) and the full iLQR::Optimise loop."""
+import numpy as np
+import pytest
+
+from helpers import make, oracle_model, oracle_task, perturbed_start, random_controls, rel_fro
+from oracle import oracle
+from trajoptkp_b200 import capi
+
+pytestmark = pytest.mark.gpu
+
+METHODS = [(capi.KP_SET_INTERVAL, 5, 20), (capi.KP_ADAPTIVE_JERK, 2, 10), (capi.KP_ADAPTIVE_ACCEL, 2, 10),
+           (capi.KP_VELOCITY_CHANGE, 1, 20), (capi.KP_VELOCITY_CHANGE, 3, 8)]
+
+
+def _setup(name, T, kp=None, min_N=None, max_N=None, seed=7, B=1):
+    tc = make(name, kp_method=kp, min_N=min_N, max_N=max_N)
+    snap0 = perturbed_start(tc, seed)
+    U = random_controls(tc, T, seed + 1)
+    tr = capi.Traj(tc, T, B)
+    return tc, snap0, U, tr
+
+
+@pytest.mark.parametrize("name", ["acrobot", "walker_run"])
+@pytest.mark.parametrize("method,min_N,max_N", METHODS)
+def test_keypoints_bit_exact(built, name, method, min_N, max_N):
+    T = 50
+    tc, snap0, U, tr = _setup(name, T, method, min_N, max_N)
+    if method in (capi.KP_ADAPTIVE_JERK, capi.KP_ADAPTIVE_ACCEL):
+        # thresholds that actually trigger on this trajectory
+        thr = np.full(tc.n, 5.0 if method == capi.KP_ADAPTIVE_JERK else 0.002)
+        tc.jerk_thr = thr
+        tr.set_keypoint_method(method, min_N, max_N, jerk_thr=thr)
+    if method == capi.KP_VELOCITY_CHANGE:
+        thr = np.full(tc.n, 0.5)
+        tc.vel_thr = thr
+        tr.set_keypoint_method(method, min_N, max_N, vel_thr=thr)
+    tr.rollout(snap0, U)
+    rows, pct = tr.keypoints()
+    X = tr.get(0, "X_old").reshape(T + 1, -1)
+    ref_rows = oracle.keypoints(method, X, tc.n, T, tc.timestep, min_N, max_N, tc.jerk_thr, tc.vel_thr)
+    assert rows[0] == ref_rows                                   # index lists, order and duplicates included
+    assert (pct[0] == oracle.percentages(ref_rows, tc.n)).all()  # bit-exact percentages
+    # structural invariants of the reference's own tests (src/tests/Keypoints_Test.cpp:10-33,81-114)
+    assert rows[0][0] == list(range(tc.n))
+    assert sorted(set(rows[0][T - 1])) == list(range(tc.n))
+    if method != capi.KP_SET_INTERVAL:
+        for j in range(tc.n):
+            ts = [t for t in range(T) if j in rows[0][t]]
+            assert max(b - a for a, b in zip(ts, ts[1:])) <= max_N
+
+
+@pytest.mark.parametrize("name", ["acrobot", "walker_run"])
+def test_interpolation_bit_exact(built, name):
+    T = 40
+    tc, snap0, U, tr = _setup(name, T, capi.KP_SET_INTERVAL, 3, 3)
+    tr.rollout(snap0, U)
+    rows, _ = tr.keypoints()
+    tr.dynamics_derivs()
+    nx, m = tr.nx, tr.m
+    A0 = tr.get(0, "A").copy()
+    B0 = tr.get(0, "B").copy()
+    tr.interpolate()
+    A1 = tr.get(0, "A").reshape(T, nx, nx)
+    B1 = tr.get(0, "B")
+    oracle.interpolate(rows[0], tc.n, m, A0, B0)
+    assert (A1.ravel() == A0).all()
+    assert (B1 == B0).all()
+    # Keypoints_Test.cpp:272-289: A[1] == A[0] + (A[3]-A[0])/3 exactly (per element, same operation order)
+    add = (A1[3] - A1[0]) / 3
+    assert (A1[1] == A1[0] + 1.0 * add).all()
+
+
+def test_iterative_error_keypoints(built):
+    T = 33
+    tc, snap0, U, tr = _setup("walker_run", T, capi.KP_ITERATIVE_ERROR, 2, 10)
+    tc.iter_thr = 5e-3
+    tr.set_keypoint_method(capi.KP_ITERATIVE_ERROR, 2, 10, iter_thr=5e-3)
+    tr.rollout(snap0, U)
+    rows, pct = tr.keypoints()
+    ref = oracle.ILQR(oracle_model(tc), oracle_task(tc), T, threads=1)
+    ref.rollout(snap0, U)
+    ref.generate_keypoints()
+    assert rows[0] == ref.keypoints()
+    assert 0 < sum(len(r) for r in rows[0]) < T * tc.n
+
+
+@pytest.mark.parametrize("name", ["acrobot", "walker_run"])
+def test_cost_derivs_backward_forward(built, name):
+    T = 40
+    tc, snap0, U, tr = _setup(name, T, capi.KP_SET_INTERVAL, 2, 2)
+    ref = oracle.ILQR(oracle_model(tc), oracle_task(tc), T, threads=4)
+    c_ref = ref.rollout(snap0, U)
+    ref.generate_derivatives()
+    c_dev = tr.rollout(snap0, U)[0]
+    tr.generate_derivatives()
+    tol = 1e-4 if name == "walker_run" else 1e-7
+    for nm in ("r_x", "r_u", "l_x", "l_xx", "l_u", "l_uu"):
+        a, b = tr.get(0, nm), ref.get(nm)
+        # l_*[T] is never written by the reference; compare t < T
+        k = a.size // (T + 1)
+        assert rel_fro(a[:T * k], b[:T * k]) < 1e-9, nm
+    assert rel_fro(tr.get(0, "A"), ref.get("A")) < tol
+    assert rel_fro(tr.get(0, "B"), ref.get("B")) < tol
+    # backward pass from identical inputs: feed the oracle's derivatives to the device
+    for nm in ("A", "B", "l_x", "l_xx", "l_u", "l_uu"):
+        tr.set(0, nm, ref.get(nm))
+    ref.set_lambda(0.1)
+    ok_ref = ref.backward()
+    ok, dJ = tr.backward_pass(0.1)
+    assert bool(ok[0]) == ok_ref
+    assert rel_fro(tr.get(0, "K"), ref.get("K")) < 1e-8
+    assert rel_fro(tr.get(0, "k"), ref.get("k")) < 1e-8
+    assert abs(dJ[0] - ref.scalars()["delta_J"]) <= 1e-8 * abs(ref.scalars()["delta_J"])
+    # forward pass with identical gains
+    tr.set(0, "K", ref.get("K"))
+    tr.set(0, "k", ref.get("k"))
+    alphas = [(i / 6.0) ** 2 for i in range(1, 7)]
+    costs = tr.forward_pass(alphas)[0]
+    ref_costs = np.array([ref.forward(i, a) for i, a in enumerate(alphas)])
+    assert np.allclose(costs, ref_costs, rtol=1e-7, atol=1e-9), (costs, ref_costs)
+    # acceptance: SaveBestRollout + UpdateNominal incl. the one-step shift and the zeroed first control
+    best = int(np.argmin(ref_costs))
+    ref.save_best(best, float(ref_costs[best]))
+    tr.accept(0, best)
+    for nm in ("X_old", "U_old", "resid"):
+        a, b = tr.get(0, nm), ref.get(nm)
+        assert np.allclose(a, b, rtol=1e-7, atol=1e-9), nm
+    assert (tr.get(0, "U_old").reshape(T, -1)[0] == 0).all()          # quirk C.1-2
+    sT = tr.get_snapshot(0, T)                                         # saved[T] <- never-written rollout slot:
+    assert (sT[:tc.model.S - tc.model.nu] == 0).all()                  # state zeroed, its ctrl keeps the old value
+
+
+@pytest.mark.parametrize("name,T,max_it", [("acrobot", 100, 6), ("walker_run", 40, 3)])
+def test_optimise_final_cost(built, name, T, max_it):
+    tc = make(name, kp_method=capi.KP_SET_INTERVAL, min_N=1)
+    snap0 = perturbed_start(tc, 21)
+    U = np.zeros((T, tc.m))
+    ref = oracle.ILQR(oracle_model(tc), oracle_task(tc), T, threads=4)
+    ref.set_lambda(0.1)
+    U_ref = ref.optimise(snap0, U, max_it, 1)
+    sc = ref.scalars()
+    tr = capi.Traj(tc, T, 2)
+    U_dev, stats = tr.optimise(snap0, U, max_it, 1, lam=0.1)
+    for b in range(2):
+        assert abs(stats[b, 0] - sc["initial_cost"]) <= 1e-9 * abs(sc["initial_cost"])
+        assert abs(stats[b, 1] - sc["new_cost"]) <= 0.01 * abs(sc["new_cost"]), (stats[b], sc)   # final cost within 1 %
+        assert int(stats[b, 2]) == int(sc["num_iterations"])
+    assert stats[0, 1] < stats[0, 0]

@@ -1,0 +1,129 @@
+"""GPU parity tests: every stage of the CUDA path (through the C ABI) against the CPU oracle on the same seeded
+inputs.  Tolerances (BASELINE.json north_star): key-point indices bit-exact; per-step states 1e-9 relative on
+smooth models; A/B 1e-4 relative Frobenius on contact-rich tasks; final cost within 1 %."""
+import numpy as np
+import pytest
+
+from helpers import make, oracle_model, oracle_task, perturbed_start, random_controls, rel_fro
+from oracle import oracle
+from trajoptkp_b200 import capi
+
+pytestmark = pytest.mark.gpu
+
+STATE_RTOL = 1e-9
+AB_RTOL_SMOOTH = 1e-7   # acrobot: FD of a smooth map, both sides fp64
+AB_RTOL_CONTACT = 1e-4  # walker (contacts + limits)
+
+
+def _cfg(name):
+    return {"acrobot": dict(T=60, ab_tol=AB_RTOL_SMOOTH), "walker_run": dict(T=40, ab_tol=AB_RTOL_CONTACT)}[name]
+
+
+@pytest.mark.parametrize("name", ["acrobot", "walker_run"])
+def test_step_worlds_match_oracle(built, name):
+    tc = make(name)
+    m = tc.model
+    om = oracle_model(tc)
+    rng = np.random.default_rng(1)
+    count, nsteps = 24, 15
+    snaps = np.stack([perturbed_start(tc, 100 + i, dq=0.2, dv=0.5) for i in range(count)])
+    snaps[:, m.S - m.nu:] = rng.uniform(-1, 1, (count, m.nu))
+    out = np.zeros_like(snaps)
+    st = np.zeros(count, dtype=np.int32)
+    capi.check(capi.lib().tokp_step_worlds(m.h, capi._d(snaps), capi._d(out), count, nsteps, -1, 0.0, capi._i(st)))
+    assert not st.any()
+    d = oracle.Data(om)
+    for i in range(count):
+        d.load(snaps[i])
+        for _ in range(nsteps):
+            d.step()
+        ref = d.save()
+        err = np.abs(ref - out[i]).max() / max(1.0, np.abs(ref).max())
+        assert err < STATE_RTOL, (i, err)
+
+
+@pytest.mark.parametrize("name", ["acrobot", "walker_run"])
+def test_rollout_and_fd_jacobians(built, name):
+    cfg = _cfg(name)
+    tc = make(name, kp_method=capi.KP_SET_INTERVAL, min_N=1)
+    T = cfg["T"]
+    om = oracle_model(tc)
+    ot = oracle_task(tc)
+    snap0 = perturbed_start(tc, 7)
+    U = random_controls(tc, T, 3)
+    # oracle
+    ref = oracle.ILQR(om, ot, T, threads=4)
+    c_ref = ref.rollout(snap0, U)
+    ref.generate_keypoints()
+    ref.dynamics_derivs()
+    # device
+    tr = capi.Traj(tc, T, 1)
+    c_dev = tr.rollout(snap0, U)[0]
+    assert abs(c_dev - c_ref) <= 1e-9 * max(1.0, abs(c_ref))
+    X_ref = ref.get("X_old")
+    X_dev = tr.get(0, "X_old")
+    assert np.abs(X_ref - X_dev).max() / max(1.0, np.abs(X_ref).max()) < STATE_RTOL
+    assert np.allclose(ref.get("resid"), tr.get(0, "resid"), rtol=0, atol=1e-9)
+    for t in (0, 1, T // 2, T):
+        s_ref = ref.get("saved").reshape(T + 1, -1)[t]
+        assert np.abs(s_ref - tr.get_snapshot(0, t)).max() / max(1.0, np.abs(s_ref).max()) < STATE_RTOL
+    rows, pct = tr.keypoints()
+    assert rows[0] == ref.keypoints()
+    tr.dynamics_derivs()
+    nx = tr.nx
+    A_ref = ref.get("A").reshape(T, nx, nx)
+    B_ref = ref.get("B").reshape(T, tr.m, nx)
+    A_dev = tr.get(0, "A").reshape(T, nx, nx)
+    B_dev = tr.get(0, "B").reshape(T, tr.m, nx)
+    worst = 0.0
+    for t in range(T):
+        worst = max(worst, rel_fro(A_dev[t], A_ref[t]), rel_fro(B_dev[t], B_ref[t]))
+    assert worst < cfg["ab_tol"], worst
+    worlds, jac_x1e6, _, _ = tr.counters()
+    assert worlds == T * (1 + 2 * tr.m + 4 * tr.n)
+    assert jac_x1e6 == T * 1000000
+
+
+@pytest.mark.parametrize("name", ["acrobot", "walker_run"])
+def test_derivs_cols_dropin(built, name):
+    """tokp_dynamics_derivs_cols == Differentiator::DynamicsDerivatives for a column subset; other columns untouched."""
+    tc = make(name)
+    T = 12
+    om, ot = oracle_model(tc), oracle_task(tc)
+    snap0 = perturbed_start(tc, 11)
+    U = random_controls(tc, T, 5)
+    tr = capi.Traj(tc, T, 1)
+    tr.rollout(snap0, U)
+    cols = [0, tc.n - 1]
+    nx = tr.nx
+    for central in (True, False):
+        A = np.full((nx, nx), 7.0, order="F")
+        Bm = np.full((nx, tr.m), 7.0, order="F")
+        tr.dynamics_derivs_cols(0, 5, cols, central=central, A=A, B=Bm)
+        A_ref, B_ref = oracle.dynamics_derivs(om, ot, tr.get_snapshot(0, 5), cols, central=central)
+        for c in cols:
+            assert rel_fro(A[:, c], A_ref[:, c]) < _cfg(name)["ab_tol"]
+            assert rel_fro(A[:, c + tc.n], A_ref[:, c + tc.n]) < _cfg(name)["ab_tol"]
+            if c < tc.m:
+                assert rel_fro(Bm[:, c], B_ref[:, c]) < _cfg(name)["ab_tol"]
+        untouched = [c for c in range(nx) if c not in cols and c - tc.n not in cols]
+        assert (A[:, untouched] == 7.0).all()
+
+
+def test_control_clamp_one_sided(built):
+    """A control sitting on its limit gets a one-sided difference (Differentiator.cpp:98-143)."""
+    tc = make("walker_run")
+    T = 6
+    om, ot = oracle_model(tc), oracle_task(tc)
+    snap0 = perturbed_start(tc, 2)
+    U = np.zeros((T, tc.m))
+    U[:, 0] = 1.0     # at the upper limit: forward nudge infeasible
+    U[:, 1] = -1.0    # at the lower limit: backward nudge infeasible
+    tr = capi.Traj(tc, T, 1)
+    tr.rollout(snap0, U)
+    nx = tr.nx
+    for t in (2, 4):
+        A, Bm = tr.dynamics_derivs_cols(0, t, list(range(tc.n)))
+        A_ref, B_ref = oracle.dynamics_derivs(om, ot, tr.get_snapshot(0, t), list(range(tc.n)))
+        assert rel_fro(Bm, B_ref) < AB_RTOL_CONTACT
+        assert rel_fro(A, A_ref) < AB_RTOL_CONTACT

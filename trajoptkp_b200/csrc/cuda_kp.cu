@@ -21,7 +21,7 @@ __global__ void k_kp_set_interval(unsigned long long* mask, int B, int T, int n,
 }
 
 // one thread per (b, dof): serial scan over t.  mode 0: jerk profile, 1: acceleration profile, 2: velocity change
-__global__ void k_kp_scan(unsigned long long* mask, const double* __restrict__ X, int B, int T, int n, int mode, int min_N,
+__global__ void k_kp_scan(unsigned long long* mask, unsigned long long* last_row, const double* __restrict__ X, int B, int T, int n, int mode, int min_N,
                           int max_N, const double* __restrict__ thr, double dt) {
   int gid = blockIdx.x * blockDim.x + threadIdx.x;
   if (gid >= B * n) return;
@@ -73,7 +73,7 @@ __global__ void k_kp_scan(unsigned long long* mask, const double* __restrict__ X
         }
       }
       if (!hit && counter >= max_N) hit = true;
-      if (hit) { atomicOr(&mb[t], bit); last_val = 0.0; counter = 0; }
+      if (hit) { atomicOr(&mb[t], bit); last_val = 0.0; counter = 0; if (t == T - 1) atomicOr(&last_row[b], bit); }
     }
     atomicOr(&mb[T - 1], bit);
   }
@@ -246,7 +246,8 @@ int generate_keypoints(tokp_traj* tr) {
     cudaMemsetAsync(tr->kp_mask, 0, (size_t)B * T * 8, tr->stream);
     int mode = t.kp_method == TOKP_KP_ADAPTIVE_JERK ? 0 : (t.kp_method == TOKP_KP_ADAPTIVE_ACCEL ? 1 : 2);
     const double* thr = mode == 2 ? t.vel_thr : t.jerk_thr;
-    k_kp_scan<<<(B * n + 63) / 64, 64, 0, tr->stream>>>(tr->kp_mask, tr->X, B, T, n, mode, t.min_N, t.max_N, thr, tr->dm.timestep);
+    cudaMemsetAsync(tr->kp_last, 0, (size_t)B * 8, tr->stream);
+    k_kp_scan<<<(B * n + 63) / 64, 64, 0, tr->stream>>>(tr->kp_mask, tr->kp_last, tr->X, B, T, n, mode, t.min_N, t.max_N, thr, tr->dm.timestep);
     g_launches++;
     if (mode == 2) flags = 1;
   }
@@ -277,6 +278,8 @@ int read_keypoints(tokp_traj* tr, int* counts, int* indices, double* pct) {
   int B = tr->B, T = tr->T, n = tr->n;
   std::vector<unsigned long long> hm((size_t)B * T);
   std::vector<int> hf(B);
+  std::vector<unsigned long long> hl(B);
+  TOKP_CUDA(cudaMemcpyAsync(hl.data(), tr->kp_last, B * 8, cudaMemcpyDeviceToHost, tr->stream));
   TOKP_CUDA(cudaMemcpyAsync(hm.data(), tr->kp_mask, hm.size() * 8, cudaMemcpyDeviceToHost, tr->stream));
   TOKP_CUDA(cudaMemcpyAsync(hf.data(), tr->kp_flags, B * 4, cudaMemcpyDeviceToHost, tr->stream));
   TOKP_CUDA(cudaStreamSynchronize(tr->stream));
@@ -284,6 +287,7 @@ int read_keypoints(tokp_traj* tr, int* counts, int* indices, double* pct) {
     std::vector<int> cnt(n, 0);
     for (int t = 0; t < T; t++) {
       unsigned long long mk = hm[(size_t)b * T + t];
+      if (t == T - 1 && (hf[b] & 1)) mk = hl[b];  // the scan's own hits; every dof is appended below
       int c = 0;
       int* row = indices ? indices + ((size_t)b * T + t) * 2 * n : nullptr;
       for (int j = 0; j < n; j++)

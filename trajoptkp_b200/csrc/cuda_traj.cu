@@ -64,6 +64,7 @@ extern "C" int tokp_traj_create(const tokp_model* m, const tokp_task_desc* td, i
   size_t o_candcost = p.take((size_t)B * NA, 8);
   size_t o_fd = p.take((size_t)B * T * tr->W * (dm.nq + dm.nv), 8);
   size_t o_mask = p.take((size_t)B * T, 8);
+  size_t o_last = p.take((size_t)B, 8);
   size_t o_flags = p.take((size_t)B, 4);
   size_t o_prev = p.take((size_t)B * T * n, 4);
   size_t o_next = p.take((size_t)B * T * n, 4);
@@ -85,7 +86,7 @@ extern "C" int tokp_traj_create(const tokp_model* m, const tokp_task_desc* td, i
   tr->lx = (double*)(base + o_lx); tr->lxx = (double*)(base + o_lxx); tr->lu = (double*)(base + o_lu); tr->luu = (double*)(base + o_luu);
   tr->K = (double*)(base + o_K); tr->k = (double*)(base + o_k); tr->target = (double*)(base + o_target);
   tr->cand = (double*)(base + o_cand); tr->cand_cost = (double*)(base + o_candcost); tr->fd_out = (double*)(base + o_fd);
-  tr->kp_mask = (unsigned long long*)(base + o_mask); tr->kp_flags = (int*)(base + o_flags);
+  tr->kp_mask = (unsigned long long*)(base + o_mask); tr->kp_last = (unsigned long long*)(base + o_last); tr->kp_flags = (int*)(base + o_flags);
   tr->kp_prev = (int*)(base + o_prev); tr->kp_next = (int*)(base + o_next); tr->status = (int*)(base + o_status);
   tr->cost = (double*)(base + o_cost); tr->deltaJ = (double*)(base + o_dJ); tr->lambda_d = (double*)(base + o_lam);
   tr->bp_ok = (int*)(base + o_ok);

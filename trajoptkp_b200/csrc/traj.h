@@ -58,6 +58,7 @@ struct tokp_traj {
   double *cand_cost;  // [B][NA]
   double *fd_out;     // [B][T][W][nq+nv]
   unsigned long long* kp_mask;  // [B][T]
+  unsigned long long* kp_last;  // [B] velocity_change: scan hits of row T-1 (before every dof is appended again)
   int* kp_flags;      // [B]: bit0 = velocity_change duplicate last row
   int *kp_prev, *kp_next;  // [B][T][n]
   int* status;        // [B][T][W]

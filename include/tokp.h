@@ -134,7 +134,8 @@ int tokp_forward_pass(tokp_traj* tr, const double* alphas, int nalpha, double* c
 /* Optimiser::SaveBestRollout + iLQR::UpdateNominal (Optimiser.cpp:440-468, iLQR.cpp:936-948) */
 int tokp_accept(tokp_traj* tr, int b, int alpha_idx);
 /* iLQR::Optimise (iLQR.cpp:269-410) for all B trajectories in lock-step: U_out[B][T][m], stats[B][8] =
- * {initial_cost, final_cost, iterations, lambda, avg_pct_derivs, derivs_ms, bp_ms, fp_ms} (device-timed totals) */
+ * {initial_cost, final_cost, iterations, lambda, avg_pct_derivs, derivs_ms, bp_ms, fp_ms} (device-timed totals).
+ * snapshot0 == U_init == NULL re-uses the device-resident inputs of the previous call; U_out / stats may be NULL. */
 int tokp_optimise(tokp_traj* tr, const double* snapshot0, const double* U_init, int max_iterations, int min_iterations,
                   const double* lambda_init, double* U_out, double* stats);
 
@@ -146,6 +147,11 @@ int tokp_traj_set(tokp_traj* tr, int b, const char* name, const double* in, int 
 int tokp_traj_counters(tokp_traj* tr, int64_t out[4]);
 /* CUDA-event time of the last derivative / backward / forward phase, ms (time_get_derivs_ms etc., iLQR.cpp:418-505) */
 int tokp_timers(tokp_traj* tr, double ms[3]);
+/* device time of the dominant kernel (k_fd_worlds, CUDA events on the launching stream):
+ * out = {last launch ms, sum over launches ms, number of launches} */
+int tokp_fd_kernel_ms(tokp_traj* tr, double out[3]);
+/* live roofline denominators: out = {FP64 FMA TFLOP/s, device copy GB/s (read+write)} */
+int tokp_measure_peaks(double out[2]);
 /* total number of kernels this library launched since load */
 int64_t tokp_launch_count(void);
 

@@ -92,6 +92,8 @@ def lib():
         L.tokp_traj_set.argtypes = [vp, C.c_int, C.c_char_p, _dp, C.c_int]
         L.tokp_traj_counters.argtypes = [vp, C.POINTER(C.c_int64)]
         L.tokp_timers.argtypes = [vp, _dp]
+        L.tokp_fd_kernel_ms.argtypes = [vp, _dp]
+        L.tokp_measure_peaks.argtypes = [_dp]
     _lib = L
     return L
 
@@ -261,6 +263,18 @@ class Traj:
     def accept(self, b, alpha_idx):
         check(lib().tokp_accept(self.h, b, alpha_idx))
 
+    def fd_kernel_ms(self):
+        t = np.zeros(3)
+        check(lib().tokp_fd_kernel_ms(self.h, _d(t)))
+        return t
+
+    def optimise_resident(self, max_it, min_it, lam=None, want_stats=True):
+        """tokp_optimise on the device-resident inputs of the previous call (no bulk host<->device copies)."""
+        lamv = None if lam is None else np.ascontiguousarray(np.broadcast_to(np.asarray(lam, dtype=np.float64), (self.B,)))
+        stats = np.zeros((self.B, 8)) if want_stats else None
+        check(lib().tokp_optimise(self.h, None, None, max_it, min_it, _d(lamv), None, _d(stats)))
+        return stats
+
     def optimise(self, snap0, U, max_it, min_it, lam=None):
         s = np.ascontiguousarray(np.broadcast_to(np.asarray(snap0, dtype=np.float64), (self.B, self.model.S)))
         U = np.ascontiguousarray(np.broadcast_to(np.asarray(U, dtype=np.float64), (self.B, self.T, self.m)))
@@ -292,3 +306,9 @@ class Traj:
         t = np.zeros(3)
         check(lib().tokp_timers(self.h, _d(t)))
         return t
+
+
+def measure_peaks():
+    out = np.zeros(2)
+    check(lib().tokp_measure_peaks(_d(out)))
+    return {"fp64_tflops": float(out[0]), "copy_gbs": float(out[1])}

@@ -353,6 +353,7 @@ int launch_fd(tokp_traj* tr, const unsigned long long* mask, const int* rows, in
 void pack_snapshot(const tokp_traj* tr, const double* s, double* d);
 int check_applied_zero(const tokp_traj* tr, const double* s);
 int read_keypoints(tokp_traj* tr, int* counts, int* indices, double* pct);
+int update_fd_counters(tokp_traj* tr);
 
 static int cost_derivs(tokp_traj* tr, int central, double eps) {
   int B = tr->B, T = tr->T;
@@ -373,6 +374,8 @@ static int generate_derivatives(tokp_traj* tr) {
   if (rc) return rc;
   if (tr->task.kp_method != TOKP_KP_ITERATIVE_ERROR) {
     rc = launch_fd(tr, tr->kp_mask, nullptr, tr->B * tr->T, 1, 1e-6);
+    if (rc) return rc;
+    rc = update_fd_counters(tr);
     if (rc) return rc;
   }
   rc = interpolate(tr);
@@ -420,20 +423,35 @@ struct Timer {
 
 using namespace tokp;
 
+// scatter the resident start snapshots into saved[b][0]
+__global__ void k_seed_snap0(double* __restrict__ snap, const double* __restrict__ snap0, int B, int T, int SD) {
+  int gid = blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= B * SD) return;
+  int b = gid / SD, i = gid - b * SD;
+  snap[(size_t)b * (T + 1) * SD + i] = snap0[gid];
+}
+
 extern "C" int tokp_rollout(tokp_traj* tr, const double* snapshot0, const double* U, double* cost) {
-  if (!tr || !snapshot0 || !U) { set_error("tokp_rollout: bad argument"); return TOKP_ERR_ARG; }
+  if (!tr || (!snapshot0) != (!U)) { set_error("tokp_rollout: bad argument"); return TOKP_ERR_ARG; }
   int B = tr->B, T = tr->T, m = tr->m;
-  std::vector<double> d((size_t)tr->SD);
-  for (int b = 0; b < B; b++) {
-    int rc = check_applied_zero(tr, snapshot0 + (size_t)b * tr->S);
-    if (rc) return rc;
-    pack_snapshot(tr, snapshot0 + (size_t)b * tr->S, d.data());
-    TOKP_CUDA(cudaMemcpyAsync(tr->snap + (size_t)b * (T + 1) * tr->SD, d.data(), tr->SD * 8, cudaMemcpyHostToDevice, tr->stream));
+  if (snapshot0) {
+    std::vector<double> d((size_t)B * tr->SD);
+    for (int b = 0; b < B; b++) {
+      int rc = check_applied_zero(tr, snapshot0 + (size_t)b * tr->S);
+      if (rc) return rc;
+      pack_snapshot(tr, snapshot0 + (size_t)b * tr->S, d.data() + (size_t)b * tr->SD);
+    }
+    TOKP_CUDA(cudaMemcpyAsync(tr->snap0_in, d.data(), d.size() * 8, cudaMemcpyHostToDevice, tr->stream));
+    TOKP_CUDA(cudaMemcpyAsync(tr->U0_in, U, (size_t)B * T * m * 8, cudaMemcpyHostToDevice, tr->stream));
     TOKP_CUDA(cudaStreamSynchronize(tr->stream));
+    tr->have_inputs = true;
+  } else if (!tr->have_inputs) {
+    set_error("tokp_rollout: no resident inputs (call once with host buffers first)");
+    return TOKP_ERR_STATE;
   }
-  double* d_U = tr->fd_out;  // staging (free outside the FD phase)
-  TOKP_CUDA(cudaMemcpyAsync(d_U, U, (size_t)B * T * m * 8, cudaMemcpyHostToDevice, tr->stream));
-  int rc = launch_rollout(tr, 0, d_U, nullptr, 1);
+  k_seed_snap0<<<(B * tr->SD + 127) / 128, 128, 0, tr->stream>>>(tr->snap, tr->snap0_in, B, T, tr->SD);
+  g_launches++;
+  int rc = launch_rollout(tr, 0, tr->U0_in, nullptr, 1);
   if (rc) return rc;
   std::vector<double> hc(B);
   TOKP_CUDA(cudaMemcpyAsync(hc.data(), tr->cost, B * 8, cudaMemcpyDeviceToHost, tr->stream));
@@ -513,7 +531,8 @@ extern "C" int tokp_accept(tokp_traj* tr, int b, int alpha_idx) {
 // iLQR::Optimise + iLQR::Iteration for B trajectories in lock-step (per-trajectory lambda / convergence state)
 extern "C" int tokp_optimise(tokp_traj* tr, const double* snapshot0, const double* U_init, int max_iterations,
                              int min_iterations, const double* lambda_init, double* U_out, double* stats) {
-  if (!tr || !snapshot0 || !U_init || max_iterations < 0) { set_error("tokp_optimise: bad argument"); return TOKP_ERR_ARG; }
+  // snapshot0 == U_init == NULL: re-use the device-resident inputs of the previous call (no bulk H2D)
+  if (!tr || (!snapshot0) != (!U_init) || max_iterations < 0) { set_error("tokp_optimise: bad argument"); return TOKP_ERR_ARG; }
   int B = tr->B, T = tr->T, m = tr->m, NA = tokp_traj::NA;
   const double max_lambda = 10.0, min_lambda = 0.0001, lambda_factor = 10.0, eps_converge = 0.02;
   std::vector<double> old_cost(B), new_cost(B), initial(B), lambda(B, 0.1), t_der(B, 0), t_bp(B, 0), t_fp(B, 0), pct_sum(B, 0);

@@ -1,6 +1,7 @@
 // Device model upload + batched plain stepping (tokp_step_worlds).
 // Replaces mj_makeData/mj_step usage of MuJoCoHelper (src/PhysicsSimulators/MuJoCoHelper.cpp:877-923)
 // for batches of independent worlds.
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 
@@ -19,6 +20,10 @@ void device_model_free(DeviceModel* dm) {
 }
 
 int lanes_for_model(const DM& dm) {
+  if (const char* e = getenv("TOKP_LANES")) {  // tuning override (8 / 16 / 32)
+    int v = atoi(e);
+    if (v == 8 || v == 16 || v == 32) return v;
+  }
   int k = dm.nv > dm.nbody ? dm.nv : dm.nbody;
   if (k <= 10) return 8;
   if (k <= 20) return 16;

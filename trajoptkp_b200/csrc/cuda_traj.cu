@@ -73,6 +73,8 @@ extern "C" int tokp_traj_create(const tokp_model* m, const tokp_task_desc* td, i
   size_t o_dJ = p.take((size_t)B, 8);
   size_t o_lam = p.take((size_t)B, 8);
   size_t o_ok = p.take((size_t)B, 4);
+  size_t o_s0 = p.take((size_t)B * tr->SD, 8);
+  size_t o_u0 = p.take((size_t)B * T * mm, 8);
   size_t o_tints = p.take((size_t)(2 * n + mm), 4);
   size_t o_treals = p.take((size_t)(2 * nr + 2 * n + 2 * mm), 8);
   cudaError_t e = cudaMalloc(&tr->arena, p.bytes);
@@ -90,6 +92,7 @@ extern "C" int tokp_traj_create(const tokp_model* m, const tokp_task_desc* td, i
   tr->kp_prev = (int*)(base + o_prev); tr->kp_next = (int*)(base + o_next); tr->status = (int*)(base + o_status);
   tr->cost = (double*)(base + o_cost); tr->deltaJ = (double*)(base + o_dJ); tr->lambda_d = (double*)(base + o_lam);
   tr->bp_ok = (int*)(base + o_ok);
+  tr->snap0_in = (double*)(base + o_s0); tr->U0_in = (double*)(base + o_u0);
   tr->task_ints = (int*)(base + o_tints); tr->task_reals = (double*)(base + o_treals);
   // task tables
   std::vector<int> ti;
@@ -118,6 +121,8 @@ extern "C" int tokp_traj_create(const tokp_model* m, const tokp_task_desc* td, i
   cudaStreamCreate(&tr->stream);
   cudaEventCreate(&tr->ev0);
   cudaEventCreate(&tr->ev1);
+  cudaEventCreate(&tr->ev2);
+  cudaEventCreate(&tr->ev3);
   e = cudaGetLastError();
   if (e != cudaSuccess) { set_error(std::string("traj init: ") + cudaGetErrorString(e)); tokp_traj_destroy(tr); return TOKP_ERR_CUDA; }
   *out = tr;
@@ -129,6 +134,8 @@ extern "C" void tokp_traj_destroy(tokp_traj* tr) {
   if (tr->stream) { cudaStreamSynchronize(tr->stream); cudaStreamDestroy(tr->stream); }
   if (tr->ev0) cudaEventDestroy(tr->ev0);
   if (tr->ev1) cudaEventDestroy(tr->ev1);
+  if (tr->ev2) cudaEventDestroy(tr->ev2);
+  if (tr->ev3) cudaEventDestroy(tr->ev3);
   if (tr->arena) cudaFree(tr->arena);
   delete tr;
 }
@@ -236,6 +243,19 @@ extern "C" int tokp_traj_set(tokp_traj* tr, int b, const char* name, const doubl
 extern "C" int tokp_traj_counters(tokp_traj* tr, int64_t out[4]) {
   if (!tr || !out) return TOKP_ERR_ARG;
   for (int i = 0; i < 4; i++) out[i] = tr->counters[i];
+  return TOKP_OK;
+}
+
+extern "C" int tokp_fd_kernel_ms(tokp_traj* tr, double out[3]) {
+  if (!tr || !out) return TOKP_ERR_ARG;
+  if (tr->fd_timed) {
+    cudaEventSynchronize(tr->ev3);
+    float ms = 0;
+    cudaEventElapsedTime(&ms, tr->ev2, tr->ev3);
+    tr->fd_kernel_ms = ms; tr->fd_kernel_ms_sum += ms; tr->fd_kernel_launches++;
+    tr->fd_timed = false;
+  }
+  out[0] = tr->fd_kernel_ms; out[1] = tr->fd_kernel_ms_sum; out[2] = (double)tr->fd_kernel_launches;
   return TOKP_OK;
 }
 

@@ -49,7 +49,7 @@ struct tokp_traj {
   int B = 0, T = 0, S = 0 /* host snapshot size */, SD = 0 /* device snapshot size */, W = 0 /* worlds per key-point */;
   int n = 0, m = 0, nx = 0, nr = 0, G = 8;
   cudaStream_t stream = nullptr;
-  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr, ev3 = nullptr;
   void* arena = nullptr;
   size_t arena_bytes = 0;
   // device arrays (all inside arena)
@@ -63,11 +63,14 @@ struct tokp_traj {
   int *kp_prev, *kp_next;  // [B][T][n]
   int* status;        // [B][T][W]
   double *cost, *deltaJ, *lambda_d;  // [B]
+  double *snap0_in, *U0_in;          // resident copies of the last host inputs of tokp_optimise ([B][SD], [B][T][m])
   int* bp_ok;         // [B]
   int* task_ints;     // qpos_adr | dof_adr | ctrl_adr
   double* task_reals;
   static const int NA = 6;
-  bool have_rollout = false;
+  bool have_rollout = false, have_inputs = false, fd_timed = false;
+  double fd_kernel_ms = 0, fd_kernel_ms_sum = 0;
+  int64_t fd_kernel_launches = 0;
   double timers[3] = {0, 0, 0};
   int64_t counters[4] = {0, 0, 0, 0};
   std::vector<double> h_stage;  // host staging

@@ -1,0 +1,79 @@
+"""CPU tests of the multi-GPU sweep's host logic: trial j -> rank j mod G, no data-path collective,
+one all_gather of fixed-size records.  The N>1 path runs here as world_size-2 gloo processes."""
+import os
+import socket
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from trajoptkp_b200 import sweep
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.mark.parametrize("n,world", [(100, 1), (100, 2), (100, 8), (7, 4), (3, 8), (0, 2)])
+def test_shard_trials_partitions_exactly(n, world):
+    seen = []
+    for r in range(world):
+        mine = sweep.shard_trials(n, r, world)
+        assert all(j % world == r for j in mine)
+        assert len(mine) <= sweep.pad_count(n, world)
+        seen += mine
+    assert sorted(seen) == list(range(n))
+    with pytest.raises(ValueError):
+        sweep.shard_trials(n, world, world)
+
+
+def test_pack_and_single_process_gather():
+    n = 5
+    mine = sweep.shard_trials(n, 0, 1)
+    recs = [np.arange(sweep.RECORD_SIZE - 1) + 10 * j for j in mine]
+    table = sweep.gather_records(sweep.pack_records(mine, recs, n, 1), n)
+    assert table.shape == (n, sweep.RECORD_SIZE)
+    assert np.array_equal(table[:, -1], np.arange(n))
+    assert np.array_equal(table[3, :-1], recs[3])
+    txt = sweep.summary_csv(table)
+    assert txt.splitlines()[0] == sweep.SUMMARY_HEADER and len(txt.splitlines()) == n + 1
+
+
+def test_gather_detects_missing_trials():
+    local = sweep.pack_records([0, 2], [np.zeros(sweep.RECORD_SIZE - 1)] * 2, 3, 1)
+    with pytest.raises(RuntimeError):
+        sweep.gather_records(local, 3)
+
+
+WORKER = r'''
+import os, sys
+sys.path.insert(0, %(root)r)
+import numpy as np, torch.distributed as dist
+from trajoptkp_b200 import sweep
+dist.init_process_group("gloo")
+rank, world = dist.get_rank(), dist.get_world_size()
+n = 7
+mine = sweep.shard_trials(n, rank, world)
+recs = [np.full(sweep.RECORD_SIZE - 1, 100.0 * rank + j) for j in mine]
+table = sweep.gather_records(sweep.pack_records(mine, recs, n, world), n, dist=dist)
+assert table.shape == (n, sweep.RECORD_SIZE)
+for j in range(n):
+    assert table[j, -1] == j and table[j, 0] == 100.0 * (j %% world) + j, (j, table[j])
+dist.barrier()
+dist.destroy_process_group()
+sys.stdout.write("rank%d-ok\n" % rank)
+'''
+
+
+def test_gather_world_size_2_gloo(tmp_path):
+    script = tmp_path / "worker.py"
+    script.write_text(WORKER % {"root": ROOT})
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+           "--master-port", str(port), str(script)]
+    env = dict(os.environ, OMP_NUM_THREADS="1")
+    p = subprocess.run(cmd, capture_output=True, text=True, timeout=240, env=env)
+    assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-2000:]
+    assert "rank0-ok" in p.stdout and "rank1-ok" in p.stdout

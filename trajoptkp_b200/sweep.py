@@ -1,0 +1,110 @@
+"""Multi-GPU trial sweep: host-side logic for SURVEY 8(e).
+
+Replaces the serial `for i in 0..99` of GenTestingData::GenDataOpenloopOptimisation
+(src/GenTestingData.cpp:136-259) and TestingMPC (:328-420): trials are independent, so trial j goes to rank
+j mod G (one process per GPU), each rank runs complete Optimise calls on its own device batch, and ONE
+all_gather of fixed-size result records ends the sweep.  There is no data-path collective and a single
+trajectory never leaves its GPU.
+
+Record columns follow the reference's summary.csv (GenTestingData.cpp:236-247) plus two device figures:
+  cost_reduction, opt_time_ms, iterations, avg_dofs, avg_pct_derivs, t_derivs_ms, t_bp_ms, t_fp_ms,
+  jacobians, trial_index
+"""
+import numpy as np
+
+RECORD_FIELDS = ("cost_reduction", "opt_time_ms", "iterations", "avg_dofs", "avg_pct_derivs", "t_derivs_ms",
+                 "t_bp_ms", "t_fp_ms", "jacobians", "trial_index")
+RECORD_SIZE = len(RECORD_FIELDS)
+SUMMARY_HEADER = ("Cost reduction,Optimisation time (ms),Number iterations,Average num dofs,Average percent derivs,"
+                  "Average time derivs (ms),Average time BP (ms),Average time FP (ms)")
+
+
+def shard_trials(num_trials, rank, world):
+    """Trial indices owned by `rank`: j with j mod world == rank (SURVEY 8(e) partitioning)."""
+    if not (0 <= rank < world):
+        raise ValueError("rank %d outside world %d" % (rank, world))
+    return list(range(rank, num_trials, world))
+
+
+def pad_count(num_trials, world):
+    """Records per rank after padding so that all_gather sees equal shapes."""
+    return (num_trials + world - 1) // world
+
+
+def pack_records(trial_indices, records, num_trials, world):
+    """[pad_count, RECORD_SIZE] array; unused rows carry trial_index = -1."""
+    out = np.zeros((pad_count(num_trials, world), RECORD_SIZE))
+    out[:, -1] = -1.0
+    for r, (j, rec) in enumerate(zip(trial_indices, records)):
+        rec = np.asarray(rec, dtype=np.float64)
+        assert rec.shape == (RECORD_SIZE - 1,), rec.shape
+        out[r, :-1] = rec
+        out[r, -1] = j
+    return out
+
+
+def gather_records(local, num_trials, dist=None, device=None):
+    """The sweep's only collective: all_gather of each rank's packed records, re-ordered by trial index.
+    `dist` is torch.distributed (initialised: NCCL over NVLink on the GPU box, gloo in the CPU tests) or None for a
+    single process."""
+    if dist is None or not dist.is_initialized() or dist.get_world_size() == 1:
+        allr = local[None]
+    else:
+        import torch
+        t = torch.as_tensor(local, dtype=torch.float64, device=device)
+        bufs = [torch.empty_like(t) for _ in range(dist.get_world_size())]
+        dist.all_gather(bufs, t)
+        allr = torch.stack(bufs).cpu().numpy()
+    flat = allr.reshape(-1, RECORD_SIZE)
+    flat = flat[flat[:, -1] >= 0]
+    order = np.argsort(flat[:, -1], kind="stable")
+    flat = flat[order]
+    if len(flat) != num_trials or not np.array_equal(flat[:, -1], np.arange(num_trials)):
+        raise RuntimeError("sweep gather: expected %d trial records, got indices %s" % (num_trials, flat[:, -1]))
+    return flat
+
+
+def summary_csv(records):
+    """The reference's summary.csv text (GenTestingData.cpp:236-250) from gathered records."""
+    lines = [SUMMARY_HEADER]
+    for r in records:
+        lines.append("%g,%g,%d,%g,%g,%g,%g,%g" % (r[0], r[1], int(r[2]), r[3], r[4], r[5], r[6], r[7]))
+    return "\n".join(lines) + "\n"
+
+
+def run_openloop_sweep(tc, horizon, num_trials=100, rank=0, world=1, dist=None, device=None, max_iter=10, min_iter=3,
+                       lam=0.01, init_controls=None, batch=None):
+    """GenDataOpenloopOptimisation on the device: this rank's trials as ONE tokp_traj batch (all trials of the rank
+    advance in lock-step through tokp_optimise), then the gather.  Returns the [num_trials, RECORD_SIZE] table."""
+    import time
+
+    from . import capi
+    mine = shard_trials(num_trials, rank, world)
+    B = len(mine)
+    recs = []
+    if B:
+        snaps = np.zeros((B, tc.model.S))
+        targets = np.zeros((B, tc.nr))
+        for r, j in enumerate(mine):
+            start, tg = tc.load_trial(j % tc.num_trials())
+            snaps[r] = tc.start_snapshot(start_pos=start)
+            targets[r] = tg
+        # GenTestingData.cpp:189: one plant step before the optimisation starts
+        out = np.zeros_like(snaps)
+        st = np.zeros(B, dtype=np.int32)
+        capi.check(capi.lib().tokp_step_worlds(tc.model.h, capi._d(snaps), capi._d(out), B, 1, -1, 0.0, capi._i(st)))
+        snaps = out
+        U = np.zeros((B, horizon, tc.m)) if init_controls is None else init_controls(tc, mine, horizon)
+        tr = capi.Traj(tc, horizon, B)
+        for r in range(B):
+            tr.set_targets(r, targets[r])
+        t0 = time.perf_counter()
+        _, stats = tr.optimise(snaps, U, max_iter, min_iter, lam=lam)
+        wall_ms = 1e3 * (time.perf_counter() - t0)
+        jac = tr.counters()[1] / 1e6
+        for r in range(B):
+            ini, fin, its = stats[r, 0], stats[r, 1], stats[r, 2]
+            recs.append([1.0 - fin / ini if ini != 0 else 0.0, wall_ms / B, its, float(tc.n), stats[r, 4], stats[r, 5],
+                         stats[r, 6], stats[r, 7], jac / B])
+    local = pack_records(mine, recs, num_trials, world)
+    return gather_records(local, num_trials, dist=dist, device=device)

@@ -88,6 +88,10 @@ class TaskConfig:
         return d
 
     # ---- TestTasks fixtures --------------------------------------------------------------------
+    def num_trials(self):
+        path = os.path.join(ASSETS, "test_tasks", self.name + ".csv")
+        return sum(1 for l in open(path) if l.strip() and not l.startswith("#"))
+
     def load_trial(self, i):
         """Row i of TestTasks/<task>: (start joint positions, residual targets[num_resid])."""
         path = os.path.join(ASSETS, "test_tasks", self.name + ".csv")

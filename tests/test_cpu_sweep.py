@@ -60,7 +60,7 @@ for j in range(n):
     assert table[j, -1] == j and table[j, 0] == 100.0 * (j %% world) + j, (j, table[j])
 dist.barrier()
 dist.destroy_process_group()
-sys.stdout.write("rank%d-ok\n" % rank)
+sys.stdout.write("rank%%d-ok\n" %% rank)
 '''
 
 

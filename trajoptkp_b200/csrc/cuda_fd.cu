@@ -32,6 +32,7 @@ struct FdArgs {
   double eps;
   int iterations;
   double tolerance;
+  int ecap, pass;                   // constraint-row capacity of this pass; pass 1 redoes overflowed worlds only
 };
 
 template <int G>
@@ -49,6 +50,7 @@ __global__ void k_fd_worlds(DM dm, FdArgs a, int wsd) {
   int b = row / a.T, t = row - b * a.T;
   unsigned long long mask = a.mask[row];
   int* st_out = a.status + (size_t)row * a.W + slot;
+  if (a.pass == 1 && !(*st_out & tk::ST_OVERFLOW)) return;
   if (mask == 0ull) { if (g.gl == 0) *st_out = 0; return; }
   // decode
   int kind = 0, col = 0, sgn = 0;
@@ -74,7 +76,7 @@ __global__ void k_fd_worlds(DM dm, FdArgs a, int wsd) {
     return;
   }
   tk::WS w;
-  tk::ws_init(w, smem + (size_t)slot_s * wsd, dm);
+  tk::ws_init(w, smem + (size_t)slot_s * wsd, dm, a.ecap);
   double time = s[0];
   for (int i = g.gl; i < nq; i += G) w.qpos[i] = s[1 + i];
   for (int i = g.gl; i < nv; i += G) {
@@ -180,35 +182,35 @@ int launch_fd(tokp_traj* tr, const unsigned long long* mask, const int* rows, in
   a.ctrl_limits = tr->task.ctrl_limits;
   a.central = central; a.eps = eps;
   a.iterations = 5; a.tolerance = 0.0;  // MuJoCoHelper::InitModelForFiniteDifferencing (MuJoCoHelper.cpp:925-931)
-  int G = tr->G, gpw = 32 / G;
-  int wsd = tk::ws_doubles(dm);
-  int warps = 4;
-  if (const char* e = getenv("TOKP_FD_WARPS")) warps = atoi(e) > 0 ? atoi(e) : warps;
-  while (warps > 1 && (size_t)warps * gpw * wsd * 8 > 110 * 1024) warps >>= 1;
-  size_t smem = (size_t)warps * gpw * wsd * 8;
-  if (smem > 227 * 1024) { set_error("model too large for the shared-memory workspace"); return TOKP_ERR_UNSUPPORTED; }
+  int G = tr->G;
   long long worlds = (long long)nrows * tr->W;
-  int wpb = warps * gpw;
-  int blocks = (int)((worlds + wpb - 1) / wpb);
-  if (blocks < 1) return TOKP_OK;
-#define LAUNCH(GG)                                                                                             \
-  TOKP_CUDA(cudaFuncSetAttribute(k_fd_worlds<GG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));    \
-  k_fd_worlds<GG><<<blocks, warps * 32, smem, tr->stream>>>(dm, a, wsd);
+  if (worlds < 1) return TOKP_OK;
   if (tr->fd_timed) {  // fold the previous launch's duration into the running sum before reusing the events
     double tmp[3];
     tokp_fd_kernel_ms(tr, tmp);
   }
   cudaEventRecord(tr->ev2, tr->stream);
-  if (G == 8) { LAUNCH(8) } else if (G == 16) { LAUNCH(16) } else { LAUNCH(32) }
+  for (int pass = 0; pass < (needs_redo_pass(dm) ? 2 : 1); pass++) {
+    LaunchPlan lp;
+    int rc = plan_launch(dm, G, pass, &lp);
+    if (rc) return rc;
+    a.ecap = lp.ecap; a.pass = pass;
+    int blocks = (int)((worlds + lp.worlds_per_block - 1) / lp.worlds_per_block);
+#define LAUNCH(GG)                                                                                               \
+  TOKP_CUDA(cudaFuncSetAttribute(k_fd_worlds<GG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lp.smem));   \
+  k_fd_worlds<GG><<<blocks, lp.warps * 32, lp.smem, tr->stream>>>(dm, a, lp.wsd);
+    if (G == 8) { LAUNCH(8) } else if (G == 16) { LAUNCH(16) } else { LAUNCH(32) }
 #undef LAUNCH
+    g_launches++;
+    tr->counters[2] += 1;
+  }
   cudaEventRecord(tr->ev3, tr->stream);
   tr->fd_timed = true;
-  g_launches++;
   long long tot = (long long)nrows * (tr->m + 2 * tr->n) * tr->nx;
   k_fd_assemble<<<(int)((tot + 255) / 256), 256, 0, tr->stream>>>(dm, a, tr->A, tr->Bm);
   g_launches++;
   TOKP_CUDA(cudaGetLastError());
-  tr->counters[2] += 2;
+  tr->counters[2] += 1;
   return TOKP_OK;
 }
 

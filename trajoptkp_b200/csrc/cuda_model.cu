@@ -30,6 +30,37 @@ int lanes_for_model(const DM& dm) {
   return 32;
 }
 
+int fast_ecap(const DM& dm) {
+  int cap = 32;
+  if (const char* e = getenv("TOKP_EFC_CAP")) { int v = atoi(e); if (v > 0) cap = v; }
+  return cap < dm.maxefc ? cap : dm.maxefc;
+}
+
+int plan_launch(const DM& dm, int G, int pass, LaunchPlan* out) {
+  LaunchPlan p;
+  p.G = G; p.gpw = 32 / G;
+  p.ecap = pass == 0 ? fast_ecap(dm) : dm.maxefc;
+  p.wsd = tk::ws_doubles(dm, p.ecap);
+  size_t per_world = (size_t)p.wsd * 8;
+  const size_t sm_bytes = 227 * 1024, block_overhead = 1024;
+  // warps per block: the choice that keeps the most worlds resident per SM (ties -> larger blocks)
+  int best = 0, best_worlds = -1;
+  for (int w = 4; w >= 1; w >>= 1) {
+    size_t blk = per_world * w * p.gpw;
+    if (blk > sm_bytes) continue;
+    int resident = (int)(sm_bytes / (blk + block_overhead));
+    if (resident > 32) resident = 32;
+    if (resident * w > 64) resident = 64 / w;
+    int worlds = resident * w * p.gpw;
+    if (worlds > best_worlds) { best_worlds = worlds; best = w; }
+  }
+  if (const char* e = getenv("TOKP_WARPS")) { int v = atoi(e); if (v > 0 && per_world * v * p.gpw <= sm_bytes) best = v; }
+  if (best == 0) { set_error("model too large for the shared-memory workspace"); return TOKP_ERR_UNSUPPORTED; }
+  p.warps = best; p.worlds_per_block = best * p.gpw; p.smem = per_world * best * p.gpw;
+  *out = p;
+  return TOKP_OK;
+}
+
 int ensure_device_model(const tokp_model* mc, const DM** out) {
   tokp_model* m = const_cast<tokp_model*>(mc);
   std::lock_guard<std::mutex> lock(g_upload_mutex);
@@ -97,7 +128,7 @@ int ensure_device_model(const tokp_model* mc, const DM** out) {
 // in/out: host-layout snapshots [count][S] already on the device
 template <int G>
 __global__ void k_step_worlds(DM dm, const double* __restrict__ in, double* __restrict__ out, int* __restrict__ status,
-                              int count, int nsteps, int iterations, double tolerance, int S, int wsd) {
+                              int count, int nsteps, int iterations, double tolerance, int S, int wsd, int ecap, int pass) {
   extern __shared__ double smem[];
   constexpr int GPW = 32 / G;  // groups per warp
   tk::Grp<G> g;
@@ -105,8 +136,9 @@ __global__ void k_step_worlds(DM dm, const double* __restrict__ in, double* __re
   int gidx = (blockIdx.x * (blockDim.x >> 5) + warp) * GPW + lane / G;  // world index
   int slot = warp * GPW + lane / G;
   if (gidx >= count) return;
+  if (pass == 1 && !(status[gidx] & tk::ST_OVERFLOW)) return;  // redo pass: only worlds that overflowed the fast cap
   tk::WS w;
-  tk::ws_init(w, smem + (size_t)slot * wsd, dm);
+  tk::ws_init(w, smem + (size_t)slot * wsd, dm, ecap);
   const double* s = in + (size_t)gidx * S;
   int nq = dm.nq, nv = dm.nv;
   double time = s[0];
@@ -165,20 +197,19 @@ extern "C" int tokp_step_worlds(const tokp_model* m, const double* snapshots_in,
   int iters = solver_iterations < 0 ? dm.iterations : solver_iterations;
   double tol = solver_iterations < 0 ? dm.tolerance : solver_tolerance;
   int G = lanes_for_model(dm);
-  int wsd = tk::ws_doubles(dm);
-  int gpw = 32 / G;
-  int warps = 4;
-  while (warps > 1 && (size_t)warps * gpw * wsd * 8 > 200 * 1024) warps >>= 1;
-  size_t smem = (size_t)warps * gpw * wsd * 8;
-  if (smem > 227 * 1024) { set_error("model too large for the shared-memory workspace"); return TOKP_ERR_UNSUPPORTED; }
-  int worlds_per_block = warps * gpw;
-  int blocks = (count + worlds_per_block - 1) / worlds_per_block;
-#define LAUNCH(GG)                                                                                                  \
-  TOKP_CUDA(cudaFuncSetAttribute(k_step_worlds<GG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));       \
-  k_step_worlds<GG><<<blocks, warps * 32, smem>>>(dm, d_in, d_out, d_st, count, nsteps, iters, tol, S, wsd);
-  if (G == 8) { LAUNCH(8) } else if (G == 16) { LAUNCH(16) } else { LAUNCH(32) }
+  for (int pass = 0; pass < (needs_redo_pass(dm) ? 2 : 1); pass++) {
+    LaunchPlan lp;
+    rc = plan_launch(dm, G, pass, &lp);
+    if (rc) { cudaFree(d_in); cudaFree(d_out); cudaFree(d_st); return rc; }
+    int blocks = (count + lp.worlds_per_block - 1) / lp.worlds_per_block;
+#define LAUNCH(GG)                                                                                                    \
+  TOKP_CUDA(cudaFuncSetAttribute(k_step_worlds<GG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lp.smem));      \
+  k_step_worlds<GG><<<blocks, lp.warps * 32, lp.smem>>>(dm, d_in, d_out, d_st, count, nsteps, iters, tol, S, lp.wsd, \
+                                                        lp.ecap, pass);
+    if (G == 8) { LAUNCH(8) } else if (G == 16) { LAUNCH(16) } else { LAUNCH(32) }
 #undef LAUNCH
-  g_launches++;
+    g_launches++;
+  }
   TOKP_CUDA(cudaGetLastError());
   TOKP_CUDA(cudaDeviceSynchronize());
   TOKP_CUDA(cudaMemcpy(snapshots_out, d_out, bytes, cudaMemcpyDeviceToHost));

@@ -23,6 +23,9 @@ struct RollArgs {
   int iterations;
   double tolerance;
   TaskDev task;
+  int* flags;          // [nworlds] overflow flags written by pass 0, consumed by pass 1
+  int ecap, pass;
+  int spread;          // 1: one world per warp (first group only) - latency layout for small batches
 };
 
 template <int G>
@@ -30,15 +33,17 @@ __global__ void k_rollout(DM dm, RollArgs a, int wsd) {
   extern __shared__ double smem[];
   tk::Grp<G> g;
   int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  // one world per warp (latency path): only the first group of each warp works
-  if (lane / G != 0) return;
-  int widx = blockIdx.x * (blockDim.x >> 5) + warp;
+  constexpr int GPW = 32 / G;
+  if (a.spread && lane / G != 0) return;
+  int widx = a.spread ? blockIdx.x * (blockDim.x >> 5) + warp : (blockIdx.x * (blockDim.x >> 5) + warp) * GPW + lane / G;
+  int slot = a.spread ? warp : warp * GPW + lane / G;
   int nworlds = a.mode == 0 ? a.B : a.B * a.NA;
   if (widx >= nworlds) return;
+  if (a.pass == 1 && !a.flags[widx]) return;
   int b = a.mode == 0 ? widx : widx / a.NA;
   int ai = a.mode == 0 ? 0 : widx - b * a.NA;
   tk::WS w;
-  tk::ws_init(w, smem + (size_t)warp * wsd, dm);
+  tk::ws_init(w, smem + (size_t)slot * wsd, dm, a.ecap);
   const TaskDev& tk_ = a.task;
   int nq = dm.nq, nv = dm.nv, nu = dm.nu, n = tk_.n, m = tk_.m, nx = 2 * n, nr = tk_.nr, T = a.T, SD = a.SD;
   double* snapb = a.snap + (size_t)b * (T + 1) * SD;
@@ -120,6 +125,8 @@ __global__ void k_rollout(DM dm, RollArgs a, int wsd) {
     g.sync();
   }
   if (g.gl == 0) a.cost[a.mode == 0 ? b : b * a.NA + ai] = cost;
+  int ovf = g.any(st & tk::ST_OVERFLOW);
+  if (g.gl == 0) a.flags[widx] = (a.pass == 0 && ovf) ? 1 : 0;
 }
 
 int launch_rollout(tokp_traj* tr, int mode, const double* d_Uin, const double* d_alphas, int nalpha) {
@@ -132,18 +139,25 @@ int launch_rollout(tokp_traj* tr, int mode, const double* d_Uin, const double* d
   a.task = tr->task;
   if (mode == 1) a.NA = tokp_traj::NA;  // buffer stride; unused alpha slots are skipped by the grid size
   int G = tr->G;
-  int wsd = tk::ws_doubles(dm);
-  int warps = 1;
-  size_t smem = (size_t)warps * wsd * 8;
-  if (smem > 227 * 1024) { set_error("model too large for the shared-memory workspace"); return TOKP_ERR_UNSUPPORTED; }
+  a.flags = tr->roll_flags;
   int nworlds = mode == 0 ? tr->B : tr->B * tokp_traj::NA;
-  int blocks = (nworlds + warps - 1) / warps;
-#define LAUNCH(GG)                                                                                           \
-  TOKP_CUDA(cudaFuncSetAttribute(k_rollout<GG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));    \
-  k_rollout<GG><<<blocks, warps * 32, smem, tr->stream>>>(dm, a, wsd);
-  if (G == 8) { LAUNCH(8) } else if (G == 16) { LAUNCH(16) } else { LAUNCH(32) }
+  for (int pass = 0; pass < (needs_redo_pass(dm) ? 2 : 1); pass++) {
+    LaunchPlan lp;
+    int rc = plan_launch(dm, G, pass, &lp);
+    if (rc) return rc;
+    a.ecap = lp.ecap; a.pass = pass;
+    // few worlds: spread them over the SMs (one group per warp, one warp per block) rather than packing a warp
+    int warps = lp.warps;
+    int blocks = (nworlds + lp.worlds_per_block - 1) / lp.worlds_per_block;
+    a.spread = nworlds <= 148 * 4;
+    if (a.spread) { warps = 1; blocks = nworlds; lp.smem = (size_t)lp.wsd * 8; }
+#define LAUNCH(GG)                                                                                              \
+  TOKP_CUDA(cudaFuncSetAttribute(k_rollout<GG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lp.smem));    \
+  k_rollout<GG><<<blocks, warps * 32, lp.smem, tr->stream>>>(dm, a, lp.wsd);
+    if (G == 8) { LAUNCH(8) } else if (G == 16) { LAUNCH(16) } else { LAUNCH(32) }
 #undef LAUNCH
-  g_launches++;
+    g_launches++;
+  }
   TOKP_CUDA(cudaGetLastError());
   return TOKP_OK;
 }

@@ -73,6 +73,7 @@ extern "C" int tokp_traj_create(const tokp_model* m, const tokp_task_desc* td, i
   size_t o_dJ = p.take((size_t)B, 8);
   size_t o_lam = p.take((size_t)B, 8);
   size_t o_ok = p.take((size_t)B, 4);
+  size_t o_rflags = p.take((size_t)B * NA, 4);
   size_t o_s0 = p.take((size_t)B * tr->SD, 8);
   size_t o_u0 = p.take((size_t)B * T * mm, 8);
   size_t o_tints = p.take((size_t)(2 * n + mm), 4);
@@ -92,6 +93,7 @@ extern "C" int tokp_traj_create(const tokp_model* m, const tokp_task_desc* td, i
   tr->kp_prev = (int*)(base + o_prev); tr->kp_next = (int*)(base + o_next); tr->status = (int*)(base + o_status);
   tr->cost = (double*)(base + o_cost); tr->deltaJ = (double*)(base + o_dJ); tr->lambda_d = (double*)(base + o_lam);
   tr->bp_ok = (int*)(base + o_ok);
+  tr->roll_flags = (int*)(base + o_rflags);
   tr->snap0_in = (double*)(base + o_s0); tr->U0_in = (double*)(base + o_u0);
   tr->task_ints = (int*)(base + o_tints); tr->task_reals = (double*)(base + o_treals);
   // task tables

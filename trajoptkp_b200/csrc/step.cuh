@@ -143,66 +143,78 @@ TK_DEV bool in_mask(unsigned lo, unsigned hi, int bit) { return bit < 32 ? ((lo 
 TK_DEV bool bad_value(double x) { return !(fabs(x) <= 1e10); }
 
 // ---- per-world workspace (shared memory) ---------------------------------------------------------
+// Layout = persistent part P, followed by a union region shared by two groups of arrays with disjoint lifetimes:
+//   A  position-stage temporaries (dead once make_constraint has produced J, D, B, kterm)
+//      xpos xquat xanchor xaxis | crb  U  (con_dist con_pos con_frame) | efc_pos efc_margin | int tables
+//   B  H | (cvel cacc cfrc cdof_dot : velocity stage)  U  (jar jv quad efc_force : solver)
+// Rotation matrices (xmat, ximat, geom_xmat) are not stored: they are rebuilt from xquat where needed with the same
+// operation sequence (quat2mat then mat_vec3), so results are bit-identical to the stored-matrix form.
+// `ecap` is the constraint-row capacity of this launch: the fast pass uses a small cap, worlds that overflow it are
+// flagged (ST_OVERFLOW) and re-run by a second pass with ecap = maxefc.
 struct WS {
   // state
   double *qpos, *qvel, *qacc, *warm, *ctrl;
   // position stage
-  double *xpos, *xquat, *xmat, *xipos, *ximat, *xanchor, *xaxis, *gxpos, *gxmat;
+  double *xpos, *xquat, *xipos, *xanchor, *xaxis;
   double *rootcom, *cinert, *crb, *cdof, *cdof_dot;
   double *M, *LD, *LDinv, *H, *Hinv;  // Hinv: diag inverse for the Euler factor
   // contacts
   double *con_dist, *con_pos, *con_frame;
   int *con_pair;
   // constraint rows
-  double *J, *efc_pos, *efc_margin, *efc_D, *efc_aref, *efc_K, *efc_B, *efc_imp, *jar, *jv, *quad, *efc_force;
+  double *J, *efc_pos, *efc_margin, *efc_D, *efc_aref, *efc_B, *efc_kterm, *jar, *jv, *quad, *efc_force;
   int *row_type, *row_id, *row_sub, *cnt;  // cnt: scratch counters (max(njnt, npair) + 2)
   // velocity / acceleration stage
   double *cvel, *cacc, *cfrc;
   double *frc_passive, *frc_bias, *frc_act, *frc_smooth, *acc_smooth, *frc_con, *Ma, *Mv, *grad, *Mgrad, *search, *tmpv;
-  int ncon, nefc;
+  int ncon, nefc, ecap;
 };
 
-__host__ __device__ inline int ws_doubles(const DM& m) {
-  int nb = m.nbody, nv = m.nv, ne = m.maxefc, nc = m.maxcontact;
-  int n = 0;
-  n += m.nq + 3 * nv + m.nu;
-  n += nb * (3 + 4 + 9 + 3 + 9) + 6 * m.njnt + 12 * m.ngeom;
-  n += 3 * nb + 20 * nb + 12 * nv;
-  n += 3 * nv * nv + 2 * nv;
-  n += nc * 13;
-  n += ne * nv + ne * 13;
-  n += 18 * nb;
-  n += 12 * nv;
-  // int region (counted in doubles, rounded up)
-  int ints = nc + 3 * ne + (m.njnt > m.npair ? m.njnt : m.npair) + 4;
-  n += (ints + 1) / 2;
-  return n;
+__host__ __device__ inline int ws_imax(int a, int b) { return a > b ? a : b; }
+
+__host__ __device__ inline int ws_doubles(const DM& m, int ecap) {
+  int nb = m.nbody, nv = m.nv, ne = ecap, nc = m.maxcontact;
+  int P = m.nq + 3 * nv + m.nu + 3 * nb + 3 * nb + 10 * nb + 6 * nv + 2 * nv * nv + 2 * nv + 12 * nv + ne * nv + 4 * ne;
+  int ints = nc + 3 * ne + ws_imax(m.njnt, m.npair) + 4;
+  int A = 3 * nb + 4 * nb + 6 * m.njnt + ws_imax(10 * nb, 13 * nc) + 2 * ne + (ints + 1) / 2;
+  int B = nv * nv + ws_imax(18 * nb + 6 * nv, 6 * ne);
+  return P + ws_imax(A, B);
 }
 
-TK_DEV void ws_init(WS& w, double* base, const DM& m) {
-  int nb = m.nbody, nv = m.nv, ne = m.maxefc, nc = m.maxcontact;
+TK_DEV void ws_init(WS& w, double* base, const DM& m, int ecap) {
+  int nb = m.nbody, nv = m.nv, ne = ecap, nc = m.maxcontact;
   double* p = base;
   auto take = [&](int n) { double* r = p; p += n; return r; };
+  // P
   w.qpos = take(m.nq); w.qvel = take(nv); w.qacc = take(nv); w.warm = take(nv); w.ctrl = take(m.nu);
-  w.xpos = take(3 * nb); w.xquat = take(4 * nb); w.xmat = take(9 * nb); w.xipos = take(3 * nb); w.ximat = take(9 * nb);
-  w.xanchor = take(3 * m.njnt); w.xaxis = take(3 * m.njnt); w.gxpos = take(3 * m.ngeom); w.gxmat = take(9 * m.ngeom);
-  w.rootcom = take(3 * nb); w.cinert = take(10 * nb); w.crb = take(10 * nb); w.cdof = take(6 * nv); w.cdof_dot = take(6 * nv);
-  w.M = take(nv * nv); w.LD = take(nv * nv); w.H = take(nv * nv); w.LDinv = take(nv); w.Hinv = take(nv);
-  w.con_dist = take(nc); w.con_pos = take(3 * nc); w.con_frame = take(9 * nc);
-  w.J = take(ne * nv);
-  w.efc_pos = take(ne); w.efc_margin = take(ne); w.efc_D = take(ne); w.efc_aref = take(ne); w.efc_K = take(ne);
-  w.efc_B = take(ne); w.efc_imp = take(ne); w.jar = take(ne); w.jv = take(ne); w.quad = take(3 * ne); w.efc_force = take(ne);
-  w.cvel = take(6 * nb); w.cacc = take(6 * nb); w.cfrc = take(6 * nb);
+  w.xipos = take(3 * nb); w.rootcom = take(3 * nb); w.cinert = take(10 * nb); w.cdof = take(6 * nv);
+  w.M = take(nv * nv); w.LD = take(nv * nv); w.LDinv = take(nv); w.Hinv = take(nv);
   w.frc_passive = take(nv); w.frc_bias = take(nv); w.frc_act = take(nv); w.frc_smooth = take(nv); w.acc_smooth = take(nv);
   w.frc_con = take(nv); w.Ma = take(nv); w.Mv = take(nv); w.grad = take(nv); w.Mgrad = take(nv); w.search = take(nv);
   w.tmpv = take(nv);
+  w.J = take(ne * nv); w.efc_D = take(ne); w.efc_aref = take(ne); w.efc_B = take(ne); w.efc_kterm = take(ne);
+  double* u = p;
+  // A
+  w.xpos = take(3 * nb); w.xquat = take(4 * nb); w.xanchor = take(3 * m.njnt); w.xaxis = take(3 * m.njnt);
+  double* u2 = p;
+  w.crb = u2;
+  w.con_dist = u2; w.con_pos = u2 + nc; w.con_frame = u2 + 4 * nc;
+  p = u2 + ws_imax(10 * nb, 13 * nc);
+  w.efc_pos = take(ne); w.efc_margin = take(ne);
   int* ip = reinterpret_cast<int*>(p);
   w.con_pair = ip; ip += nc;
   w.row_type = ip; ip += ne;
   w.row_id = ip; ip += ne;
   w.row_sub = ip; ip += ne;
   w.cnt = ip;
-  w.ncon = 0; w.nefc = 0;
+  // B
+  p = u;
+  w.H = take(nv * nv);
+  double* u3 = p;
+  w.cvel = take(6 * nb); w.cacc = take(6 * nb); w.cfrc = take(6 * nb); w.cdof_dot = take(6 * nv);
+  p = u3;
+  w.jar = take(ne); w.jv = take(ne); w.quad = take(3 * ne); w.efc_force = take(ne);
+  w.ncon = 0; w.nefc = 0; w.ecap = ecap;
 }
 
 }  // namespace tk

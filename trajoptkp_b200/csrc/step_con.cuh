@@ -81,10 +81,9 @@ TK_DEV void collision(const DM& m, WS& w, const Grp<G>& g, int& status) {
     int slot = 0;
     for (int q = 0; q < p; q++) slot += pair_slots(m.geom_type[m.pair_geom1[q]], m.geom_type[m.pair_geom2[q]]);
     double margin = fmax(m.geom_margin[g1], m.geom_margin[g2]);
-    const double* pos1 = &w.gxpos[3 * g1];
-    const double* mat1 = &w.gxmat[9 * g1];
-    const double* pos2 = &w.gxpos[3 * g2];
-    const double* mat2 = &w.gxmat[9 * g2];
+    double pos1[3], mat1[9], pos2[3], mat2[9];
+    geom_pose(m, w, g1, pos1, mat1);
+    geom_pose(m, w, g2, pos2, mat2);
     int n = 0;
     if (t1 == GEOM_PLANE) {
       double nrm[3] = {mat1[2], mat1[5], mat1[8]};
@@ -196,7 +195,7 @@ TK_DEV void make_constraint(const DM& m, WS& w, const Grp<G>& g, int& status) {
       for (int side = -1; side <= 1; side += 2) {
         double dist = side * (m.jnt_range[2 * j + (side + 1) / 2] - value);
         if (dist < margin) {
-          if (r >= m.maxefc) { status |= ST_OVERFLOW; continue; }
+          if (r >= w.ecap) { status |= ST_OVERFLOW; continue; }
           w.row_type[r] = ROW_LIMIT; w.row_id[r] = j; w.row_sub[r] = side;
           w.efc_pos[r] = dist; w.efc_margin[r] = margin;
           r++;
@@ -212,7 +211,7 @@ TK_DEV void make_constraint(const DM& m, WS& w, const Grp<G>& g, int& status) {
       if (w.con_dist[c] >= inc) continue;  // excluded (in the gap)
       int rows = cp.dim == 1 ? 1 : (cp.dim == 3 ? 4 : -1);
       if (rows < 0) { status |= ST_UNSUPPORTED; continue; }
-      if (r + rows > m.maxefc) { status |= ST_OVERFLOW; continue; }
+      if (r + rows > w.ecap) { status |= ST_OVERFLOW; continue; }
       for (int k = 0; k < rows; k++) {
         w.row_type[r] = rows == 1 ? ROW_FRICTIONLESS : ROW_PYRAMIDAL;
         w.row_id[r] = c; w.row_sub[r] = k;
@@ -280,7 +279,8 @@ TK_DEV void make_constraint(const DM& m, WS& w, const Grp<G>& g, int& status) {
         Rr = 2.0 * cp.mu * cp.mu * R0;
       }
     }
-    w.efc_K[r] = K; w.efc_B[r] = B; w.efc_imp[r] = imp;
+    w.efc_B[r] = B;
+    w.efc_kterm[r] = K * imp * (w.efc_pos[r] - w.efc_margin[r]);
     w.efc_D[r] = 1.0 / Rr;
   }
   g.sync();
@@ -293,7 +293,7 @@ TK_DEV void reference_constraint(const DM& m, WS& w, const Grp<G>& g) {
   for (int r = g.gl; r < w.nefc; r += G) {
     double vel = 0.0;
     for (int i = 0; i < nv; i++) vel += w.J[r * nv + i] * w.qvel[i];
-    w.efc_aref[r] = -w.efc_B[r] * vel - w.efc_K[r] * w.efc_imp[r] * (w.efc_pos[r] - w.efc_margin[r]);
+    w.efc_aref[r] = -w.efc_B[r] * vel - w.efc_kterm[r];
   }
   g.sync();
 }

@@ -11,7 +11,6 @@ TK_DEV void kinematics(const DM& m, WS& w, const Grp<G>& g) {
   if (g.gl == 0) {
     w.xpos[0] = w.xpos[1] = w.xpos[2] = 0.0;
     w.xquat[0] = 1.0; w.xquat[1] = w.xquat[2] = w.xquat[3] = 0.0;
-    for (int k = 0; k < 9; k++) { w.xmat[k] = (k % 4 == 0) ? 1.0 : 0.0; w.ximat[k] = w.xmat[k]; }
     w.xipos[0] = w.xipos[1] = w.xipos[2] = 0.0;
   }
   g.sync();
@@ -31,7 +30,7 @@ TK_DEV void kinematics(const DM& m, WS& w, const Grp<G>& g) {
       } else {
         double bpos[3] = {m.body_pos[3 * i], m.body_pos[3 * i + 1], m.body_pos[3 * i + 2]};
         double bquat[4] = {m.body_quat[4 * i], m.body_quat[4 * i + 1], m.body_quat[4 * i + 2], m.body_quat[4 * i + 3]};
-        mat_vec3(xpos, &w.xmat[9 * pid], bpos);
+        { double pm[9]; quat2mat(pm, &w.xquat[4 * pid]); mat_vec3(xpos, pm, bpos); }
         for (int k = 0; k < 3; k++) xpos[k] += w.xpos[3 * pid + k];
         mul_quat(xquat, &w.xquat[4 * pid], bquat);
         for (int j = jntadr; j < jntadr + jntnum; j++) {
@@ -60,28 +59,29 @@ TK_DEV void kinematics(const DM& m, WS& w, const Grp<G>& g) {
       normalize4(xquat);
       for (int k = 0; k < 3; k++) w.xpos[3 * i + k] = xpos[k];
       for (int k = 0; k < 4; k++) w.xquat[4 * i + k] = xquat[k];
-      quat2mat(&w.xmat[9 * i], xquat);
+      double xm[9];
+      quat2mat(xm, xquat);
       double ipos[3] = {m.body_ipos[3 * i], m.body_ipos[3 * i + 1], m.body_ipos[3 * i + 2]};
-      double iquat[4] = {m.body_iquat[4 * i], m.body_iquat[4 * i + 1], m.body_iquat[4 * i + 2], m.body_iquat[4 * i + 3]};
-      double v[3], q[4];
-      mat_vec3(v, &w.xmat[9 * i], ipos);
+      double v[3];
+      mat_vec3(v, xm, ipos);
       for (int k = 0; k < 3; k++) w.xipos[3 * i + k] = xpos[k] + v[k];
-      mul_quat(q, xquat, iquat);
-      quat2mat(&w.ximat[9 * i], q);
     }
     g.sync();
   }
-  for (int gi = g.gl; gi < m.ngeom; gi += G) {
-    int b = m.geom_bodyid[gi];
-    double gpos[3] = {m.geom_pos[3 * gi], m.geom_pos[3 * gi + 1], m.geom_pos[3 * gi + 2]};
-    double gquat[4] = {m.geom_quat[4 * gi], m.geom_quat[4 * gi + 1], m.geom_quat[4 * gi + 2], m.geom_quat[4 * gi + 3]};
-    double v[3], q[4];
-    mat_vec3(v, &w.xmat[9 * b], gpos);
-    for (int k = 0; k < 3; k++) w.gxpos[3 * gi + k] = w.xpos[3 * b + k] + v[k];
-    mul_quat(q, &w.xquat[4 * b], gquat);
-    quat2mat(&w.gxmat[9 * gi], q);
-  }
-  g.sync();
+}
+
+// world pose of a geom (mj_kinematics' geom_xpos / geom_xmat), rebuilt from the body pose on demand
+TK_DEV void geom_pose(const DM& m, const WS& w, int gi, double* gpos_out, double* gmat_out) {
+  int b = m.geom_bodyid[gi];
+  double gpos[3] = {m.geom_pos[3 * gi], m.geom_pos[3 * gi + 1], m.geom_pos[3 * gi + 2]};
+  double gquat[4] = {m.geom_quat[4 * gi], m.geom_quat[4 * gi + 1], m.geom_quat[4 * gi + 2], m.geom_quat[4 * gi + 3]};
+  double v[3], q[4], xm[9];
+  if (b == 0) { for (int k = 0; k < 9; k++) xm[k] = (k % 4 == 0) ? 1.0 : 0.0; }
+  else quat2mat(xm, &w.xquat[4 * b]);
+  mat_vec3(v, xm, gpos);
+  for (int k = 0; k < 3; k++) gpos_out[k] = w.xpos[3 * b + k] + v[k];
+  mul_quat(q, &w.xquat[4 * b], gquat);
+  quat2mat(gmat_out, q);
 }
 
 // mj_comPos: centre of mass of every kinematic tree (stored at its root body), com-frame inertias, motion axes
@@ -110,7 +110,12 @@ TK_DEV void com_pos(const DM& m, WS& w, const Grp<G>& g) {
     int root = m.body_rootid[i];
     double dif[3], mass = m.body_mass[i];
     for (int k = 0; k < 3; k++) dif[k] = w.xipos[3 * i + k] - w.rootcom[3 * root + k];
-    const double* mat = &w.ximat[9 * i];
+    double mat[9];
+    {
+      double iquat[4] = {m.body_iquat[4 * i], m.body_iquat[4 * i + 1], m.body_iquat[4 * i + 2], m.body_iquat[4 * i + 3]}, q[4];
+      mul_quat(q, &w.xquat[4 * i], iquat);
+      quat2mat(mat, q);
+    }
     double in0 = m.body_inertia[3 * i], in1 = m.body_inertia[3 * i + 1], in2 = m.body_inertia[3 * i + 2];
     double t0 = mat[0] * in0, t3 = mat[1] * in1, t6 = mat[2] * in2;
     double t1 = mat[3] * in0, t4 = mat[4] * in1, t7 = mat[5] * in2;
@@ -132,8 +137,10 @@ TK_DEV void com_pos(const DM& m, WS& w, const Grp<G>& g) {
     if (jt == JNT_FREE) {
       for (int k = 0; k < 18; k++) w.cdof[6 * da + k] = 0.0;
       w.cdof[6 * da + 3] = 1.0; w.cdof[6 * (da + 1) + 4] = 1.0; w.cdof[6 * (da + 2) + 5] = 1.0;
+      double xm[9];
+      quat2mat(xm, &w.xquat[4 * bi]);
       for (int k = 0; k < 3; k++) {
-        double ax[3] = {w.xmat[9 * bi + k], w.xmat[9 * bi + 3 + k], w.xmat[9 * bi + 6 + k]};
+        double ax[3] = {xm[k], xm[3 + k], xm[6 + k]};
         double* c = &w.cdof[6 * (da + 3 + k)];
         c[0] = ax[0]; c[1] = ax[1]; c[2] = ax[2];
         cross3(c + 3, ax, off);

@@ -29,6 +29,17 @@ int ensure_device_model(const tokp_model* m, const DM** out);
 // number of lanes per world for a model (8, 16 or 32)
 int lanes_for_model(const DM& dm);
 
+// Shared-memory launch plan of the world kernels.  pass 0 = fast pass with a small constraint-row capacity
+// (TOKP_EFC_CAP, default min(maxefc, 32)); pass 1 = redo pass with ecap = maxefc for the worlds that overflowed.
+struct LaunchPlan {
+  int G, gpw, ecap, wsd, warps, worlds_per_block;
+  size_t smem;
+};
+int fast_ecap(const DM& dm);
+inline bool needs_redo_pass(const DM& dm) { return fast_ecap(dm) < dm.maxefc; }
+// returns TOKP_OK or TOKP_ERR_UNSUPPORTED (workspace does not fit shared memory)
+int plan_launch(const DM& dm, int G, int pass, LaunchPlan* out);
+
 // compact device snapshot: [time | qpos nq | qvel nv | qacc nv | warm nv | ctrl nu]
 inline int dsnap_size(const DM& dm) { return 1 + dm.nq + 3 * dm.nv + dm.nu; }
 
@@ -65,6 +76,7 @@ struct tokp_traj {
   double *cost, *deltaJ, *lambda_d;  // [B]
   double *snap0_in, *U0_in;          // resident copies of the last host inputs of tokp_optimise ([B][SD], [B][T][m])
   int* bp_ok;         // [B]
+  int* roll_flags;    // [B][NA] rollout worlds that overflowed the fast constraint-row capacity
   int* task_ints;     // qpos_adr | dof_adr | ctrl_adr
   double* task_reals;
   static const int NA = 6;

@@ -44,37 +44,47 @@ __global__ void k_fd_worlds(DM dm, FdArgs a, int wsd) {
   long long gidx = ((long long)blockIdx.x * (blockDim.x >> 5) + warp) * GPW + lane / G;
   int slot_s = warp * GPW + lane / G;
   long long total = (long long)a.nrows * a.W;
-  if (gidx >= total) return;
-  int rowi = (int)(gidx / a.W), slot = (int)(gidx - (long long)rowi * a.W);
-  int row = a.rows ? a.rows[rowi] : rowi;
-  int b = row / a.T, t = row - b * a.T;
-  unsigned long long mask = a.mask[row];
-  int* st_out = a.status + (size_t)row * a.W + slot;
-  if (a.pass == 1 && !(*st_out & tk::ST_OVERFLOW)) return;
-  if (mask == 0ull) { if (g.gl == 0) *st_out = 0; return; }
-  // decode
-  int kind = 0, col = 0, sgn = 0;
-  if (slot > 0) {
-    int s = slot - 1;
-    if (s < 2 * a.m) { kind = 1; col = s >> 1; sgn = s & 1; }
-    else if (s < 2 * a.m + 2 * a.n) { s -= 2 * a.m; kind = 2; col = s >> 1; sgn = s & 1; }
-    else { s -= 2 * a.m + 2 * a.n; kind = 3; col = s >> 1; sgn = s & 1; }
-    if (!((mask >> col) & 1ull)) { if (g.gl == 0) *st_out = 0; return; }
-  }
-  const double* s = a.snap + ((size_t)b * (a.T + 1) + t) * a.SD;
+  // decide whether this group simulates a world; the decision is balloted over the full warp so that the running
+  // groups know each other (Grp::wmask) before any of them returns
   int nq = dm.nq, nv = dm.nv;
-  // control perturbations are clamp-aware (Differentiator.cpp:98-102,136-143); forward mode drops the minus
-  // side unless the plus side is infeasible
-  if (kind == 1) {
-    double u = s[1 + nq + 3 * nv + a.ctrl_adr[col]];
-    bool fwd_ok = !(u + a.eps > a.ctrl_limits[2 * col + 1]);
-    bool back_wanted = a.central || !fwd_ok;
-    bool back_ok = back_wanted && !(u - a.eps < a.ctrl_limits[2 * col]);
-    if ((sgn == 0 && !fwd_ok) || (sgn == 1 && !back_ok)) { if (g.gl == 0) *st_out = 0; return; }
-  } else if (kind >= 2 && sgn == 1 && !a.central) {
-    if (g.gl == 0) *st_out = 0;
-    return;
+  bool run = gidx < total, clear_status = false;
+  int rowi = 0, slot = 0, row = 0, b = 0, t = 0, kind = 0, col = 0, sgn = 0;
+  int* st_out = nullptr;
+  const double* s = nullptr;
+  if (run) {
+    rowi = (int)(gidx / a.W); slot = (int)(gidx - (long long)rowi * a.W);
+    row = a.rows ? a.rows[rowi] : rowi;
+    b = row / a.T; t = row - b * a.T;
+    unsigned long long mask = a.mask[row];
+    st_out = a.status + (size_t)row * a.W + slot;
+    s = a.snap + ((size_t)b * (a.T + 1) + t) * a.SD;
+    if (a.pass == 1) {
+      run = (*st_out & tk::ST_OVERFLOW) != 0;
+    } else if (mask == 0ull) {
+      run = false; clear_status = true;
+    }
+    if (run && slot > 0) {
+      int q = slot - 1;
+      if (q < 2 * a.m) { kind = 1; col = q >> 1; sgn = q & 1; }
+      else if (q < 2 * a.m + 2 * a.n) { q -= 2 * a.m; kind = 2; col = q >> 1; sgn = q & 1; }
+      else { q -= 2 * a.m + 2 * a.n; kind = 3; col = q >> 1; sgn = q & 1; }
+      if (!((mask >> col) & 1ull)) { run = false; clear_status = true; }
+    }
+    // control perturbations are clamp-aware (Differentiator.cpp:98-102,136-143); forward mode drops the minus
+    // side unless the plus side is infeasible
+    if (run && kind == 1) {
+      double u = s[1 + nq + 3 * nv + a.ctrl_adr[col]];
+      bool fwd_ok = !(u + a.eps > a.ctrl_limits[2 * col + 1]);
+      bool back_wanted = a.central || !fwd_ok;
+      bool back_ok = back_wanted && !(u - a.eps < a.ctrl_limits[2 * col]);
+      if ((sgn == 0 && !fwd_ok) || (sgn == 1 && !back_ok)) { run = false; clear_status = true; }
+    } else if (run && kind >= 2 && sgn == 1 && !a.central) {
+      run = false; clear_status = true;
+    }
   }
+  unsigned wm = __ballot_sync(0xffffffffu, run);
+  if (!run) { if (clear_status && g.gl == 0) *st_out = 0; return; }
+  g.wmask = wm;
   tk::WS w;
   tk::ws_init(w, smem + (size_t)slot_s * wsd, dm, a.ecap);
   double time = s[0];

@@ -135,8 +135,11 @@ __global__ void k_step_worlds(DM dm, const double* __restrict__ in, double* __re
   int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   int gidx = (blockIdx.x * (blockDim.x >> 5) + warp) * GPW + lane / G;  // world index
   int slot = warp * GPW + lane / G;
-  if (gidx >= count) return;
-  if (pass == 1 && !(status[gidx] & tk::ST_OVERFLOW)) return;  // redo pass: only worlds that overflowed the fast cap
+  bool run = gidx < count;
+  if (run && pass == 1 && !(status[gidx] & tk::ST_OVERFLOW)) run = false;  // redo pass: only overflowed worlds
+  unsigned wm = __ballot_sync(0xffffffffu, run);
+  if (!run) return;
+  g.wmask = wm;
   tk::WS w;
   tk::ws_init(w, smem + (size_t)slot * wsd, dm, ecap);
   const double* s = in + (size_t)gidx * S;

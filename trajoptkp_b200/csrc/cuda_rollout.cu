@@ -34,12 +34,14 @@ __global__ void k_rollout(DM dm, RollArgs a, int wsd) {
   tk::Grp<G> g;
   int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   constexpr int GPW = 32 / G;
-  if (a.spread && lane / G != 0) return;
   int widx = a.spread ? blockIdx.x * (blockDim.x >> 5) + warp : (blockIdx.x * (blockDim.x >> 5) + warp) * GPW + lane / G;
   int slot = a.spread ? warp : warp * GPW + lane / G;
   int nworlds = a.mode == 0 ? a.B : a.B * a.NA;
-  if (widx >= nworlds) return;
-  if (a.pass == 1 && !a.flags[widx]) return;
+  bool run = widx < nworlds && !(a.spread && lane / G != 0);
+  if (run && a.pass == 1 && !a.flags[widx]) run = false;
+  unsigned wm = __ballot_sync(0xffffffffu, run);
+  if (!run) return;
+  g.wmask = wm;
   int b = a.mode == 0 ? widx : widx / a.NA;
   int ai = a.mode == 0 ? 0 : widx - b * a.NA;
   tk::WS w;

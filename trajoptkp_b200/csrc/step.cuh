@@ -30,12 +30,18 @@ enum { ST_BAD_QPOS = 1, ST_BAD_QVEL = 2, ST_BAD_QACC = 4, ST_OVERFLOW = 8, ST_UN
 template <int G>
 struct Grp {
   unsigned mask;
+  unsigned wmask;  // lanes of every group of this warp that runs a world (set by the kernel with a full-warp ballot)
   int gl;  // lane index inside the group
   TK_DEV Grp() {
     int lane = threadIdx.x & 31;
     gl = lane % G;
     mask = (G == 32) ? 0xffffffffu : (((1u << G) - 1u) << (lane - gl));
+    wmask = mask;
   }
+  // warp-uniform loop condition: true while any running group of the warp still wants to iterate.  All running
+  // groups must reach every any_warp() call; it doubles as the point where the groups of a warp reconverge, so that
+  // the worlds sharing a warp execute the solver's loops in lock-step instead of one after the other.
+  TK_DEV int any_warp(int p) const { return __any_sync(wmask, p); }
   TK_DEV void sync() const { __syncwarp(mask); }
   TK_DEV double sum(double v) const {
 #pragma unroll

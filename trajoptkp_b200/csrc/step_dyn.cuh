@@ -159,80 +159,6 @@ TK_DEV Pnt primal_eval(const WS& w, const Grp<G>& g, const double qg[3], double 
   return p;
 }
 
-template <int G>
-TK_DEV int update_bracket(const WS& w, const Grp<G>& g, const double qg[3], Pnt& p, const Pnt cand[3], Pnt& pnext, int& lsiter) {
-  int flag = 0;
-  for (int i = 0; i < 3; i++) {
-    if (p.d0 < 0.0 && cand[i].d0 < 0.0 && p.d0 < cand[i].d0) { p = cand[i]; flag = 1; }
-    else if (p.d0 > 0.0 && cand[i].d0 > 0.0 && p.d0 > cand[i].d0) { p = cand[i]; flag = 2; }
-  }
-  if (flag) pnext = primal_eval(w, g, qg, p.alpha - p.d0 / p.d1, lsiter);
-  return flag;
-}
-
-// exact line search along w.search (PrimalSearch); returns the step
-template <int G>
-TK_DEV double primal_search(const DM& m, WS& w, const Grp<G>& g, double gauss, double tolerance) {
-  int nv = m.nv;
-  double sn = 0.0;
-  for (int i = g.gl; i < nv; i += G) sn += w.search[i] * w.search[i];
-  double snorm = sqrt(g.sum(sn));
-  if (snorm < kMinVal) return 0.0;
-  double scale = 1.0 / (m.meaninertia * (double)max(1, nv));
-  double gtol = tolerance * m.ls_tolerance * snorm / scale;
-  mul_M(m, w, w.Mv, w.search, g);
-  for (int r = g.gl; r < w.nefc; r += G) {
-    double s = 0.0;
-    for (int i = 0; i < nv; i++) s += w.J[r * nv + i] * w.search[i];
-    w.jv[r] = s;
-    double DJ0 = w.efc_D[r] * w.jar[r];
-    w.quad[3 * r] = 0.5 * w.jar[r] * DJ0;
-    w.quad[3 * r + 1] = s * DJ0;
-    w.quad[3 * r + 2] = 0.5 * s * w.efc_D[r] * s;
-  }
-  g.sync();
-  double a = 0.0, b = 0.0, c = 0.0;
-  for (int i = g.gl; i < nv; i += G) {
-    a += w.search[i] * w.Ma[i];
-    b += w.frc_smooth[i] * w.search[i];
-    c += w.search[i] * w.Mv[i];
-  }
-  double qg[3] = {gauss, g.sum(a) - g.sum(b), 0.5 * g.sum(c)};
-  int lsiter = 0;
-  Pnt p0 = primal_eval(w, g, qg, 0.0, lsiter);
-  Pnt p1 = primal_eval(w, g, qg, p0.alpha - p0.d0 / p0.d1, lsiter);
-  if (p0.cost < p1.cost) p1 = p0;
-  if (fabs(p1.d0) < gtol) return p1.alpha;
-  double dir = (p1.d0 < 0.0) ? 1.0 : -1.0;
-  int p2update = 0;
-  Pnt p2 = p1;
-  while (p1.d0 * dir <= -gtol && lsiter < m.ls_iterations) {
-    p2 = p1;
-    p2update = 1;
-    p1 = primal_eval(w, g, qg, p1.alpha - p1.d0 / p1.d1, lsiter);
-    if (fabs(p1.d0) < gtol) return p1.alpha;
-  }
-  if (lsiter >= m.ls_iterations) return p1.alpha;
-  if (!p2update) return p1.alpha;
-  Pnt p2next = p1;
-  Pnt p1next = primal_eval(w, g, qg, p1.alpha - p1.d0 / p1.d1, lsiter);
-  while (lsiter < m.ls_iterations) {
-    Pnt pmid = primal_eval(w, g, qg, 0.5 * (p1.alpha + p2.alpha), lsiter);
-    Pnt cand[3] = {p1next, p2next, pmid};
-    double bestcost = 0.0;
-    int bestind = -1;
-    for (int i = 0; i < 3; i++)
-      if (fabs(cand[i].d0) < gtol && (bestind == -1 || cand[i].cost < bestcost)) { bestcost = cand[i].cost; bestind = i; }
-    if (bestind >= 0) return cand[bestind].alpha;
-    int b1 = update_bracket(w, g, qg, p1, cand, p1next, lsiter);
-    int b2 = update_bracket(w, g, qg, p2, cand, p2next, lsiter);
-    if (!b1 && !b2) return pmid.alpha;
-  }
-  if (p1.cost <= p2.cost && p1.cost < p0.cost) return p1.alpha;
-  if (p2.cost <= p1.cost && p2.cost < p0.cost) return p2.alpha;
-  return 0.0;
-}
-
 // in-place dense Cholesky (lower) of the nv x nv matrix in w.H, right-looking, lanes over the trailing block
 template <int G>
 TK_DEV void chol_factor(double* H, int n, const Grp<G>& g) {
@@ -274,39 +200,16 @@ TK_DEV void chol_solve(const double* L, int n, double* x, const double* b, const
   }
 }
 
-// mj_fwdConstraint with the Newton solver
+}  // namespace tk
+#include "step_ls.cuh"
+namespace tk {
+
+// mj_fwdConstraint with the Newton solver.  The Newton and line-search loops are warp-uniform (Grp::any_warp): every
+// running world of the warp passes through them together; worlds without constraints or already converged idle.
 template <int G>
 TK_DEV void fwd_constraint(const DM& m, WS& w, const Grp<G>& g, int iterations, double tolerance) {
   int nv = m.nv, nefc = w.nefc;
-  if (nefc == 0) {
-    for (int i = g.gl; i < nv; i += G) { w.qacc[i] = w.acc_smooth[i]; w.warm[i] = w.acc_smooth[i]; w.frc_con[i] = 0.0; }
-    g.sync();
-    return;
-  }
-  // warm start: keep qacc_warmstart only if it costs less than qacc_smooth
-  for (int r = g.gl; r < nefc; r += G) {
-    double s1 = 0.0, s2 = 0.0;
-    for (int i = 0; i < nv; i++) { s1 += w.J[r * nv + i] * w.warm[i]; s2 += w.J[r * nv + i] * w.acc_smooth[i]; }
-    w.jar[r] = s1 - w.efc_aref[r];
-    w.jv[r] = s2 - w.efc_aref[r];
-  }
-  mul_M(m, w, w.Ma, w.warm, g);
-  g.sync();
-  double cw = constraint_cost(w, w.jar, g);
-  double gs = 0.0;
-  for (int i = g.gl; i < nv; i += G) gs += (w.Ma[i] - w.frc_smooth[i]) * (w.warm[i] - w.acc_smooth[i]);
-  cw += 0.5 * g.sum(gs);
-  double cs = constraint_cost(w, w.jv, g);
-  bool use_smooth = cw > cs;
-  g.sync();
-  for (int i = g.gl; i < nv; i += G) w.qacc[i] = use_smooth ? w.acc_smooth[i] : w.warm[i];
-  if (use_smooth) {
-    for (int r = g.gl; r < nefc; r += G) w.jar[r] = w.jv[r];
-    g.sync();
-    mul_M(m, w, w.Ma, w.qacc, g);
-  }
-  g.sync();
-
+  const bool has = nefc > 0;
   double cost = 0.0, gauss = 0.0;
   auto update = [&]() {
     // forces, cost, qfrc_constraint, gradient, Hessian, Newton direction
@@ -342,27 +245,69 @@ TK_DEV void fwd_constraint(const DM& m, WS& w, const Grp<G>& g, int iterations, 
     for (int i = g.gl; i < nv; i += G) w.search[i] = -w.Mgrad[i];
     g.sync();
   };
-
-  update();
-  double scale = 1.0 / (m.meaninertia * (double)max(1, nv));
-  int iter = 0;
-  while (iter < iterations) {
-    double alpha = primal_search(m, w, g, gauss, tolerance);
-    if (alpha == 0.0) break;
-    for (int i = g.gl; i < nv; i += G) { w.qacc[i] += alpha * w.search[i]; w.Ma[i] += alpha * w.Mv[i]; }
-    for (int r = g.gl; r < nefc; r += G) w.jar[r] += alpha * w.jv[r];
+  if (!has) {
+    for (int i = g.gl; i < nv; i += G) { w.qacc[i] = w.acc_smooth[i]; w.warm[i] = w.acc_smooth[i]; w.frc_con[i] = 0.0; }
     g.sync();
-    double oldcost = cost;
-    update();
-    double gn = 0.0;
-    for (int i = g.gl; i < nv; i += G) gn += w.grad[i] * w.grad[i];
-    double improvement = scale * (oldcost - cost);
-    double gradient = scale * sqrt(g.sum(gn));
-    iter++;
-    if (improvement < tolerance || gradient < tolerance) break;
+  } else {
+    // warm start: keep qacc_warmstart only if it costs less than qacc_smooth
+    for (int r = g.gl; r < nefc; r += G) {
+      double s1 = 0.0, s2 = 0.0;
+      for (int i = 0; i < nv; i++) { s1 += w.J[r * nv + i] * w.warm[i]; s2 += w.J[r * nv + i] * w.acc_smooth[i]; }
+      w.jar[r] = s1 - w.efc_aref[r];
+      w.jv[r] = s2 - w.efc_aref[r];
+    }
+    mul_M(m, w, w.Ma, w.warm, g);
+    g.sync();
+    double cw = constraint_cost(w, w.jar, g);
+    double gs = 0.0;
+    for (int i = g.gl; i < nv; i += G) gs += (w.Ma[i] - w.frc_smooth[i]) * (w.warm[i] - w.acc_smooth[i]);
+    cw += 0.5 * g.sum(gs);
+    double cs = constraint_cost(w, w.jv, g);
+    bool use_smooth = cw > cs;
+    g.sync();
+    for (int i = g.gl; i < nv; i += G) w.qacc[i] = use_smooth ? w.acc_smooth[i] : w.warm[i];
+    if (use_smooth) {
+      for (int r = g.gl; r < nefc; r += G) w.jar[r] = w.jv[r];
+      g.sync();
+      mul_M(m, w, w.Ma, w.qacc, g);
+    }
+    g.sync();
   }
-  for (int i = g.gl; i < nv; i += G) w.warm[i] = w.qacc[i];
-  g.sync();
+  double scale = 1.0 / (m.meaninertia * (double)max(1, nv));
+  // iter == -1 is the initial update(); sharing the call site keeps one copy of the Hessian/Cholesky code and lets
+  // all running worlds of the warp execute it together
+  int iter = -1;
+  bool run = has;
+  double alpha = 1.0, oldcost = 0.0;
+  while (g.any_warp(run)) {
+    if (run) {
+      if (iter >= 0 && alpha == 0.0) {
+        run = false;
+      } else {
+        if (iter >= 0) {
+          for (int i = g.gl; i < nv; i += G) { w.qacc[i] += alpha * w.search[i]; w.Ma[i] += alpha * w.Mv[i]; }
+          for (int r = g.gl; r < nefc; r += G) w.jar[r] += alpha * w.jv[r];
+          g.sync();
+        }
+        oldcost = cost;
+        update();
+        if (iter >= 0) {
+          double gn = 0.0;
+          for (int i = g.gl; i < nv; i += G) gn += w.grad[i] * w.grad[i];
+          double improvement = scale * (oldcost - cost);
+          double gradient = scale * sqrt(g.sum(gn));
+          if (improvement < tolerance || gradient < tolerance) run = false;
+        }
+        iter++;
+        if (iter >= iterations) run = false;
+      }
+    }
+    alpha = primal_search(m, w, g, gauss, tolerance, run);
+  }
+  if (has) {
+    for (int i = g.gl; i < nv; i += G) w.warm[i] = w.qacc[i];
+    g.sync();
+  }
 }
 
 // mj_EulerSkip + mj_advance

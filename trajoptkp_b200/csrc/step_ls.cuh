@@ -1,0 +1,128 @@
+// Exact line search of the Newton constraint solver (MuJoCo PrimalSearch) as a warp-uniform state machine.
+// Included by step_dyn.cuh after primal_eval.
+#pragma once
+
+namespace tk {
+
+// Same evaluation sequence as the sequential algorithm (one Newton step from 0, one-sided Newton iterations until the
+// derivative changes sign, then bracketing with the midpoint and the two Newton candidates).  Every trip of the
+// warp-uniform loop performs at most ONE cost evaluation per world, so the worlds that share a warp run their
+// evaluations together although they sit in different phases of the search.  `run` = this world takes part.
+enum { LS_P0 = 0, LS_P1, LS_ONESIDED, LS_P1NEXT, LS_MID, LS_UB1, LS_UB2, LS_DONE };
+
+template <int G>
+TK_DEV double primal_search(const DM& m, WS& w, const Grp<G>& g, double gauss, double tolerance, bool run) {
+  int nv = m.nv;
+  int state = LS_DONE;
+  double result = 0.0, gtol = 0.0;
+  double qg[3] = {0.0, 0.0, 0.0};
+  if (run) {
+    double sn = 0.0;
+    for (int i = g.gl; i < nv; i += G) sn += w.search[i] * w.search[i];
+    double snorm = sqrt(g.sum(sn));
+    if (!(snorm < kMinVal)) {
+      double scale = 1.0 / (m.meaninertia * (double)max(1, nv));
+      gtol = tolerance * m.ls_tolerance * snorm / scale;
+      mul_M(m, w, w.Mv, w.search, g);
+      for (int r = g.gl; r < w.nefc; r += G) {
+        double s = 0.0;
+        for (int i = 0; i < nv; i++) s += w.J[r * nv + i] * w.search[i];
+        w.jv[r] = s;
+        double DJ0 = w.efc_D[r] * w.jar[r];
+        w.quad[3 * r] = 0.5 * w.jar[r] * DJ0;
+        w.quad[3 * r + 1] = s * DJ0;
+        w.quad[3 * r + 2] = 0.5 * s * w.efc_D[r] * s;
+      }
+      g.sync();
+      double a = 0.0, b = 0.0, c = 0.0;
+      for (int i = g.gl; i < nv; i += G) {
+        a += w.search[i] * w.Ma[i];
+        b += w.frc_smooth[i] * w.search[i];
+        c += w.search[i] * w.Mv[i];
+      }
+      qg[0] = gauss; qg[1] = g.sum(a) - g.sum(b); qg[2] = 0.5 * g.sum(c);
+      state = LS_P0;
+    }
+  }
+  const int LS = m.ls_iterations;
+  int lsiter = 0, p2update = 0, b2 = 0;
+  double dir = 0.0, a_eval = 0.0;
+  Pnt p0 = {0, 0, 0, 0}, p1 = p0, p2 = p0, p1next = p0, p2next = p0;
+  while (g.any_warp(state != LS_DONE)) {
+    if (state == LS_DONE) continue;
+    Pnt pe = primal_eval(w, g, qg, a_eval, lsiter);
+    enum { C_NONE = 0, C_ONESIDED, C_AFTER, C_BRACKET, C_FINAL };
+    int ctl = C_NONE;
+    if (state == LS_P0) {
+      p0 = pe;
+      a_eval = p0.alpha - p0.d0 / p0.d1;
+      state = LS_P1;
+    } else if (state == LS_P1) {
+      p1 = pe;
+      if (p0.cost < p1.cost) p1 = p0;
+      if (fabs(p1.d0) < gtol) { result = p1.alpha; state = LS_DONE; }
+      else { dir = (p1.d0 < 0.0) ? 1.0 : -1.0; p2update = 0; p2 = p1; ctl = C_ONESIDED; }
+    } else if (state == LS_ONESIDED) {
+      p1 = pe;
+      if (fabs(p1.d0) < gtol) { result = p1.alpha; state = LS_DONE; }
+      else ctl = C_ONESIDED;
+    } else if (state == LS_P1NEXT) {
+      p1next = pe;
+      ctl = C_BRACKET;
+    } else if (state == LS_MID) {
+      Pnt cand[3] = {p1next, p2next, pe};
+      double bestcost = 0.0;
+      int bestind = -1;
+      for (int i = 0; i < 3; i++)
+        if (fabs(cand[i].d0) < gtol && (bestind == -1 || cand[i].cost < bestcost)) { bestcost = cand[i].cost; bestind = i; }
+      if (bestind >= 0) { result = cand[bestind].alpha; state = LS_DONE; }
+      else {
+        int b1 = 0;
+        b2 = 0;
+        for (int i = 0; i < 3; i++) {
+          if (p1.d0 < 0.0 && cand[i].d0 < 0.0 && p1.d0 < cand[i].d0) { p1 = cand[i]; b1 = 1; }
+          else if (p1.d0 > 0.0 && cand[i].d0 > 0.0 && p1.d0 > cand[i].d0) { p1 = cand[i]; b1 = 2; }
+        }
+        for (int i = 0; i < 3; i++) {
+          if (p2.d0 < 0.0 && cand[i].d0 < 0.0 && p2.d0 < cand[i].d0) { p2 = cand[i]; b2 = 1; }
+          else if (p2.d0 > 0.0 && cand[i].d0 > 0.0 && p2.d0 > cand[i].d0) { p2 = cand[i]; b2 = 2; }
+        }
+        if (b1) { a_eval = p1.alpha - p1.d0 / p1.d1; state = LS_UB1; }
+        else if (b2) { a_eval = p2.alpha - p2.d0 / p2.d1; state = LS_UB2; }
+        else { result = pe.alpha; state = LS_DONE; }
+      }
+    } else if (state == LS_UB1) {
+      p1next = pe;
+      if (b2) { a_eval = p2.alpha - p2.d0 / p2.d1; state = LS_UB2; }
+      else ctl = C_BRACKET;
+    } else {  // LS_UB2
+      p2next = pe;
+      ctl = C_BRACKET;
+    }
+    if (ctl == C_ONESIDED) {
+      if (p1.d0 * dir <= -gtol && lsiter < LS) {
+        p2 = p1;
+        p2update = 1;
+        a_eval = p1.alpha - p1.d0 / p1.d1;
+        state = LS_ONESIDED;
+      } else ctl = C_AFTER;
+    }
+    if (ctl == C_AFTER) {
+      if (lsiter >= LS || !p2update) { result = p1.alpha; state = LS_DONE; }
+      else { p2next = p1; a_eval = p1.alpha - p1.d0 / p1.d1; state = LS_P1NEXT; }
+    }
+    if (ctl == C_BRACKET) {
+      if (lsiter < LS) { a_eval = 0.5 * (p1.alpha + p2.alpha); state = LS_MID; }
+      else ctl = C_FINAL;
+    }
+    if (ctl == C_FINAL) {
+      if (p1.cost <= p2.cost && p1.cost < p0.cost) result = p1.alpha;
+      else if (p2.cost <= p1.cost && p2.cost < p0.cost) result = p2.alpha;
+      else result = 0.0;
+      state = LS_DONE;
+    }
+  }
+  return result;
+}
+
+}  // namespace tk

@@ -33,102 +33,144 @@ struct FdArgs {
   int iterations;
   double tolerance;
   int ecap, pass;                   // constraint-row capacity of this pass; pass 1 redoes overflowed worlds only
+  int *list0, *list1;               // compacted world lists (gidx = row index * W + slot): all running / overflowed
+  int* counts;                      // [0] |list0|, [1] |list1|, [2] cursor of pass 0, [3] cursor of pass 1
 };
 
+// which perturbation a world slot carries: kind 0 nominal, 1 control, 2 velocity, 3 position
+struct FdWorld {
+  int row, slot, b, t, kind, col, sgn;
+};
+
+// decode world `gidx` (= row index * W + slot) and decide whether it is simulated at all
+__device__ inline bool fd_decode(const DM& dm, const FdArgs& a, long long gidx, FdWorld& wd) {
+  int rowi = (int)(gidx / a.W);
+  wd.slot = (int)(gidx - (long long)rowi * a.W);
+  wd.row = a.rows ? a.rows[rowi] : rowi;
+  wd.b = wd.row / a.T; wd.t = wd.row - wd.b * a.T;
+  wd.kind = 0; wd.col = 0; wd.sgn = 0;
+  unsigned long long mask = a.mask[wd.row];
+  if (mask == 0ull) return false;
+  if (wd.slot > 0) {
+    int q = wd.slot - 1;
+    if (q < 2 * a.m) { wd.kind = 1; wd.col = q >> 1; wd.sgn = q & 1; }
+    else if (q < 2 * a.m + 2 * a.n) { q -= 2 * a.m; wd.kind = 2; wd.col = q >> 1; wd.sgn = q & 1; }
+    else { q -= 2 * a.m + 2 * a.n; wd.kind = 3; wd.col = q >> 1; wd.sgn = q & 1; }
+    if (!((mask >> wd.col) & 1ull)) return false;
+  }
+  // control perturbations are clamp-aware (Differentiator.cpp:98-102,136-143); forward mode drops the minus
+  // side unless the plus side is infeasible
+  if (wd.kind == 1) {
+    const double* s = a.snap + ((size_t)wd.b * (a.T + 1) + wd.t) * a.SD;
+    double u = s[1 + dm.nq + 3 * dm.nv + a.ctrl_adr[wd.col]];
+    bool fwd_ok = !(u + a.eps > a.ctrl_limits[2 * wd.col + 1]);
+    bool back_wanted = a.central || !fwd_ok;
+    bool back_ok = back_wanted && !(u - a.eps < a.ctrl_limits[2 * wd.col]);
+    if ((wd.sgn == 0 && !fwd_ok) || (wd.sgn == 1 && !back_ok)) return false;
+  } else if (wd.kind >= 2 && wd.sgn == 1 && !a.central) {
+    return false;
+  }
+  return true;
+}
+
+// Work list of the launch: one thread per candidate world; the worlds that run are appended (warp-aggregated) to
+// list0, all others get status 0.  Sparse key-point rows leave most of the B*T*W candidates empty; compaction fills
+// every warp of k_fd_worlds with running worlds.
+__global__ void k_fd_plan(DM dm, FdArgs a) {
+  long long gidx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  long long total = (long long)a.nrows * a.W;
+  bool run = false;
+  FdWorld wd;
+  if (gidx < total) {
+    run = fd_decode(dm, a, gidx, wd);
+    if (!run) a.status[(size_t)wd.row * a.W + wd.slot] = 0;
+  }
+  unsigned bal = __ballot_sync(0xffffffffu, run);
+  int lane = threadIdx.x & 31;
+  int base = 0;
+  if (lane == 0 && bal) base = atomicAdd(&a.counts[0], __popc(bal));
+  base = __shfl_sync(0xffffffffu, base, 0);
+  if (run) a.list0[base + __popc(bal & ((1u << lane) - 1u))] = (int)gidx;
+}
+
+// Persistent kernel: every warp fetches GPW worlds at a time from the compacted list (dynamic cursor), one group of
+// G lanes per world.  pass 0 reads list0 and appends the worlds that overflow the fast constraint-row capacity to
+// list1; pass 1 re-runs list1 with ecap = maxefc.
 template <int G>
 __global__ void k_fd_worlds(DM dm, FdArgs a, int wsd) {
   extern __shared__ double smem[];
   constexpr int GPW = 32 / G;
   tk::Grp<G> g;
   int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  long long gidx = ((long long)blockIdx.x * (blockDim.x >> 5) + warp) * GPW + lane / G;
   int slot_s = warp * GPW + lane / G;
-  long long total = (long long)a.nrows * a.W;
-  // decide whether this group simulates a world; the decision is balloted over the full warp so that the running
-  // groups know each other (Grp::wmask) before any of them returns
+  const int* list = a.pass == 0 ? a.list0 : a.list1;
+  const int count = a.counts[a.pass];
+  int* cursor = &a.counts[2 + a.pass];
   int nq = dm.nq, nv = dm.nv;
-  bool run = gidx < total, clear_status = false;
-  int rowi = 0, slot = 0, row = 0, b = 0, t = 0, kind = 0, col = 0, sgn = 0;
-  int* st_out = nullptr;
-  const double* s = nullptr;
-  if (run) {
-    rowi = (int)(gidx / a.W); slot = (int)(gidx - (long long)rowi * a.W);
-    row = a.rows ? a.rows[rowi] : rowi;
-    b = row / a.T; t = row - b * a.T;
-    unsigned long long mask = a.mask[row];
-    st_out = a.status + (size_t)row * a.W + slot;
-    s = a.snap + ((size_t)b * (a.T + 1) + t) * a.SD;
-    if (a.pass == 1) {
-      run = (*st_out & tk::ST_OVERFLOW) != 0;
-    } else if (mask == 0ull) {
-      run = false; clear_status = true;
-    }
-    if (run && slot > 0) {
-      int q = slot - 1;
-      if (q < 2 * a.m) { kind = 1; col = q >> 1; sgn = q & 1; }
-      else if (q < 2 * a.m + 2 * a.n) { q -= 2 * a.m; kind = 2; col = q >> 1; sgn = q & 1; }
-      else { q -= 2 * a.m + 2 * a.n; kind = 3; col = q >> 1; sgn = q & 1; }
-      if (!((mask >> col) & 1ull)) { run = false; clear_status = true; }
-    }
-    // control perturbations are clamp-aware (Differentiator.cpp:98-102,136-143); forward mode drops the minus
-    // side unless the plus side is infeasible
-    if (run && kind == 1) {
-      double u = s[1 + nq + 3 * nv + a.ctrl_adr[col]];
-      bool fwd_ok = !(u + a.eps > a.ctrl_limits[2 * col + 1]);
-      bool back_wanted = a.central || !fwd_ok;
-      bool back_ok = back_wanted && !(u - a.eps < a.ctrl_limits[2 * col]);
-      if ((sgn == 0 && !fwd_ok) || (sgn == 1 && !back_ok)) { run = false; clear_status = true; }
-    } else if (run && kind >= 2 && sgn == 1 && !a.central) {
-      run = false; clear_status = true;
-    }
-  }
-  unsigned wm = __ballot_sync(0xffffffffu, run);
-  if (!run) { if (clear_status && g.gl == 0) *st_out = 0; return; }
-  g.wmask = wm;
   tk::WS w;
   tk::ws_init(w, smem + (size_t)slot_s * wsd, dm, a.ecap);
-  double time = s[0];
-  for (int i = g.gl; i < nq; i += G) w.qpos[i] = s[1 + i];
-  for (int i = g.gl; i < nv; i += G) {
-    w.qvel[i] = s[1 + nq + i];
-    w.qacc[i] = s[1 + nq + nv + i];
-    w.warm[i] = s[1 + nq + 2 * nv + i];
-  }
-  for (int i = g.gl; i < dm.nu; i += G) w.ctrl[i] = s[1 + nq + 3 * nv + i];
-  g.sync();
-  if (g.gl == 0 && kind != 0) {
-    double e = sgn ? -a.eps : a.eps;
-    if (kind == 1) {
-      w.ctrl[a.ctrl_adr[col]] += e;
-    } else if (kind == 2) {
-      w.qvel[a.dof_adr[col]] += e;
-    } else {
-      // mj_integratePos(qpos, e_dof, +-eps)
-      int d = a.dof_adr[col];
-      int j = dm.dof_jntid[d];
-      int pa = dm.jnt_qposadr[j], va = dm.jnt_dofadr[j];
-      if (dm.jnt_type[j] == tk::JNT_FREE) {
-        int kk = d - va;
-        if (kk < 3) w.qpos[pa + kk] += e * 1.0;
-        else {
-          double vel[3] = {0.0, 0.0, 0.0};
-          vel[kk - 3] = 1.0;
-          tk::quat_integrate(&w.qpos[pa + 3], vel, e);
-        }
-      } else {
-        w.qpos[pa] += e * 1.0;
+  for (;;) {
+    int base = 0;
+    if (lane == 0) base = atomicAdd(cursor, GPW);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (base >= count) break;
+    int li = base + lane / G;
+    bool run = li < count;
+    g.wmask = __ballot_sync(0xffffffffu, run);
+    if (run) {
+      long long gidx = list[li];
+      FdWorld wd;
+      fd_decode(dm, a, gidx, wd);
+      const double* s = a.snap + ((size_t)wd.b * (a.T + 1) + wd.t) * a.SD;
+      double time = s[0];
+      for (int i = g.gl; i < nq; i += G) w.qpos[i] = s[1 + i];
+      for (int i = g.gl; i < nv; i += G) {
+        w.qvel[i] = s[1 + nq + i];
+        w.qacc[i] = s[1 + nq + nv + i];
+        w.warm[i] = s[1 + nq + 2 * nv + i];
       }
+      for (int i = g.gl; i < dm.nu; i += G) w.ctrl[i] = s[1 + nq + 3 * nv + i];
+      g.sync();
+      if (g.gl == 0 && wd.kind != 0) {
+        double e = wd.sgn ? -a.eps : a.eps;
+        if (wd.kind == 1) {
+          w.ctrl[a.ctrl_adr[wd.col]] += e;
+        } else if (wd.kind == 2) {
+          w.qvel[a.dof_adr[wd.col]] += e;
+        } else {
+          // mj_integratePos(qpos, e_dof, +-eps)
+          int d = a.dof_adr[wd.col];
+          int j = dm.dof_jntid[d];
+          int pa = dm.jnt_qposadr[j], va = dm.jnt_dofadr[j];
+          if (dm.jnt_type[j] == tk::JNT_FREE) {
+            int kk = d - va;
+            if (kk < 3) w.qpos[pa + kk] += e * 1.0;
+            else {
+              double vel[3] = {0.0, 0.0, 0.0};
+              vel[kk - 3] = 1.0;
+              tk::quat_integrate(&w.qpos[pa + 3], vel, e);
+            }
+          } else {
+            w.qpos[pa] += e * 1.0;
+          }
+        }
+      }
+      g.sync();
+      int st = 0;
+      tk::step<G>(dm, w, g, a.iterations, a.tolerance, time, st);
+      double* o = a.fd_out + ((size_t)wd.row * a.W + wd.slot) * (nq + nv);
+      for (int i = g.gl; i < nq; i += G) o[i] = w.qpos[i];
+      for (int i = g.gl; i < nv; i += G) o[nq + i] = w.qvel[i];
+      int bits = 0;
+      for (int k = 0; k < 6; k++) if (g.any((st >> k) & 1)) bits |= (1 << k);
+      if (g.gl == 0) {
+        a.status[(size_t)wd.row * a.W + wd.slot] = bits | (1 << 30);
+        if (a.pass == 0 && (bits & tk::ST_OVERFLOW)) a.list1[atomicAdd(&a.counts[1], 1)] = (int)gidx;
+      }
+      g.sync();
     }
+    __syncwarp();
   }
-  g.sync();
-  int st = 0;
-  tk::step<G>(dm, w, g, a.iterations, a.tolerance, time, st);
-  double* o = a.fd_out + ((size_t)row * a.W + slot) * (nq + nv);
-  for (int i = g.gl; i < nq; i += G) o[i] = w.qpos[i];
-  for (int i = g.gl; i < nv; i += G) o[nq + i] = w.qvel[i];
-  int bits = 0;
-  for (int k = 0; k < 6; k++) if (g.any((st >> k) & 1)) bits |= (1 << k);
-  if (g.gl == 0) *st_out = bits | (1 << 30);
 }
 
 // (q2 - q1)/h on the configuration manifold for one dof (mj_differentiatePos restricted to a dof)
@@ -195,17 +237,26 @@ int launch_fd(tokp_traj* tr, const unsigned long long* mask, const int* rows, in
   int G = tr->G;
   long long worlds = (long long)nrows * tr->W;
   if (worlds < 1) return TOKP_OK;
+  if (worlds >= (1ll << 31)) { set_error("too many FD worlds for one launch"); return TOKP_ERR_ARG; }
   if (tr->fd_timed) {  // fold the previous launch's duration into the running sum before reusing the events
     double tmp[3];
     tokp_fd_kernel_ms(tr, tmp);
   }
+  a.list0 = tr->fd_list0; a.list1 = tr->fd_list1; a.counts = tr->fd_counts;
+  a.ecap = 0; a.pass = 0;
+  TOKP_CUDA(cudaMemsetAsync(tr->fd_counts, 0, 4 * sizeof(int), tr->stream));
+  k_fd_plan<<<(int)((worlds + 255) / 256), 256, 0, tr->stream>>>(dm, a);
+  g_launches++;
+  tr->counters[2] += 1;
   cudaEventRecord(tr->ev2, tr->stream);
   for (int pass = 0; pass < (needs_redo_pass(dm) ? 2 : 1); pass++) {
     LaunchPlan lp;
     int rc = plan_launch(dm, G, pass, &lp);
     if (rc) return rc;
     a.ecap = lp.ecap; a.pass = pass;
-    int blocks = (int)((worlds + lp.worlds_per_block - 1) / lp.worlds_per_block);
+    // persistent grid: as many blocks as stay resident, never more than the worlds need
+    long long need = (worlds + lp.worlds_per_block - 1) / lp.worlds_per_block;
+    int blocks = (int)(need < (long long)lp.resident_blocks ? need : (long long)lp.resident_blocks);
 #define LAUNCH(GG)                                                                                               \
   TOKP_CUDA(cudaFuncSetAttribute(k_fd_worlds<GG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lp.smem));   \
   k_fd_worlds<GG><<<blocks, lp.warps * 32, lp.smem, tr->stream>>>(dm, a, lp.wsd);

@@ -57,6 +57,19 @@ int plan_launch(const DM& dm, int G, int pass, LaunchPlan* out) {
   if (const char* e = getenv("TOKP_WARPS")) { int v = atoi(e); if (v > 0 && per_world * v * p.gpw <= sm_bytes) best = v; }
   if (best == 0) { set_error("model too large for the shared-memory workspace"); return TOKP_ERR_UNSUPPORTED; }
   p.warps = best; p.worlds_per_block = best * p.gpw; p.smem = per_world * best * p.gpw;
+  {
+    static int sm_count = 0;
+    if (!sm_count) {
+      int dev = 0;
+      cudaGetDevice(&dev);
+      if (cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sm_count <= 0) sm_count = 148;
+    }
+    int resident = (int)(sm_bytes / (p.smem + block_overhead));
+    if (resident > 32) resident = 32;
+    if (resident * best > 16) resident = 16 / best;  // 128-register kernels: 16 warps per SM
+    if (resident < 1) resident = 1;
+    p.resident_blocks = resident * sm_count;
+  }
   *out = p;
   return TOKP_OK;
 }

@@ -74,6 +74,9 @@ extern "C" int tokp_traj_create(const tokp_model* m, const tokp_task_desc* td, i
   size_t o_lam = p.take((size_t)B, 8);
   size_t o_ok = p.take((size_t)B, 4);
   size_t o_rflags = p.take((size_t)B * NA, 4);
+  size_t o_l0 = p.take((size_t)B * T * tr->W, 4);
+  size_t o_l1 = p.take((size_t)B * T * tr->W, 4);
+  size_t o_cnt = p.take(4, 4);
   size_t o_s0 = p.take((size_t)B * tr->SD, 8);
   size_t o_u0 = p.take((size_t)B * T * mm, 8);
   size_t o_tints = p.take((size_t)(2 * n + mm), 4);
@@ -94,6 +97,7 @@ extern "C" int tokp_traj_create(const tokp_model* m, const tokp_task_desc* td, i
   tr->cost = (double*)(base + o_cost); tr->deltaJ = (double*)(base + o_dJ); tr->lambda_d = (double*)(base + o_lam);
   tr->bp_ok = (int*)(base + o_ok);
   tr->roll_flags = (int*)(base + o_rflags);
+  tr->fd_list0 = (int*)(base + o_l0); tr->fd_list1 = (int*)(base + o_l1); tr->fd_counts = (int*)(base + o_cnt);
   tr->snap0_in = (double*)(base + o_s0); tr->U0_in = (double*)(base + o_u0);
   tr->task_ints = (int*)(base + o_tints); tr->task_reals = (double*)(base + o_treals);
   // task tables

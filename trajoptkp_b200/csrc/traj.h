@@ -33,6 +33,7 @@ int lanes_for_model(const DM& dm);
 // (TOKP_EFC_CAP, default min(maxefc, 32)); pass 1 = redo pass with ecap = maxefc for the worlds that overflowed.
 struct LaunchPlan {
   int G, gpw, ecap, wsd, warps, worlds_per_block;
+  int resident_blocks;  // blocks of this shape that stay resident on the whole device (persistent-grid size)
   size_t smem;
 };
 int fast_ecap(const DM& dm);
@@ -76,6 +77,8 @@ struct tokp_traj {
   double *cost, *deltaJ, *lambda_d;  // [B]
   double *snap0_in, *U0_in;          // resident copies of the last host inputs of tokp_optimise ([B][SD], [B][T][m])
   int* bp_ok;         // [B]
+  int *fd_list0, *fd_list1;  // [B*T*W] compacted FD world lists
+  int* fd_counts;     // [4]
   int* roll_flags;    // [B][NA] rollout worlds that overflowed the fast constraint-row capacity
   int* task_ints;     // qpos_adr | dof_adr | ctrl_adr
   double* task_reals;

@@ -260,7 +260,7 @@ int launch_fd(tokp_traj* tr, const unsigned long long* mask, const int* rows, in
 #define LAUNCH(GG)                                                                                               \
   TOKP_CUDA(cudaFuncSetAttribute(k_fd_worlds<GG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lp.smem));   \
   k_fd_worlds<GG><<<blocks, lp.warps * 32, lp.smem, tr->stream>>>(dm, a, lp.wsd);
-    if (G == 8) { LAUNCH(8) } else if (G == 16) { LAUNCH(16) } else { LAUNCH(32) }
+    if (G == 4) { LAUNCH(4) } else if (G == 8) { LAUNCH(8) } else if (G == 16) { LAUNCH(16) } else { LAUNCH(32) }
 #undef LAUNCH
     g_launches++;
     tr->counters[2] += 1;

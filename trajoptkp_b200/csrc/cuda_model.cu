@@ -22,7 +22,7 @@ void device_model_free(DeviceModel* dm) {
 int lanes_for_model(const DM& dm) {
   if (const char* e = getenv("TOKP_LANES")) {  // tuning override (8 / 16 / 32)
     int v = atoi(e);
-    if (v == 8 || v == 16 || v == 32) return v;
+    if (v == 4 || v == 8 || v == 16 || v == 32) return v;
   }
   int k = dm.nv > dm.nbody ? dm.nv : dm.nbody;
   if (k <= 10) return 8;
@@ -41,6 +41,9 @@ int plan_launch(const DM& dm, int G, int pass, LaunchPlan* out) {
   p.G = G; p.gpw = 32 / G;
   p.ecap = pass == 0 ? fast_ecap(dm) : dm.maxefc;
   p.wsd = tk::ws_doubles(dm, p.ecap);
+  // the groups of a warp access their workspaces at the same offsets: a stride of 64 B (mod 128 B) between consecutive
+  // workspaces spreads a unit-stride fp64 access of the whole warp over all 32 banks (2 wavefronts, the minimum)
+  if (p.gpw > 1) while (p.wsd % 16 != 8) p.wsd++;
   size_t per_world = (size_t)p.wsd * 8;
   const size_t sm_bytes = 227 * 1024, block_overhead = 1024;
   // warps per block: the choice that keeps the most worlds resident per SM (ties -> larger blocks)
@@ -66,7 +69,7 @@ int plan_launch(const DM& dm, int G, int pass, LaunchPlan* out) {
     }
     int resident = (int)(sm_bytes / (p.smem + block_overhead));
     if (resident > 32) resident = 32;
-    if (resident * best > 16) resident = 16 / best;  // 128-register kernels: 16 warps per SM
+    if (resident * best > 8) resident = 8 / best;  // <= 255-register kernels: 8 warps per SM
     if (resident < 1) resident = 1;
     p.resident_blocks = resident * sm_count;
   }
@@ -222,7 +225,7 @@ extern "C" int tokp_step_worlds(const tokp_model* m, const double* snapshots_in,
   TOKP_CUDA(cudaFuncSetAttribute(k_step_worlds<GG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lp.smem));      \
   k_step_worlds<GG><<<blocks, lp.warps * 32, lp.smem>>>(dm, d_in, d_out, d_st, count, nsteps, iters, tol, S, lp.wsd, \
                                                         lp.ecap, pass);
-    if (G == 8) { LAUNCH(8) } else if (G == 16) { LAUNCH(16) } else { LAUNCH(32) }
+    if (G == 4) { LAUNCH(4) } else if (G == 8) { LAUNCH(8) } else if (G == 16) { LAUNCH(16) } else { LAUNCH(32) }
 #undef LAUNCH
     g_launches++;
   }

@@ -156,7 +156,7 @@ int launch_rollout(tokp_traj* tr, int mode, const double* d_Uin, const double* d
 #define LAUNCH(GG)                                                                                              \
   TOKP_CUDA(cudaFuncSetAttribute(k_rollout<GG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lp.smem));    \
   k_rollout<GG><<<blocks, warps * 32, lp.smem, tr->stream>>>(dm, a, lp.wsd);
-    if (G == 8) { LAUNCH(8) } else if (G == 16) { LAUNCH(16) } else { LAUNCH(32) }
+    if (G == 4) { LAUNCH(4) } else if (G == 8) { LAUNCH(8) } else if (G == 16) { LAUNCH(16) } else { LAUNCH(32) }
 #undef LAUNCH
     g_launches++;
   }

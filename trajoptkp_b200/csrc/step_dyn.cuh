@@ -159,6 +159,50 @@ TK_DEV Pnt primal_eval(const WS& w, const Grp<G>& g, const double qg[3], double 
   return p;
 }
 
+// Lower-triangle entries of an nv x nv matrix owned by one lane (entry idx = lane + k*G, row-major over the triangle):
+// used by the Hessian assembly and the Cholesky trailing update when nv(nv+1)/2 <= TRI_MAX*G.
+constexpr int TRI_MAX = 8;
+template <int G>
+struct TriMap {
+  int cnt;             // entries of this lane
+  int ei[TRI_MAX], ej[TRI_MAX];
+  TK_DEV void init(int nv, int gl) {
+    int ntri = nv * (nv + 1) / 2;
+    cnt = 0;
+#pragma unroll
+    for (int k = 0; k < TRI_MAX; k++) {
+      int idx = gl + k * G;
+      ei[k] = 0; ej[k] = 0;
+      if (idx < ntri) {
+        int i = (int)((sqrt(8.0 * (double)idx + 1.0) - 1.0) * 0.5);
+        while (i * (i + 1) / 2 > idx) i--;
+        while ((i + 1) * (i + 2) / 2 <= idx) i++;
+        ei[k] = i; ej[k] = idx - i * (i + 1) / 2;
+        cnt = k + 1;
+      }
+    }
+  }
+};
+
+// same factorisation as chol_factor with the trailing update driven by the lane's triangle entries (no integer
+// division, no wasted upper-triangle iterations); identical arithmetic per entry
+template <int G>
+TK_DEV void chol_factor_tri(double* H, int n, const Grp<G>& g, const TriMap<G>& tm) {
+  for (int j = 0; j < n; j++) {
+    double d = H[j * n + j];
+    if (d < kMinVal) d = kMinVal;
+    d = sqrt(d);
+    double inv = 1.0 / d;
+    g.sync();
+    for (int i = j + g.gl; i < n; i += G) H[i * n + j] = (i == j) ? d : H[i * n + j] * inv;
+    g.sync();
+#pragma unroll
+    for (int k = 0; k < TRI_MAX; k++)
+      if (k < tm.cnt && tm.ej[k] > j) H[tm.ei[k] * n + tm.ej[k]] -= H[tm.ei[k] * n + j] * H[tm.ej[k] * n + j];
+    g.sync();
+  }
+}
+
 // in-place dense Cholesky (lower) of the nv x nv matrix in w.H, right-looking, lanes over the trailing block
 template <int G>
 TK_DEV void chol_factor(double* H, int n, const Grp<G>& g) {
@@ -211,6 +255,10 @@ TK_DEV void fwd_constraint(const DM& m, WS& w, const Grp<G>& g, int iterations, 
   int nv = m.nv, nefc = w.nefc;
   const bool has = nefc > 0;
   double cost = 0.0, gauss = 0.0;
+  const bool tri = nv * (nv + 1) / 2 <= TRI_MAX * G;
+  TriMap<G> tm;
+  tm.cnt = 0;
+  if (tri && has) tm.init(nv, g.gl);
   auto update = [&]() {
     // forces, cost, qfrc_constraint, gradient, Hessian, Newton direction
     double c = 0.0;
@@ -231,16 +279,36 @@ TK_DEV void fwd_constraint(const DM& m, WS& w, const Grp<G>& g, int iterations, 
     }
     gauss = 0.5 * g.sum(gsum);
     cost = c + gauss;
-    for (int e = g.gl; e < nv * nv; e += G) {
-      int i = e / nv, j = e - i * nv;
-      if (j > i) continue;
-      double h = w.M[e];
-      for (int r = 0; r < nefc; r++)
-        if (w.efc_force[r] != 0.0) h += w.efc_D[r] * w.J[r * nv + i] * w.J[r * nv + j];
-      w.H[e] = h;
+    if (tri) {
+      // rows outermost, the lane's triangle entries in registers: inactive rows cost one broadcast load
+      double h[TRI_MAX];
+#pragma unroll
+      for (int k = 0; k < TRI_MAX; k++) h[k] = k < tm.cnt ? w.M[tm.ei[k] * nv + tm.ej[k]] : 0.0;
+      for (int r = 0; r < nefc; r++) {
+        if (w.efc_force[r] == 0.0) continue;
+        double D = w.efc_D[r];
+        const double* Jr = &w.J[r * nv];
+#pragma unroll
+        for (int k = 0; k < TRI_MAX; k++)
+          if (k < tm.cnt) h[k] += D * Jr[tm.ei[k]] * Jr[tm.ej[k]];
+      }
+#pragma unroll
+      for (int k = 0; k < TRI_MAX; k++)
+        if (k < tm.cnt) w.H[tm.ei[k] * nv + tm.ej[k]] = h[k];
+      g.sync();
+      chol_factor_tri(w.H, nv, g, tm);
+    } else {
+      for (int e = g.gl; e < nv * nv; e += G) {
+        int i = e / nv, j = e - i * nv;
+        if (j > i) continue;
+        double h = w.M[e];
+        for (int r = 0; r < nefc; r++)
+          if (w.efc_force[r] != 0.0) h += w.efc_D[r] * w.J[r * nv + i] * w.J[r * nv + j];
+        w.H[e] = h;
+      }
+      g.sync();
+      chol_factor(w.H, nv, g);
     }
-    g.sync();
-    chol_factor(w.H, nv, g);
     chol_solve(w.H, nv, w.Mgrad, w.grad, g);
     for (int i = g.gl; i < nv; i += G) w.search[i] = -w.Mgrad[i];
     g.sync();

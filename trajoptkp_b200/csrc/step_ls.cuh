@@ -10,12 +10,42 @@ namespace tk {
 // evaluations together although they sit in different phases of the search.  `run` = this world takes part.
 enum { LS_P0 = 0, LS_P1, LS_ONESIDED, LS_P1NEXT, LS_MID, LS_UB1, LS_UB2, LS_DONE };
 
+// Rows of the search that one lane keeps in registers (row r = lane + k*G): with nefc <= LS_ROWS*G every cost
+// evaluation runs without touching shared memory.  Same per-row terms and the same lane-local summation order as
+// primal_eval, so both paths return identical values.
+constexpr int LS_ROWS = 4;
+
+template <int G>
+TK_DEV Pnt primal_eval_reg(const Grp<G>& g, const double qg[3], double alpha, int& lsiter, const double (&rj)[LS_ROWS],
+                           const double (&rv)[LS_ROWS], const double (&r0)[LS_ROWS], const double (&r1)[LS_ROWS],
+                           const double (&r2)[LS_ROWS]) {
+  lsiter++;
+  double q0 = 0.0, q1 = 0.0, q2 = 0.0;
+#pragma unroll
+  for (int k = 0; k < LS_ROWS; k++) {
+    double x = rj[k] + alpha * rv[k];
+    if (x < 0.0) { q0 += r0[k]; q1 += r1[k]; q2 += r2[k]; }
+  }
+  q0 = g.sum(q0) + qg[0]; q1 = g.sum(q1) + qg[1]; q2 = g.sum(q2) + qg[2];
+  Pnt p;
+  p.alpha = alpha;
+  p.cost = alpha * alpha * q2 + alpha * q1 + q0;
+  p.d0 = 2.0 * alpha * q2 + q1;
+  p.d1 = 2.0 * q2;
+  if (p.d1 <= 0.0) p.d1 = kMinVal;
+  return p;
+}
+
 template <int G>
 TK_DEV double primal_search(const DM& m, WS& w, const Grp<G>& g, double gauss, double tolerance, bool run) {
   int nv = m.nv;
   int state = LS_DONE;
   double result = 0.0, gtol = 0.0;
   double qg[3] = {0.0, 0.0, 0.0};
+  const bool regpath = w.nefc <= LS_ROWS * G;
+  double rj[LS_ROWS], rv[LS_ROWS], r0[LS_ROWS], r1[LS_ROWS], r2[LS_ROWS];
+#pragma unroll
+  for (int k = 0; k < LS_ROWS; k++) { rj[k] = 1.0; rv[k] = 0.0; r0[k] = 0.0; r1[k] = 0.0; r2[k] = 0.0; }
   if (run) {
     double sn = 0.0;
     for (int i = g.gl; i < nv; i += G) sn += w.search[i] * w.search[i];
@@ -24,14 +54,32 @@ TK_DEV double primal_search(const DM& m, WS& w, const Grp<G>& g, double gauss, d
       double scale = 1.0 / (m.meaninertia * (double)max(1, nv));
       gtol = tolerance * m.ls_tolerance * snorm / scale;
       mul_M(m, w, w.Mv, w.search, g);
-      for (int r = g.gl; r < w.nefc; r += G) {
-        double s = 0.0;
-        for (int i = 0; i < nv; i++) s += w.J[r * nv + i] * w.search[i];
-        w.jv[r] = s;
-        double DJ0 = w.efc_D[r] * w.jar[r];
-        w.quad[3 * r] = 0.5 * w.jar[r] * DJ0;
-        w.quad[3 * r + 1] = s * DJ0;
-        w.quad[3 * r + 2] = 0.5 * s * w.efc_D[r] * s;
+      if (regpath) {
+#pragma unroll
+        for (int k = 0; k < LS_ROWS; k++) {
+          int r = g.gl + k * G;
+          if (r < w.nefc) {
+            double s = 0.0;
+            for (int i = 0; i < nv; i++) s += w.J[r * nv + i] * w.search[i];
+            w.jv[r] = s;
+            double jr = w.jar[r], D = w.efc_D[r];
+            double DJ0 = D * jr;
+            rj[k] = jr; rv[k] = s;
+            r0[k] = 0.5 * jr * DJ0;
+            r1[k] = s * DJ0;
+            r2[k] = 0.5 * s * D * s;
+          }
+        }
+      } else {
+        for (int r = g.gl; r < w.nefc; r += G) {
+          double s = 0.0;
+          for (int i = 0; i < nv; i++) s += w.J[r * nv + i] * w.search[i];
+          w.jv[r] = s;
+          double DJ0 = w.efc_D[r] * w.jar[r];
+          w.quad[3 * r] = 0.5 * w.jar[r] * DJ0;
+          w.quad[3 * r + 1] = s * DJ0;
+          w.quad[3 * r + 2] = 0.5 * s * w.efc_D[r] * s;
+        }
       }
       g.sync();
       double a = 0.0, b = 0.0, c = 0.0;
@@ -50,7 +98,7 @@ TK_DEV double primal_search(const DM& m, WS& w, const Grp<G>& g, double gauss, d
   Pnt p0 = {0, 0, 0, 0}, p1 = p0, p2 = p0, p1next = p0, p2next = p0;
   while (g.any_warp(state != LS_DONE)) {
     if (state == LS_DONE) continue;
-    Pnt pe = primal_eval(w, g, qg, a_eval, lsiter);
+    Pnt pe = regpath ? primal_eval_reg(g, qg, a_eval, lsiter, rj, rv, r0, r1, r2) : primal_eval(w, g, qg, a_eval, lsiter);
     enum { C_NONE = 0, C_ONESIDED, C_AFTER, C_BRACKET, C_FINAL };
     int ctl = C_NONE;
     if (state == LS_P0) {

@@ -1,0 +1,94 @@
+// Driver for the C++ host mirror: runs the reference's call sequence (main.cpp:100-165 wiring, then
+// RolloutTrajectory -> GenerateKeyPoints -> DynamicsDerivatives -> InterpolateDerivatives -> Optimise) on the acrobot
+// task through the shim classes and prints one JSON object that tests/test_gpu_shim.py compares with the ctypes path
+// and the oracle.  usage: shim_test <acrobot.xml> [--no-gpu]
+#include <cmath>
+#include <cstdio>
+
+#include "tokp_shim_optimiser.h"
+
+static void print_vec(const char* name, const std::vector<double>& v, bool last = false) {
+  std::printf("\"%s\": [", name);
+  for (size_t i = 0; i < v.size(); i++) std::printf("%s%.17g", i ? ", " : "", v[i]);
+  std::printf("]%s\n", last ? "" : ",");
+}
+
+int main(int argc, char** argv) {
+  if (argc < 2) { std::fprintf(stderr, "usage: shim_test model.xml [--no-gpu]\n"); return 2; }
+  bool no_gpu = argc > 2 && std::string(argv[2]) == "--no-gpu";
+  const int T = 50;
+  try {
+    auto helper = std::make_shared<MuJoCoHelper>();
+    helper->InitSimulator(0.01, argv[1]);
+    keypoint_method kp;
+    kp.name = "set_interval"; kp.min_N = 5; kp.max_N = 50;
+    kp.jerk_thresholds = {0.1, 0.1}; kp.velocity_change_thresholds = {6.0, 6.0};
+    auto mt = std::make_shared<ModelTranslator>();
+    // TaskConfigs/toys/acrobot.yaml: joints shoulder, elbow; actuator shoulder; residual weights / terminal weights
+    mt->InitModelTranslator(helper, TOKP_TASK_ACROBOT, {"shoulder", "elbow"}, {"shoulder"},
+                            {0.0, 0.0, 0.0, 0.0, 0.0}, {0.0, 0.0, 0.001, 0.001, 100.0}, {100.0, 100.0, 1.0, 1.0, 100.0}, kp);
+    std::printf("{\"dof\": %d, \"num_ctrl\": %d, \"nq\": %d, \"S\": %d,\n", mt->dof, mt->num_ctrl, helper->nq, helper->S);
+    if (no_gpu) {
+      // without a device the arena cannot be created: the error must surface, nothing falls back to the host
+      try {
+        TrajHandle th(mt, T);
+        std::printf("\"traj_create\": \"unexpected success\"}\n");
+        return 1;
+      } catch (const std::exception& e) {
+        std::printf("\"traj_create_error\": \"%s\"}\n", "raised");
+        return 0;
+      }
+    }
+    auto traj = std::make_shared<TrajHandle>(mt, T);
+    auto diff = std::make_shared<Differentiator>(mt, helper, traj);
+    iLQR opt(mt, helper, diff, T);
+    mjData start = *helper->master_reset_data;
+    helper->qpos(&start)[0] = 0.3;
+    helper->qpos(&start)[1] = -0.2;
+    std::vector<MatrixXd> U0(T, MatrixXd(1, 1));
+    for (int t = 0; t < T; t++) U0[t](0, 0) = 0.2 * std::sin(0.3 * t);
+    double cost = opt.RolloutTrajectory(&start, true, U0);
+    std::printf("\"rollout_cost\": %.17g,\n", cost);
+    opt.keypoint_generator->GenerateKeyPoints(opt.X_old, opt.A, opt.B);
+    std::vector<double> rows;
+    for (int t = 0; t < T; t++) rows.push_back((double)opt.keypoint_generator->keypoints[t].size());
+    print_vec("keypoint_counts", rows);
+    print_vec("percentages", opt.keypoint_generator->last_percentages);
+    opt.GenerateDerivatives();
+    // per-call drop-in at key-point t = 5 must reproduce the batched result
+    MatrixXd A5(4, 4), B5(4, 1);
+    diff->DynamicsDerivatives(A5, B5, {0, 1}, 5, 0, true, 1e-6);
+    double dmax = 0;
+    for (int i = 0; i < 4; i++) {
+      for (int j = 0; j < 4; j++) dmax = std::fmax(dmax, std::fabs(A5(i, j) - opt.A[5](i, j)));
+      dmax = std::fmax(dmax, std::fabs(B5(i, 0) - opt.B[5](i, 0)));
+    }
+    std::printf("\"cols_vs_batched_maxabs\": %.3g,\n", dmax);
+    std::vector<double> a5(A5.data(), A5.data() + 16);
+    print_vec("A5", a5);
+    // Keypoints_Test.cpp:272-289: A[1] == A[0] + (A[3]-A[0])/3 after interpolation with key-points {0, 3, ...}
+    std::vector<std::vector<int>> kps(T);
+    for (int t = 0; t < T; t++) if (t % 3 == 0 || t == T - 1) kps[t] = {0, 1};
+    std::vector<MatrixXd> A2 = opt.A, B2 = opt.B;
+    std::vector<std::vector<MatrixXd>> rx, ru;
+    opt.keypoint_generator->InterpolateDerivatives(kps, T, A2, B2, rx, ru, false, 1);
+    int exact = 1;
+    for (int i = 0; i < 4; i++)
+      for (int j = 0; j < 4; j++) {
+        double add = (opt.A[3](i, j) - opt.A[0](i, j)) / 3;
+        if (A2[1](i, j) != opt.A[0](i, j) + 1 * add || A2[2](i, j) != opt.A[0](i, j) + 2 * add) exact = 0;
+      }
+    std::printf("\"interpolation_identity_exact\": %d,\n", exact);
+    opt.lambda = 0.1;
+    auto Uopt = opt.Optimise(&start, U0, 3, 1, T);
+    std::vector<double> uo;
+    for (auto& u : Uopt) uo.push_back(u(0, 0));
+    print_vec("U_opt", uo);
+    std::printf("\"initial_cost\": %.17g, \"final_cost\": %.17g, \"iterations\": %d, \"cost_reduction\": %.17g}\n",
+                opt.initial_cost, opt.new_cost, opt.num_iterations, opt.cost_reduction);
+  } catch (const std::exception& e) {
+    std::fprintf(stderr, "shim_test: %s\n", e.what());
+    return 1;
+  }
+  return 0;
+}

@@ -1,0 +1,180 @@
+// Second half of the host mirror (see tokp_shim.h): ModelTranslator index maps, Differentiator, KeypointGenerator,
+// Optimiser / iLQR.  Every method body is marshalling + C-ABI calls; no arithmetic of the path runs on the host.
+#pragma once
+#include "tokp_shim.h"
+
+// ---- ModelTranslator: state-vector <-> qpos/qvel maps and the task description ---------------------------------
+// (InitModelTranslator ModelTranslator.cpp:18-96; ComputeStateDofAdrIndices :1548-1610; ReturnStateVector :882)
+class ModelTranslator {
+ public:
+  // joint / actuator names in YAML order (robots[].jointNames / actuatorNames), residual terms flattened with
+  // resid_dimension replication (FileHandler.cpp:276-287)
+  void InitModelTranslator(std::shared_ptr<MuJoCoHelper> helper, int task_kind, const std::vector<std::string>& joints,
+                           const std::vector<std::string>& actuators, const std::vector<double>& target,
+                           const std::vector<double>& weight, const std::vector<double>& weight_terminal,
+                           const keypoint_method& kp) {
+    MuJoCo_helper = helper;
+    kind = task_kind;
+    std::vector<int> jq(helper->nq + 64), jd(helper->nv + 64);
+    int nj = tokp_model_get_int(helper->model, "jnt_qposadr", jq.data(), (int)jq.size());
+    tokp_model_get_int(helper->model, "jnt_dofadr", jd.data(), (int)jd.size());
+    for (const auto& n : joints) {
+      int id = helper->JointId(n);
+      if (id < 0 || id >= nj) throw std::runtime_error("joint not in model: " + n);
+      qpos_adr.push_back(jq[id]);
+      state_dof_adr_indices.push_back(jd[id]);
+    }
+    for (const auto& n : actuators) {
+      int id = helper->ActuatorId(n);
+      if (id < 0) throw std::runtime_error("actuator not in model: " + n);
+      ctrl_adr.push_back(id);
+    }
+    dof = (int)joints.size(); num_ctrl = (int)actuators.size();
+    resid_target = target; resid_weight = weight; resid_weight_terminal = weight_terminal;
+    current_kp = kp;
+    if ((int)current_kp.jerk_thresholds.size() != dof) current_kp.jerk_thresholds.assign(dof, 0.0);
+    if ((int)current_kp.velocity_change_thresholds.size() != dof) current_kp.velocity_change_thresholds.assign(dof, 0.0);
+  }
+  tokp_task_desc Desc() const {
+    tokp_task_desc d;
+    d.kind = kind; d.n = dof; d.m = num_ctrl;
+    d.qpos_adr = qpos_adr.data(); d.dof_adr = state_dof_adr_indices.data(); d.ctrl_adr = ctrl_adr.data();
+    d.num_resid = (int)resid_target.size();
+    d.resid_target = resid_target.data(); d.resid_weight = resid_weight.data();
+    d.resid_weight_terminal = resid_weight_terminal.data();
+    d.kp_method = tokp_kp_code(current_kp.name); d.min_N = current_kp.min_N; d.max_N = current_kp.max_N;
+    d.jerk_thresholds = current_kp.jerk_thresholds.data();
+    d.velchange_thresholds = current_kp.velocity_change_thresholds.data();
+    d.iterative_error_threshold = current_kp.iterative_error_threshold;
+    return d;
+  }
+  // ReturnStateVector (ModelTranslator.cpp:882-897): [pos(n); vel(n)]
+  MatrixXd ReturnStateVector(mjData* d) const {
+    MatrixXd x(2 * dof, 1);
+    for (int i = 0; i < dof; i++) {
+      x(i, 0) = MuJoCo_helper->qpos(d)[qpos_adr[i]];
+      x(i + dof, 0) = MuJoCo_helper->qvel(d)[state_dof_adr_indices[i]];
+    }
+    return x;
+  }
+  // StateIndexToQposIndex returns a DoF address despite its name (ModelTranslator.cpp:1707)
+  int StateIndexToQposIndex(int state_index) const { return state_dof_adr_indices[state_index]; }
+  MatrixXd ReturnControlVector(mjData* d) const {
+    MatrixXd u(num_ctrl, 1);
+    for (int i = 0; i < num_ctrl; i++) u(i, 0) = MuJoCo_helper->ctrl(d)[ctrl_adr[i]];
+    return u;
+  }
+
+  std::shared_ptr<MuJoCoHelper> MuJoCo_helper;
+  int kind = 0, dof = 0, num_ctrl = 0;
+  std::vector<int> qpos_adr, state_dof_adr_indices, ctrl_adr;
+  std::vector<double> resid_target, resid_weight, resid_weight_terminal;
+  keypoint_method current_kp;
+};
+
+// Device arena shared by Differentiator / KeypointGenerator / Optimiser of one problem (replaces the per-thread
+// fd_data[] scratch and the T+1 saved mjData allocations, MuJoCoHelper.cpp:696-703,918-921)
+struct TrajHandle {
+  TrajHandle(std::shared_ptr<ModelTranslator> mt, int horizon, int batch = 1) : T(horizon), B(batch), mt_(mt) {
+    tokp_task_desc d = mt->Desc();
+    tokp_shim::check(tokp_traj_create(mt->MuJoCo_helper->model, &d, horizon, batch, &h), "tokp_traj_create");
+  }
+  ~TrajHandle() { if (h) tokp_traj_destroy(h); }
+  TrajHandle(const TrajHandle&) = delete;
+  tokp_traj* h = nullptr;
+  int T, B;
+  std::shared_ptr<ModelTranslator> mt_;
+};
+
+// ---- Differentiator (include/Differentiator.h:15-37) -------------------------------------------------------------
+class Differentiator {
+ public:
+  Differentiator(std::shared_ptr<ModelTranslator> model_translator, std::shared_ptr<MuJoCoHelper> MuJoCo_helper,
+                 std::shared_ptr<TrajHandle> traj)
+      : model_translator(model_translator), MuJoCo_helper(MuJoCo_helper), traj(traj) {}
+  // Differentiator::DynamicsDerivatives (Differentiator.cpp:8-462): writes columns {c, c+n} of A and {c | c<m} of B
+  // for c in cols at saved_systems_state_list[data_index]; thread_id is accepted and ignored (no per-thread scratch).
+  void DynamicsDerivatives(MatrixXd& A, MatrixXd& B, const std::vector<int>& cols, int data_index, int /*thread_id*/,
+                           bool central_diff, double eps) {
+    // the saved state of this index is pushed first, exactly what the reference reads (Differentiator.cpp:62-66)
+    const auto& s = MuJoCo_helper->saved_systems_state_list.at(data_index)->v;
+    tokp_shim::check(tokp_traj_set_snapshot(traj->h, 0, data_index, s.data()), "set_snapshot");
+    tokp_shim::check(tokp_dynamics_derivs_cols(traj->h, 0, data_index, cols.data(), (int)cols.size(), central_diff ? 1 : 0,
+                                               eps, A.data(), A.rows(), B.data(), B.rows()), "DynamicsDerivatives");
+  }
+  std::shared_ptr<ModelTranslator> model_translator;
+  std::shared_ptr<MuJoCoHelper> MuJoCo_helper;
+  std::shared_ptr<TrajHandle> traj;
+};
+
+// ---- KeypointGenerator (include/KeyPointGenerator.h:56-110) ------------------------------------------------------
+class KeypointGenerator {
+ public:
+  KeypointGenerator(std::shared_ptr<Differentiator> differentiator, std::shared_ptr<MuJoCoHelper> /*helper*/, int _dof,
+                    int _horizon)
+      : dof(_dof), horizon(_horizon), differentiator_(differentiator) {
+    last_percentages.assign(dof, 0.0);
+  }
+  void SetKeypointMethod(keypoint_method m) {
+    method_ = m;
+    tokp_shim::check(tokp_traj_set_keypoint_method(differentiator_->traj->h, tokp_kp_code(m.name), m.min_N, m.max_N,
+                                                   m.jerk_thresholds.empty() ? nullptr : m.jerk_thresholds.data(),
+                                                   m.velocity_change_thresholds.empty() ? nullptr : m.velocity_change_thresholds.data(),
+                                                   m.iterative_error_threshold), "SetKeypointMethod");
+  }
+  keypoint_method ReturnCurrentKeypointMethod() { return method_; }
+  void ResetCache() {}  // computed_keypoints cache lives on the device and is rebuilt per call
+  // GenerateKeyPoints (KeyPointGenerator.cpp:76-135): trajectory_states are X_old[0..T]; A, B are only touched by
+  // iterative_error (filled at the key-points it evaluates)
+  void GenerateKeyPoints(const std::vector<MatrixXd>& trajectory_states, std::vector<MatrixXd>& A, std::vector<MatrixXd>& B) {
+    tokp_traj* h = differentiator_->traj->h;
+    int nx = 2 * dof;
+    std::vector<double> X((size_t)(horizon + 1) * nx, 0.0);
+    for (size_t t = 0; t < trajectory_states.size() && t <= (size_t)horizon; t++)
+      std::memcpy(&X[t * nx], trajectory_states[t].data(), sizeof(double) * nx);
+    tokp_shim::check(tokp_traj_set(h, 0, "X_old", X.data(), (int)X.size()), "set X_old");
+    std::vector<int> counts(horizon), idx((size_t)horizon * 2 * dof);
+    tokp_shim::check(tokp_keypoints(h, counts.data(), idx.data(), last_percentages.data()), "GenerateKeyPoints");
+    keypoints.assign(horizon, {});
+    for (int t = 0; t < horizon; t++) keypoints[t].assign(&idx[(size_t)t * 2 * dof], &idx[(size_t)t * 2 * dof] + counts[t]);
+    if (method_.name == "iterative_error") PullAB(A, B);
+  }
+  // InterpolateDerivatives (KeyPointGenerator.cpp:840-954) on caller-owned A/B and an arbitrary key-point table
+  void InterpolateDerivatives(const std::vector<std::vector<int>>& keyPoints, int T, std::vector<MatrixXd>& A,
+                              std::vector<MatrixXd>& B, std::vector<std::vector<MatrixXd>>& /*r_x*/,
+                              std::vector<std::vector<MatrixXd>>& /*r_u*/, bool /*residual_derivs*/, int num_ctrl) {
+    tokp_traj* h = differentiator_->traj->h;
+    int nx = 2 * dof;
+    std::vector<int> counts(T), idx;
+    for (int t = 0; t < T; t++) { counts[t] = (int)keyPoints[t].size(); idx.insert(idx.end(), keyPoints[t].begin(), keyPoints[t].end()); }
+    idx.push_back(0);
+    tokp_shim::check(tokp_traj_set_keypoints(h, 0, counts.data(), idx.data()), "set_keypoints");
+    std::vector<double> a((size_t)T * nx * nx), b((size_t)T * nx * num_ctrl);
+    for (int t = 0; t < T; t++) {
+      std::memcpy(&a[(size_t)t * nx * nx], A[t].data(), sizeof(double) * nx * nx);
+      if (num_ctrl) std::memcpy(&b[(size_t)t * nx * num_ctrl], B[t].data(), sizeof(double) * nx * num_ctrl);
+    }
+    tokp_shim::check(tokp_traj_set(h, 0, "A", a.data(), (int)a.size()), "set A");
+    if (num_ctrl) tokp_shim::check(tokp_traj_set(h, 0, "B", b.data(), (int)b.size()), "set B");
+    tokp_shim::check(tokp_interpolate(h), "InterpolateDerivatives");
+    PullAB(A, B);
+  }
+  void PullAB(std::vector<MatrixXd>& A, std::vector<MatrixXd>& B) {
+    tokp_traj* h = differentiator_->traj->h;
+    int nx = 2 * dof, T = horizon, m = B.empty() ? 0 : B[0].cols();
+    std::vector<double> a((size_t)T * nx * nx), b((size_t)T * nx * (m ? m : 1));
+    tokp_traj_get(h, 0, "A", a.data(), (int)a.size());
+    if (m) tokp_traj_get(h, 0, "B", b.data(), (int)b.size());
+    for (int t = 0; t < T && t < (int)A.size(); t++) {
+      std::memcpy(A[t].data(), &a[(size_t)t * nx * nx], sizeof(double) * nx * nx);
+      if (m) std::memcpy(B[t].data(), &b[(size_t)t * nx * m], sizeof(double) * nx * m);
+    }
+  }
+  int dof, horizon;
+  std::vector<std::vector<int>> keypoints;
+  std::vector<double> last_percentages;
+
+ private:
+  std::shared_ptr<Differentiator> differentiator_;
+  keypoint_method method_;
+};

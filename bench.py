@@ -177,6 +177,12 @@ def main():
     from trajoptkp_b200 import capi
     tc, snaps, targets, U = workload(args, rank, world)
     B, T = args.batch, args.horizon
+    # e2e inputs live in pinned host memory (the C ABI takes plain host pointers; pinning is the caller's choice)
+    pin_s = torch.empty(snaps.shape, dtype=torch.float64, pin_memory=True)
+    pin_u = torch.empty(U.shape, dtype=torch.float64, pin_memory=True)
+    pin_s.numpy()[...] = snaps
+    pin_u.numpy()[...] = U
+    snaps, U = pin_s.numpy(), pin_u.numpy()
     tr = capi.Traj(tc, T, B)
     for b in range(B):
         tr.set_targets(b, targets[b])
@@ -272,8 +278,15 @@ def main():
     bytes_per_jac = 8 * SD + 8 * tr.nx * (tr.nx + tr.m)
     if fpj and fd_ms > 0:
         ach = fpj * jac_per_launch / (fd_ms * 1e-3) / 1e12
+        traffic = None
+        try:  # dram bytes per launch of k_fd_worlds from the committed ncu --set full capture of this workload
+            tj = json.load(open(os.path.join(ROOT, "profiles", "fd_traffic.json")))
+            if tj.get("task") == args.task and tj.get("batch") == B and tj.get("horizon") == T and tj.get("kp") == args.kp:
+                traffic = tj["dram_bytes_per_launch"]
+        except Exception:
+            pass
         line["roofline"] = {"bound": "fp64", "achieved": ach, "peak": peaks["fp64_tflops"], "unit": "TFLOP/s",
-                            "frac": ach / peaks["fp64_tflops"], "traffic": None,
+                            "frac": ach / peaks["fp64_tflops"], "traffic": traffic,
                             "peak_source": "measured live (DFMA loop, tokp_measure_peaks); MEASURED_PEAKS.json has no FP64 figure",
                             "flops_per_jacobian": fpj,
                             "hbm": {"achieved_gbs": bytes_per_jac * jac_per_launch / (fd_ms * 1e-3) / 1e9,

@@ -262,6 +262,7 @@ def main():
                     "ms_per_step": 1e3 * dt_e / args.steps},
             "gpu_launches": int(l1 - l0), "clocks": sampler.summary(),
             "fd_kernel": {"name": "k_fd_worlds", "avg_ms": fd_ms, "launches": int(fd_launches),
+                          "worlds_last": int(tr.counters()[0]), "worlds_rerun_full_capacity_last": int(tr.counters()[3]),
                           "share_of_step": fd_ms * fd_launches / (1e3 * dt) if dt > 0 else None}}
     cpu = None
     if not args.no_cpu_baseline:

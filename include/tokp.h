@@ -143,7 +143,7 @@ int tokp_optimise(tokp_traj* tr, const double* snapshot0, const double* U_init, 
  * returns count, -count if cap too small, -1e6 unknown */
 int tokp_traj_get(tokp_traj* tr, int b, const char* name, double* out, int cap);
 int tokp_traj_set(tokp_traj* tr, int b, const char* name, const double* in, int count);
-/* counters of the last tokp_dynamics_derivs: [worlds, jacobians_x1e6, kernel_launches, 0] */
+/* counters of the last tokp_dynamics_derivs: [worlds, jacobians_x1e6, kernel_launches, worlds re-run with full row capacity] */
 int tokp_traj_counters(tokp_traj* tr, int64_t out[4]);
 /* CUDA-event time of the last derivative / backward / forward phase, ms (time_get_derivs_ms etc., iLQR.cpp:418-505) */
 int tokp_timers(tokp_traj* tr, double ms[3]);

@@ -96,11 +96,11 @@ __global__ void k_fd_plan(DM dm, FdArgs a) {
 // Persistent kernel: every warp fetches GPW worlds at a time from the compacted list (dynamic cursor), one group of
 // G lanes per world.  pass 0 reads list0 and appends the worlds that overflow the fast constraint-row capacity to
 // list1; pass 1 re-runs list1 with ecap = maxefc.
-template <int G>
+template <int G, int NV>
 __global__ void k_fd_worlds(DM dm, FdArgs a, int wsd) {
   extern __shared__ double smem[];
   constexpr int GPW = 32 / G;
-  tk::Grp<G> g;
+  tk::Grp<G, NV> g;
   int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   int slot_s = warp * GPW + lane / G;
   const int* list = a.pass == 0 ? a.list0 : a.list1;
@@ -157,7 +157,7 @@ __global__ void k_fd_worlds(DM dm, FdArgs a, int wsd) {
       }
       g.sync();
       int st = 0;
-      tk::step<G>(dm, w, g, a.iterations, a.tolerance, time, st);
+      tk::step(dm, w, g, a.iterations, a.tolerance, time, st);
       double* o = a.fd_out + ((size_t)wd.row * a.W + wd.slot) * (nq + nv);
       for (int i = g.gl; i < nq; i += G) o[i] = w.qpos[i];
       for (int i = g.gl; i < nv; i += G) o[nq + i] = w.qvel[i];
@@ -257,10 +257,10 @@ int launch_fd(tokp_traj* tr, const unsigned long long* mask, const int* rows, in
     // persistent grid: as many blocks as stay resident, never more than the worlds need
     long long need = (worlds + lp.worlds_per_block - 1) / lp.worlds_per_block;
     int blocks = (int)(need < (long long)lp.resident_blocks ? need : (long long)lp.resident_blocks);
-#define LAUNCH(GG)                                                                                               \
-  TOKP_CUDA(cudaFuncSetAttribute(k_fd_worlds<GG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lp.smem));   \
-  k_fd_worlds<GG><<<blocks, lp.warps * 32, lp.smem, tr->stream>>>(dm, a, lp.wsd);
-    if (G == 4) { LAUNCH(4) } else if (G == 8) { LAUNCH(8) } else if (G == 16) { LAUNCH(16) } else { LAUNCH(32) }
+#define LAUNCH(GG, NN)                                                                                               \
+  TOKP_CUDA(cudaFuncSetAttribute(k_fd_worlds<GG, NN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lp.smem));   \
+  k_fd_worlds<GG, NN><<<blocks, lp.warps * 32, lp.smem, tr->stream>>>(dm, a, lp.wsd);
+    TOKP_DISPATCH(G, dm.nv, LAUNCH)
 #undef LAUNCH
     g_launches++;
     tr->counters[2] += 1;
@@ -279,6 +279,8 @@ int launch_fd(tokp_traj* tr, const unsigned long long* mask, const int* rows, in
 int update_fd_counters(tokp_traj* tr) {
   std::vector<unsigned long long> hm((size_t)tr->B * tr->T);
   TOKP_CUDA(cudaMemcpyAsync(hm.data(), tr->kp_mask, hm.size() * 8, cudaMemcpyDeviceToHost, tr->stream));
+  int hc[4] = {0, 0, 0, 0};
+  TOKP_CUDA(cudaMemcpyAsync(hc, tr->fd_counts, sizeof(hc), cudaMemcpyDeviceToHost, tr->stream));
   TOKP_CUDA(cudaStreamSynchronize(tr->stream));
   long long worlds = 0, cols = 0;
   for (auto mk : hm) {
@@ -289,6 +291,7 @@ int update_fd_counters(tokp_traj* tr) {
     cols += c;
   }
   tr->counters[0] = worlds;
+  tr->counters[3] = hc[1];  // worlds that overflowed the fast constraint-row capacity and were re-run
   tr->counters[1] = (int64_t)((double)cols / tr->n * 1e6);
   return TOKP_OK;
 }

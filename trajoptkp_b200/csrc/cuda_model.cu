@@ -142,12 +142,12 @@ int ensure_device_model(const tokp_model* mc, const DM** out) {
 
 // ---- tokp_step_worlds ---------------------------------------------------------------------------
 // in/out: host-layout snapshots [count][S] already on the device
-template <int G>
+template <int G, int NV>
 __global__ void k_step_worlds(DM dm, const double* __restrict__ in, double* __restrict__ out, int* __restrict__ status,
                               int count, int nsteps, int iterations, double tolerance, int S, int wsd, int ecap, int pass) {
   extern __shared__ double smem[];
   constexpr int GPW = 32 / G;  // groups per warp
-  tk::Grp<G> g;
+  tk::Grp<G, NV> g;
   int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   int gidx = (blockIdx.x * (blockDim.x >> 5) + warp) * GPW + lane / G;  // world index
   int slot = warp * GPW + lane / G;
@@ -170,7 +170,7 @@ __global__ void k_step_worlds(DM dm, const double* __restrict__ in, double* __re
   for (int i = g.gl; i < dm.nu; i += G) w.ctrl[i] = s[S - dm.nu + i];
   g.sync();
   int st = 0;
-  for (int k = 0; k < nsteps; k++) tk::step<G>(dm, w, g, iterations, tolerance, time, st);
+  for (int k = 0; k < nsteps; k++) tk::step(dm, w, g, iterations, tolerance, time, st);
   double* o = out + (size_t)gidx * S;
   for (int i = g.gl; i < S; i += G) o[i] = 0.0;
   g.sync();
@@ -221,11 +221,11 @@ extern "C" int tokp_step_worlds(const tokp_model* m, const double* snapshots_in,
     rc = plan_launch(dm, G, pass, &lp);
     if (rc) { cudaFree(d_in); cudaFree(d_out); cudaFree(d_st); return rc; }
     int blocks = (count + lp.worlds_per_block - 1) / lp.worlds_per_block;
-#define LAUNCH(GG)                                                                                                    \
-  TOKP_CUDA(cudaFuncSetAttribute(k_step_worlds<GG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lp.smem));      \
-  k_step_worlds<GG><<<blocks, lp.warps * 32, lp.smem>>>(dm, d_in, d_out, d_st, count, nsteps, iters, tol, S, lp.wsd, \
+#define LAUNCH(GG, NN)                                                                                                    \
+  TOKP_CUDA(cudaFuncSetAttribute(k_step_worlds<GG, NN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lp.smem));      \
+  k_step_worlds<GG, NN><<<blocks, lp.warps * 32, lp.smem>>>(dm, d_in, d_out, d_st, count, nsteps, iters, tol, S, lp.wsd, \
                                                         lp.ecap, pass);
-    if (G == 4) { LAUNCH(4) } else if (G == 8) { LAUNCH(8) } else if (G == 16) { LAUNCH(16) } else { LAUNCH(32) }
+    TOKP_DISPATCH(G, dm.nv, LAUNCH)
 #undef LAUNCH
     g_launches++;
   }

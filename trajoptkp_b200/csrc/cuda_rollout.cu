@@ -28,10 +28,10 @@ struct RollArgs {
   int spread;          // 1: one world per warp (first group only) - latency layout for small batches
 };
 
-template <int G>
+template <int G, int NV>
 __global__ void k_rollout(DM dm, RollArgs a, int wsd) {
   extern __shared__ double smem[];
-  tk::Grp<G> g;
+  tk::Grp<G, NV> g;
   int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   constexpr int GPW = 32 / G;
   int widx = a.spread ? blockIdx.x * (blockDim.x >> 5) + warp : (blockIdx.x * (blockDim.x >> 5) + warp) * GPW + lane / G;
@@ -99,7 +99,7 @@ __global__ void k_rollout(DM dm, RollArgs a, int wsd) {
         cost = __dadd_rn(cost, task_cost(tk_, r, t == T - 1));
       }
     }
-    tk::step<G>(dm, w, g, a.iterations, a.tolerance, time, st);
+    tk::step(dm, w, g, a.iterations, a.tolerance, time, st);
     if (a.mode == 0) {
       // residuals / cost after the step, X_old, U_old, saved[t+1] (iLQR.cpp:222-246)
       if (g.gl == 0) {
@@ -153,10 +153,10 @@ int launch_rollout(tokp_traj* tr, int mode, const double* d_Uin, const double* d
     int blocks = (nworlds + lp.worlds_per_block - 1) / lp.worlds_per_block;
     a.spread = nworlds <= 148 * 4;
     if (a.spread) { warps = 1; blocks = nworlds; lp.smem = (size_t)lp.wsd * 8; }
-#define LAUNCH(GG)                                                                                              \
-  TOKP_CUDA(cudaFuncSetAttribute(k_rollout<GG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lp.smem));    \
-  k_rollout<GG><<<blocks, warps * 32, lp.smem, tr->stream>>>(dm, a, lp.wsd);
-    if (G == 4) { LAUNCH(4) } else if (G == 8) { LAUNCH(8) } else if (G == 16) { LAUNCH(16) } else { LAUNCH(32) }
+#define LAUNCH(GG, NN)                                                                                              \
+  TOKP_CUDA(cudaFuncSetAttribute(k_rollout<GG, NN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lp.smem));    \
+  k_rollout<GG, NN><<<blocks, warps * 32, lp.smem, tr->stream>>>(dm, a, lp.wsd);
+    TOKP_DISPATCH(G, dm.nv, LAUNCH)
 #undef LAUNCH
     g_launches++;
   }

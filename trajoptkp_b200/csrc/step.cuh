@@ -27,8 +27,10 @@ enum { ROW_LIMIT = 0, ROW_FRICTIONLESS = 1, ROW_PYRAMIDAL = 2 };
 enum { ST_BAD_QPOS = 1, ST_BAD_QVEL = 2, ST_BAD_QACC = 4, ST_OVERFLOW = 8, ST_UNSUPPORTED = 32 };
 
 // ---- group of G lanes -----------------------------------------------------------------------------
-template <int G>
+template <int G, int NV = 0>
 struct Grp {
+  // NV > 0: the model's nv is this compile-time constant (loops unroll, index arithmetic folds); 0 = read m.nv
+  static constexpr int kNV = NV;
   unsigned mask;
   unsigned wmask;  // lanes of every group of this warp that runs a world (set by the kernel with a full-warp ballot)
   int gl;  // lane index inside the group
@@ -151,7 +153,7 @@ TK_DEV bool bad_value(double x) { return !(fabs(x) <= 1e10); }
 // ---- per-world workspace (shared memory) ---------------------------------------------------------
 // Layout = persistent part P, followed by a union region shared by two groups of arrays with disjoint lifetimes:
 //   A  position-stage temporaries (dead once make_constraint has produced J, D, B, kterm)
-//      xpos xquat xanchor xaxis | crb  U  (con_dist con_pos con_frame) | efc_pos efc_margin | int tables
+//      xpos xquat | (xanchor xaxis)  U  crb  U  (con_dist con_pos con_frame) | efc_pos efc_margin | int tables
 //   B  H | (cvel cacc cfrc cdof_dot : velocity stage)  U  (jar jv quad efc_force : solver)
 // Rotation matrices (xmat, ximat, geom_xmat) are not stored: they are rebuilt from xquat where needed with the same
 // operation sequence (quat2mat then mat_vec3), so results are bit-identical to the stored-matrix form.
@@ -182,7 +184,7 @@ __host__ __device__ inline int ws_doubles(const DM& m, int ecap) {
   int nb = m.nbody, nv = m.nv, ne = ecap, nc = m.maxcontact;
   int P = m.nq + 3 * nv + m.nu + 3 * nb + 3 * nb + 10 * nb + 6 * nv + 2 * nv * nv + 2 * nv + 12 * nv + ne * nv + 4 * ne;
   int ints = nc + 3 * ne + ws_imax(m.njnt, m.npair) + 4;
-  int A = 3 * nb + 4 * nb + 6 * m.njnt + ws_imax(10 * nb, 13 * nc) + 2 * ne + (ints + 1) / 2;
+  int A = 3 * nb + 4 * nb + ws_imax(ws_imax(6 * m.njnt, 10 * nb), 13 * nc) + 2 * ne + (ints + 1) / 2;
   int B = nv * nv + ws_imax(18 * nb + 6 * nv, 6 * ne);
   return P + ws_imax(A, B);
 }
@@ -201,11 +203,14 @@ TK_DEV void ws_init(WS& w, double* base, const DM& m, int ecap) {
   w.J = take(ne * nv); w.efc_D = take(ne); w.efc_aref = take(ne); w.efc_B = take(ne); w.efc_kterm = take(ne);
   double* u = p;
   // A
-  w.xpos = take(3 * nb); w.xquat = take(4 * nb); w.xanchor = take(3 * m.njnt); w.xaxis = take(3 * m.njnt);
+  w.xpos = take(3 * nb); w.xquat = take(4 * nb);
+  // three tenants of one slot, in program order: joint anchors/axes (kinematics -> com_pos), composite inertias
+  // (crb_factor), contacts (collision -> make_constraint)
   double* u2 = p;
+  w.xanchor = u2; w.xaxis = u2 + 3 * m.njnt;
   w.crb = u2;
   w.con_dist = u2; w.con_pos = u2 + nc; w.con_frame = u2 + 4 * nc;
-  p = u2 + ws_imax(10 * nb, 13 * nc);
+  p = u2 + ws_imax(ws_imax(6 * m.njnt, 10 * nb), 13 * nc);
   w.efc_pos = take(ne); w.efc_margin = take(ne);
   int* ip = reinterpret_cast<int*>(p);
   w.con_pair = ip; ip += nc;

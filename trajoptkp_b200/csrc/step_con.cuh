@@ -72,8 +72,8 @@ TK_DEV int plane_sphere(double margin, const double* ppos, const double* pmat, c
 }
 
 // mj_collision over the static pair list: lanes = pairs, fixed slots per pair, then ordered compaction
-template <int G>
-TK_DEV void collision(const DM& m, WS& w, const Grp<G>& g, int& status) {
+template <int G, int NV>
+TK_DEV void collision(const DM& m, WS& w, const Grp<G, NV>& g, int& status) {
   // slot offsets are the prefix of pair_slots: recomputed on the fly (npair is small)
   for (int p = g.gl; p < m.npair; p += G) {
     int g1 = m.pair_geom1[p], g2 = m.pair_geom2[p];
@@ -181,9 +181,9 @@ TK_DEV void make_kbip(const DM& m, const double* solref_in, const double* solimp
 }
 
 // mj_makeConstraint: row table (limits then contacts), Jacobian rows, regularisation
-template <int G>
-TK_DEV void make_constraint(const DM& m, WS& w, const Grp<G>& g, int& status) {
-  int nv = m.nv;
+template <int G, int NV>
+TK_DEV void make_constraint(const DM& m, WS& w, const Grp<G, NV>& g, int& status) {
+  const int nv = NV ? NV : m.nv;
   // 1. row table by one lane (ordered; counts are tiny)
   if (g.gl == 0) {
     int r = 0;
@@ -287,9 +287,9 @@ TK_DEV void make_constraint(const DM& m, WS& w, const Grp<G>& g, int& status) {
 }
 
 // mj_referenceConstraint: aref = -B (J qvel) - K imp (pos - margin)
-template <int G>
-TK_DEV void reference_constraint(const DM& m, WS& w, const Grp<G>& g) {
-  int nv = m.nv;
+template <int G, int NV>
+TK_DEV void reference_constraint(const DM& m, WS& w, const Grp<G, NV>& g) {
+  const int nv = NV ? NV : m.nv;
   for (int r = g.gl; r < w.nefc; r += G) {
     double vel = 0.0;
     for (int i = 0; i < nv; i++) vel += w.J[r * nv + i] * w.qvel[i];

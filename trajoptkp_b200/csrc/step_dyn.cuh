@@ -7,8 +7,8 @@
 namespace tk {
 
 // mj_comVel (level-synchronous)
-template <int G>
-TK_DEV void com_vel(const DM& m, WS& w, const Grp<G>& g) {
+template <int G, int NV>
+TK_DEV void com_vel(const DM& m, WS& w, const Grp<G, NV>& g) {
   if (g.gl == 0) for (int k = 0; k < 6; k++) w.cvel[k] = 0.0;
   g.sync();
   for (int depth = 1; depth <= m.treedepth; depth++) {
@@ -42,9 +42,9 @@ TK_DEV void com_vel(const DM& m, WS& w, const Grp<G>& g) {
 }
 
 // mj_passive (damping + gravity compensation) and mj_rne(flg_acc = 0)
-template <int G>
-TK_DEV void passive_and_bias(const DM& m, WS& w, const Grp<G>& g) {
-  int nv = m.nv;
+template <int G, int NV>
+TK_DEV void passive_and_bias(const DM& m, WS& w, const Grp<G, NV>& g) {
+  const int nv = NV ? NV : m.nv;
   for (int i = g.gl; i < nv; i += G) {
     double f = -m.dof_damping[i] * w.qvel[i];
     if (m.any_gravcomp) {
@@ -99,9 +99,9 @@ TK_DEV void passive_and_bias(const DM& m, WS& w, const Grp<G>& g) {
 }
 
 // mj_fwdActuation + mj_fwdAcceleration
-template <int G>
-TK_DEV void actuation_acceleration(const DM& m, WS& w, const Grp<G>& g) {
-  int nv = m.nv;
+template <int G, int NV>
+TK_DEV void actuation_acceleration(const DM& m, WS& w, const Grp<G, NV>& g) {
+  const int nv = NV ? NV : m.nv;
   for (int i = g.gl; i < nv; i += G) {
     double fa = 0.0;
     for (int a = 0; a < m.nu; a++) {
@@ -131,8 +131,8 @@ TK_DEV void actuation_acceleration(const DM& m, WS& w, const Grp<G>& g) {
 struct Pnt { double alpha, cost, d0, d1; };
 
 // cost of the active rows at jar (s(jar)); optionally writes forces
-template <int G>
-TK_DEV double constraint_cost(const WS& w, const double* jar, const Grp<G>& g) {
+template <int G, int NV>
+TK_DEV double constraint_cost(const WS& w, const double* jar, const Grp<G, NV>& g) {
   double c = 0.0;
   for (int r = g.gl; r < w.nefc; r += G) {
     double x = jar[r];
@@ -141,8 +141,8 @@ TK_DEV double constraint_cost(const WS& w, const double* jar, const Grp<G>& g) {
   return g.sum(c);
 }
 
-template <int G>
-TK_DEV Pnt primal_eval(const WS& w, const Grp<G>& g, const double qg[3], double alpha, int& lsiter) {
+template <int G, int NV>
+TK_DEV Pnt primal_eval(const WS& w, const Grp<G, NV>& g, const double qg[3], double alpha, int& lsiter) {
   lsiter++;
   double q0 = 0.0, q1 = 0.0, q2 = 0.0;
   for (int r = g.gl; r < w.nefc; r += G) {
@@ -162,7 +162,7 @@ TK_DEV Pnt primal_eval(const WS& w, const Grp<G>& g, const double qg[3], double 
 // Lower-triangle entries of an nv x nv matrix owned by one lane (entry idx = lane + k*G, row-major over the triangle):
 // used by the Hessian assembly and the Cholesky trailing update when nv(nv+1)/2 <= TRI_MAX*G.
 constexpr int TRI_MAX = 8;
-template <int G>
+template <int G, int NV>
 struct TriMap {
   int cnt;             // entries of this lane
   int ei[TRI_MAX], ej[TRI_MAX];
@@ -186,8 +186,8 @@ struct TriMap {
 
 // same factorisation as chol_factor with the trailing update driven by the lane's triangle entries (no integer
 // division, no wasted upper-triangle iterations); identical arithmetic per entry
-template <int G>
-TK_DEV void chol_factor_tri(double* H, int n, const Grp<G>& g, const TriMap<G>& tm) {
+template <int G, int NV>
+TK_DEV void chol_factor_tri(double* H, int n, const Grp<G, NV>& g, const TriMap<G, NV>& tm) {
   for (int j = 0; j < n; j++) {
     double d = H[j * n + j];
     if (d < kMinVal) d = kMinVal;
@@ -204,8 +204,8 @@ TK_DEV void chol_factor_tri(double* H, int n, const Grp<G>& g, const TriMap<G>& 
 }
 
 // in-place dense Cholesky (lower) of the nv x nv matrix in w.H, right-looking, lanes over the trailing block
-template <int G>
-TK_DEV void chol_factor(double* H, int n, const Grp<G>& g) {
+template <int G, int NV>
+TK_DEV void chol_factor(double* H, int n, const Grp<G, NV>& g) {
   for (int j = 0; j < n; j++) {
     double d = H[j * n + j];
     if (d < kMinVal) d = kMinVal;
@@ -224,8 +224,8 @@ TK_DEV void chol_factor(double* H, int n, const Grp<G>& g) {
 }
 
 // x = inv(L L') b  (column-oriented substitutions, lanes over the remaining rows)
-template <int G>
-TK_DEV void chol_solve(const double* L, int n, double* x, const double* b, const Grp<G>& g) {
+template <int G, int NV>
+TK_DEV void chol_solve(const double* L, int n, double* x, const double* b, const Grp<G, NV>& g) {
   for (int i = g.gl; i < n; i += G) x[i] = b[i];
   g.sync();
   for (int j = 0; j < n; j++) {
@@ -250,13 +250,13 @@ namespace tk {
 
 // mj_fwdConstraint with the Newton solver.  The Newton and line-search loops are warp-uniform (Grp::any_warp): every
 // running world of the warp passes through them together; worlds without constraints or already converged idle.
-template <int G>
-TK_DEV void fwd_constraint(const DM& m, WS& w, const Grp<G>& g, int iterations, double tolerance) {
-  int nv = m.nv, nefc = w.nefc;
+template <int G, int NV>
+TK_DEV void fwd_constraint(const DM& m, WS& w, const Grp<G, NV>& g, int iterations, double tolerance) {
+  const int nv = NV ? NV : m.nv, nefc = w.nefc;
   const bool has = nefc > 0;
   double cost = 0.0, gauss = 0.0;
   const bool tri = nv * (nv + 1) / 2 <= TRI_MAX * G;
-  TriMap<G> tm;
+  TriMap<G, NV> tm;
   tm.cnt = 0;
   if (tri && has) tm.init(nv, g.gl);
   auto update = [&]() {
@@ -379,9 +379,9 @@ TK_DEV void fwd_constraint(const DM& m, WS& w, const Grp<G>& g, int iterations, 
 }
 
 // mj_EulerSkip + mj_advance
-template <int G>
-TK_DEV void euler(const DM& m, WS& w, const Grp<G>& g, double& time) {
-  int nv = m.nv;
+template <int G, int NV>
+TK_DEV void euler(const DM& m, WS& w, const Grp<G, NV>& g, double& time) {
+  const int nv = NV ? NV : m.nv;
   double h = m.timestep;
   if (m.any_damping) {
     for (int e = g.gl; e < nv * nv; e += G) {
@@ -413,8 +413,8 @@ TK_DEV void euler(const DM& m, WS& w, const Grp<G>& g, double& time) {
 }
 
 // one full step (mj_step).  `iterations`/`tolerance`: solver options of this launch.
-template <int G>
-TK_DEV void step(const DM& m, WS& w, const Grp<G>& g, int iterations, double tolerance, double& time, int& status) {
+template <int G, int NV>
+TK_DEV void step(const DM& m, WS& w, const Grp<G, NV>& g, int iterations, double tolerance, double& time, int& status) {
   for (int i = g.gl; i < m.nq; i += G) if (bad_value(w.qpos[i])) status |= ST_BAD_QPOS;
   for (int i = g.gl; i < m.nv; i += G) if (bad_value(w.qvel[i])) status |= ST_BAD_QVEL;
   kinematics(m, w, g);

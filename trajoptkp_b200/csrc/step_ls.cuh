@@ -15,8 +15,8 @@ enum { LS_P0 = 0, LS_P1, LS_ONESIDED, LS_P1NEXT, LS_MID, LS_UB1, LS_UB2, LS_DONE
 // primal_eval, so both paths return identical values.
 constexpr int LS_ROWS = 4;
 
-template <int G>
-TK_DEV Pnt primal_eval_reg(const Grp<G>& g, const double qg[3], double alpha, int& lsiter, const double (&rj)[LS_ROWS],
+template <int G, int NV>
+TK_DEV Pnt primal_eval_reg(const Grp<G, NV>& g, const double qg[3], double alpha, int& lsiter, const double (&rj)[LS_ROWS],
                            const double (&rv)[LS_ROWS], const double (&r0)[LS_ROWS], const double (&r1)[LS_ROWS],
                            const double (&r2)[LS_ROWS]) {
   lsiter++;
@@ -36,9 +36,9 @@ TK_DEV Pnt primal_eval_reg(const Grp<G>& g, const double qg[3], double alpha, in
   return p;
 }
 
-template <int G>
-TK_DEV double primal_search(const DM& m, WS& w, const Grp<G>& g, double gauss, double tolerance, bool run) {
-  int nv = m.nv;
+template <int G, int NV>
+TK_DEV double primal_search(const DM& m, WS& w, const Grp<G, NV>& g, double gauss, double tolerance, bool run) {
+  const int nv = NV ? NV : m.nv;
   int state = LS_DONE;
   double result = 0.0, gtol = 0.0;
   double qg[3] = {0.0, 0.0, 0.0};

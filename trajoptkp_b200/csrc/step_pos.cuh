@@ -6,8 +6,8 @@
 namespace tk {
 
 // mj_kinematics: level-synchronous over the body tree (lanes = bodies of one depth)
-template <int G>
-TK_DEV void kinematics(const DM& m, WS& w, const Grp<G>& g) {
+template <int G, int NV>
+TK_DEV void kinematics(const DM& m, WS& w, const Grp<G, NV>& g) {
   if (g.gl == 0) {
     w.xpos[0] = w.xpos[1] = w.xpos[2] = 0.0;
     w.xquat[0] = 1.0; w.xquat[1] = w.xquat[2] = w.xquat[3] = 0.0;
@@ -85,8 +85,8 @@ TK_DEV void geom_pose(const DM& m, const WS& w, int gi, double* gpos_out, double
 }
 
 // mj_comPos: centre of mass of every kinematic tree (stored at its root body), com-frame inertias, motion axes
-template <int G>
-TK_DEV void com_pos(const DM& m, WS& w, const Grp<G>& g) {
+template <int G, int NV>
+TK_DEV void com_pos(const DM& m, WS& w, const Grp<G, NV>& g) {
   // subtree com of root bodies (children of the world): the only subtree_com entries the pipeline reads
   for (int b = 1 + g.gl; b < m.nbody; b += G) {
     if (m.body_parentid[b] != 0) continue;
@@ -160,9 +160,9 @@ TK_DEV void com_pos(const DM& m, WS& w, const Grp<G>& g) {
 }
 
 // mj_crb + dense M, then L'DL factor of M (mj_factorM)
-template <int G>
-TK_DEV void crb_factor(const DM& m, WS& w, const Grp<G>& g) {
-  int nv = m.nv;
+template <int G, int NV>
+TK_DEV void crb_factor(const DM& m, WS& w, const Grp<G, NV>& g) {
+  const int nv = NV ? NV : m.nv;
   for (int b = g.gl; b < m.nbody; b += G) {
     double acc[10];
     for (int k = 0; k < 10; k++) acc[k] = w.cinert[10 * b + k];
@@ -191,9 +191,9 @@ TK_DEV void crb_factor(const DM& m, WS& w, const Grp<G>& g) {
 }
 
 // L'DL factorisation (elimination from the last dof upwards, ancestors only): LD <- factor(A)
-template <int G>
-TK_DEV void factor_ldl(const DM& m, const double* A, double* LD, double* dinv, const Grp<G>& g) {
-  int nv = m.nv;
+template <int G, int NV>
+TK_DEV void factor_ldl(const DM& m, const double* A, double* LD, double* dinv, const Grp<G, NV>& g) {
+  const int nv = NV ? NV : m.nv;
   for (int e = g.gl; e < nv * nv; e += G) LD[e] = A[e];
   g.sync();
   for (int k = nv - 1; k >= 0; k--) {
@@ -215,9 +215,9 @@ TK_DEV void factor_ldl(const DM& m, const double* A, double* LD, double* dinv, c
 }
 
 // x <- inv(L'DL) x   (x in shared memory)
-template <int G>
-TK_DEV void solve_ldl(const DM& m, const double* LD, const double* dinv, double* x, const Grp<G>& g) {
-  int nv = m.nv;
+template <int G, int NV>
+TK_DEV void solve_ldl(const DM& m, const double* LD, const double* dinv, double* x, const Grp<G, NV>& g) {
+  const int nv = NV ? NV : m.nv;
   // x <- inv(L') x : once x[i] is final, push it to its ancestors
   for (int i = nv - 1; i > 0; i--) {
     double xi = x[i];
@@ -242,9 +242,9 @@ TK_DEV void solve_ldl(const DM& m, const double* LD, const double* dinv, double*
 }
 
 // y = M x
-template <int G>
-TK_DEV void mul_M(const DM& m, const WS& w, double* y, const double* x, const Grp<G>& g) {
-  int nv = m.nv;
+template <int G, int NV>
+TK_DEV void mul_M(const DM& m, const WS& w, double* y, const double* x, const Grp<G, NV>& g) {
+  const int nv = NV ? NV : m.nv;
   for (int i = g.gl; i < nv; i += G) {
     double s = 0.0;
     for (int j = 0; j < nv; j++) s += w.M[i * nv + j] * x[j];

@@ -37,6 +37,15 @@ struct LaunchPlan {
   size_t smem;
 };
 int fast_ecap(const DM& dm);
+// kernel dispatch on (lanes per world, compile-time nv): the shipped models get a specialised instantiation
+// (acrobot nv = 2, walker nv = 9), everything else the generic one (NV = 0 reads nv at run time)
+#define TOKP_DISPATCH(G, NVV, LAUNCH)                                                   \
+  if ((G) == 8 && (NVV) == 9) { LAUNCH(8, 9) }                                          \
+  else if ((G) == 8 && (NVV) == 2) { LAUNCH(8, 2) }                                     \
+  else if ((G) == 4) { LAUNCH(4, 0) }                                                   \
+  else if ((G) == 8) { LAUNCH(8, 0) }                                                   \
+  else if ((G) == 16) { LAUNCH(16, 0) }                                                 \
+  else { LAUNCH(32, 0) }
 inline bool needs_redo_pass(const DM& dm) { return fast_ecap(dm) < dm.maxefc; }
 // returns TOKP_OK or TOKP_ERR_UNSUPPORTED (workspace does not fit shared memory)
 int plan_launch(const DM& dm, int G, int pass, LaunchPlan* out);

@@ -118,23 +118,23 @@ TK_DEV double primal_search(const DM& m, WS& w, const Grp<G, NV>& g, double gaus
       p1next = pe;
       ctl = C_BRACKET;
     } else if (state == LS_MID) {
-      Pnt cand[3] = {p1next, p2next, pe};
-      double bestcost = 0.0;
-      int bestind = -1;
-      for (int i = 0; i < 3; i++)
-        if (fabs(cand[i].d0) < gtol && (bestind == -1 || cand[i].cost < bestcost)) { bestcost = cand[i].cost; bestind = i; }
-      if (bestind >= 0) { result = cand[bestind].alpha; state = LS_DONE; }
+      // candidates in the reference order: p1next, p2next, pmid (no indexed array: everything stays in registers)
+      const Pnt c0 = p1next, c1 = p2next, c2 = pe;
+      double bestcost = 0.0, bestalpha = 0.0;
+      bool found = false;
+      if (fabs(c0.d0) < gtol) { bestcost = c0.cost; bestalpha = c0.alpha; found = true; }
+      if (fabs(c1.d0) < gtol && (!found || c1.cost < bestcost)) { bestcost = c1.cost; bestalpha = c1.alpha; found = true; }
+      if (fabs(c2.d0) < gtol && (!found || c2.cost < bestcost)) { bestcost = c2.cost; bestalpha = c2.alpha; found = true; }
+      if (found) { result = bestalpha; state = LS_DONE; }
       else {
         int b1 = 0;
         b2 = 0;
-        for (int i = 0; i < 3; i++) {
-          if (p1.d0 < 0.0 && cand[i].d0 < 0.0 && p1.d0 < cand[i].d0) { p1 = cand[i]; b1 = 1; }
-          else if (p1.d0 > 0.0 && cand[i].d0 > 0.0 && p1.d0 > cand[i].d0) { p1 = cand[i]; b1 = 2; }
-        }
-        for (int i = 0; i < 3; i++) {
-          if (p2.d0 < 0.0 && cand[i].d0 < 0.0 && p2.d0 < cand[i].d0) { p2 = cand[i]; b2 = 1; }
-          else if (p2.d0 > 0.0 && cand[i].d0 > 0.0 && p2.d0 > cand[i].d0) { p2 = cand[i]; b2 = 2; }
-        }
+#define TK_BRACKET(P, C, FLAG)                                                        \
+  if (P.d0 < 0.0 && C.d0 < 0.0 && P.d0 < C.d0) { P = C; FLAG = 1; }                   \
+  else if (P.d0 > 0.0 && C.d0 > 0.0 && P.d0 > C.d0) { P = C; FLAG = 2; }
+        TK_BRACKET(p1, c0, b1) TK_BRACKET(p1, c1, b1) TK_BRACKET(p1, c2, b1)
+        TK_BRACKET(p2, c0, b2) TK_BRACKET(p2, c1, b2) TK_BRACKET(p2, c2, b2)
+#undef TK_BRACKET
         if (b1) { a_eval = p1.alpha - p1.d0 / p1.d1; state = LS_UB1; }
         else if (b2) { a_eval = p2.alpha - p2.d0 / p2.d1; state = LS_UB2; }
         else { result = pe.alpha; state = LS_DONE; }

@@ -225,6 +225,20 @@ def main():
         jac_e += tr.counters()[1] / 1e6
     barrier()
     dt_e = time.perf_counter() - t0
+    # ---- single-trajectory replan latency (B = 1, host buffers in, controls out), rank 0 only ----------------------
+    lat_ms = None
+    if rank == 0:
+        tr1 = capi.Traj(tc, T, 1)
+        tr1.set_targets(0, targets[0])
+        for _ in range(3):
+            tr1.optimise(snaps[:1], U[:1], 1, 1, lam=0.1)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(10):
+            tr1.optimise(snaps[:1], U[:1], 1, 1, lam=0.1)
+        torch.cuda.synchronize()
+        lat_ms = 1e3 * (time.perf_counter() - t0) / 10
+        del tr1
     sampler.stop_flag = True
     sampler.join(timeout=2)
     h2d = snaps.nbytes + U.nbytes + 8 * B
@@ -258,6 +272,7 @@ def main():
             "ilqr_iter_ms": 1e3 * dt / args.steps, "ilqr_iter_ms_per_replan": 1e3 * dt / args.steps / (B * world),
             "phase_ms": {"derivs": phase[0] / args.steps, "backward": phase[1] / args.steps, "forward": phase[2] / args.steps},
             "jacobians_per_step": jac / args.steps,
+            "replan_latency_ms_b1": lat_ms,   # one trajectory alone on the GPU (serial rollouts / Riccati: latency-bound)
             "e2e": {"value": e2e_value, "unit": "jacobians/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                     "ms_per_step": 1e3 * dt_e / args.steps},
             "gpu_launches": int(l1 - l0), "clocks": sampler.summary(),

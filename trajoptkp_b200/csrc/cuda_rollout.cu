@@ -1,6 +1,7 @@
 // Rollout kernels: nominal rollout and the alpha-batched closed-loop line-search rollouts, persistent over
 // the whole horizon in one launch.  Replaces iLQR::RolloutTrajectory (src/Optimiser/iLQR.cpp:202-254) and
 // iLQR::ForwardsPassParallel (:824-934) + Optimiser::SaveSystemStateToRolloutData (Optimiser.cpp:416-438).
+#include <cstdlib>
 #include "step_dyn.cuh"
 #include "task_dev.cuh"
 #include "traj.h"
@@ -152,7 +153,11 @@ int launch_rollout(tokp_traj* tr, int mode, const double* d_Uin, const double* d
     int warps = lp.warps;
     int blocks = (nworlds + lp.worlds_per_block - 1) / lp.worlds_per_block;
     a.spread = nworlds <= 148 * 4;
-    if (a.spread) { warps = 1; blocks = nworlds; lp.smem = (size_t)lp.wsd * 8; }
+    if (a.spread) {
+      // latency layout: one world per warp, all 32 lanes on it (fewer trips through every strided loop)
+      if (!getenv("TOKP_SPREAD_KEEP_LANES")) G = 32;
+      warps = 1; blocks = nworlds; lp.smem = (size_t)lp.wsd * 8;
+    }
 #define LAUNCH(GG, NN)                                                                                              \
   TOKP_CUDA(cudaFuncSetAttribute(k_rollout<GG, NN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lp.smem));    \
   k_rollout<GG, NN><<<blocks, warps * 32, lp.smem, tr->stream>>>(dm, a, lp.wsd);

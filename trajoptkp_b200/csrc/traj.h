@@ -42,6 +42,7 @@ int fast_ecap(const DM& dm);
 #define TOKP_DISPATCH(G, NVV, LAUNCH)                                                   \
   if ((G) == 8 && (NVV) == 9) { LAUNCH(8, 9) }                                          \
   else if ((G) == 8 && (NVV) == 2) { LAUNCH(8, 2) }                                     \
+  else if ((G) == 32 && (NVV) == 9) { LAUNCH(32, 9) }                                   \
   else if ((G) == 4) { LAUNCH(4, 0) }                                                   \
   else if ((G) == 8) { LAUNCH(8, 0) }                                                   \
   else if ((G) == 16) { LAUNCH(16, 0) }                                                 \

@@ -152,7 +152,12 @@ TK_DEV double primal_search(const DM& m, WS& w, const Grp<G, NV>& g, double gaus
         p2 = p1;
         p2update = 1;
         a_eval = p1.alpha - p1.d0 / p1.d1;
-        state = LS_ONESIDED;
+        // Fixed point of the Newton iteration in floating point (the step no longer changes alpha): every further
+        // evaluation would return p1 again, the loop would spin until lsiter reaches the cap and then return
+        // p1.alpha.  With the FD solver options (tolerance 0 => gtol 0) 4 of 5 evaluations of the reference schedule
+        // are such repeats (measured with an instrumented oracle); skipping them changes no result bit.
+        if (a_eval == p1.alpha) { result = p1.alpha; state = LS_DONE; }
+        else state = LS_ONESIDED;
       } else ctl = C_AFTER;
     }
     if (ctl == C_AFTER) {

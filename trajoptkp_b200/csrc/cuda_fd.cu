@@ -108,7 +108,7 @@ __global__ void k_fd_worlds(DM dm, FdArgs a, int wsd) {
   int* cursor = &a.counts[2 + a.pass];
   int nq = dm.nq, nv = dm.nv;
   tk::WS w;
-  tk::ws_init(w, smem + (size_t)slot_s * wsd, dm, a.ecap);
+  tk::ws_init(w, smem + (size_t)slot_s * wsd, dm, a.ecap, G);
   for (;;) {
     int base = 0;
     if (lane == 0) base = atomicAdd(cursor, GPW);

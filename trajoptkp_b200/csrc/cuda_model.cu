@@ -40,7 +40,7 @@ int plan_launch(const DM& dm, int G, int pass, LaunchPlan* out) {
   LaunchPlan p;
   p.G = G; p.gpw = 32 / G;
   p.ecap = pass == 0 ? fast_ecap(dm) : dm.maxefc;
-  p.wsd = tk::ws_doubles(dm, p.ecap);
+  p.wsd = tk::ws_doubles(dm, p.ecap, G);
   // the groups of a warp access their workspaces at the same offsets: a stride of 64 B (mod 128 B) between consecutive
   // workspaces spreads a unit-stride fp64 access of the whole warp over all 32 banks (2 wavefronts, the minimum)
   if (p.gpw > 1) while (p.wsd % 16 != 8) p.wsd++;
@@ -157,7 +157,7 @@ __global__ void k_step_worlds(DM dm, const double* __restrict__ in, double* __re
   if (!run) return;
   g.wmask = wm;
   tk::WS w;
-  tk::ws_init(w, smem + (size_t)slot * wsd, dm, ecap);
+  tk::ws_init(w, smem + (size_t)slot * wsd, dm, ecap, G);
   const double* s = in + (size_t)gidx * S;
   int nq = dm.nq, nv = dm.nv;
   double time = s[0];

@@ -46,7 +46,7 @@ __global__ void k_rollout(DM dm, RollArgs a, int wsd) {
   int b = a.mode == 0 ? widx : widx / a.NA;
   int ai = a.mode == 0 ? 0 : widx - b * a.NA;
   tk::WS w;
-  tk::ws_init(w, smem + (size_t)slot * wsd, dm, a.ecap);
+  tk::ws_init(w, smem + (size_t)slot * wsd, dm, a.ecap, G);
   const TaskDev& tk_ = a.task;
   int nq = dm.nq, nv = dm.nv, nu = dm.nu, n = tk_.n, m = tk_.m, nx = 2 * n, nr = tk_.nr, T = a.T, SD = a.SD;
   double* snapb = a.snap + (size_t)b * (T + 1) * SD;
@@ -144,20 +144,18 @@ int launch_rollout(tokp_traj* tr, int mode, const double* d_Uin, const double* d
   int G = tr->G;
   a.flags = tr->roll_flags;
   int nworlds = mode == 0 ? tr->B : tr->B * tokp_traj::NA;
+  // few worlds: latency layout - one world per warp with all 32 lanes on it (fewer trips through every strided
+  // loop), one warp per block so that the worlds spread over the SMs
+  a.spread = nworlds <= 148 * 4;
+  if (a.spread && !getenv("TOKP_SPREAD_KEEP_LANES")) G = 32;
   for (int pass = 0; pass < (needs_redo_pass(dm) ? 2 : 1); pass++) {
     LaunchPlan lp;
     int rc = plan_launch(dm, G, pass, &lp);
     if (rc) return rc;
     a.ecap = lp.ecap; a.pass = pass;
-    // few worlds: spread them over the SMs (one group per warp, one warp per block) rather than packing a warp
     int warps = lp.warps;
     int blocks = (nworlds + lp.worlds_per_block - 1) / lp.worlds_per_block;
-    a.spread = nworlds <= 148 * 4;
-    if (a.spread) {
-      // latency layout: one world per warp, all 32 lanes on it (fewer trips through every strided loop)
-      if (!getenv("TOKP_SPREAD_KEEP_LANES")) G = 32;
-      warps = 1; blocks = nworlds; lp.smem = (size_t)lp.wsd * 8;
-    }
+    if (a.spread) { warps = 1; blocks = nworlds; lp.smem = (size_t)lp.wsd * 8; }
 #define LAUNCH(GG, NN)                                                                                              \
   TOKP_CUDA(cudaFuncSetAttribute(k_rollout<GG, NN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lp.smem));    \
   k_rollout<GG, NN><<<blocks, warps * 32, lp.smem, tr->stream>>>(dm, a, lp.wsd);

@@ -153,8 +153,8 @@ TK_DEV bool bad_value(double x) { return !(fabs(x) <= 1e10); }
 // ---- per-world workspace (shared memory) ---------------------------------------------------------
 // Layout = persistent part P, followed by a union region shared by two groups of arrays with disjoint lifetimes:
 //   A  position-stage temporaries (dead once make_constraint has produced J, D, B, kterm)
-//      xpos xquat | (xanchor xaxis)  U  crb  U  (con_dist con_pos con_frame) | efc_pos efc_margin | int tables
-//   B  H | (cvel cacc cfrc cdof_dot : velocity stage)  U  (jar jv quad efc_force : solver)
+//      xpos xquat | (xanchor xaxis)  U  crb  U  (con_dist con_pos con_frame) | int tables
+//   B  (cvel cacc cfrc cdof_dot : velocity stage)  U  (H jar jv efc_force [quad] : solver + Euler)
 // Rotation matrices (xmat, ximat, geom_xmat) are not stored: they are rebuilt from xquat where needed with the same
 // operation sequence (quat2mat then mat_vec3), so results are bit-identical to the stored-matrix form.
 // `ecap` is the constraint-row capacity of this launch: the fast pass uses a small cap, worlds that overflow it are
@@ -171,7 +171,7 @@ struct WS {
   int *con_pair;
   // constraint rows
   double *J, *efc_pos, *efc_margin, *efc_D, *efc_aref, *efc_B, *efc_kterm, *jar, *jv, *quad, *efc_force;
-  int *row_type, *row_id, *row_sub, *cnt;  // cnt: scratch counters (max(njnt, npair) + 2)
+  int *row_info, *cnt;  // row_info: packed (type | (sub+1) << 2 | id << 5); cnt: scratch counters (max(njnt, npair) + 2)
   // velocity / acceleration stage
   double *cvel, *cacc, *cfrc;
   double *frc_passive, *frc_bias, *frc_act, *frc_smooth, *acc_smooth, *frc_con, *Ma, *Mv, *grad, *Mgrad, *search, *tmpv;
@@ -180,16 +180,21 @@ struct WS {
 
 __host__ __device__ inline int ws_imax(int a, int b) { return a > b ? a : b; }
 
-__host__ __device__ inline int ws_doubles(const DM& m, int ecap) {
+// rows of the line search that one lane keeps in registers (step_ls.cuh); with ecap <= LS_ROWS * lanes the quad[]
+// array of the shared-memory path is never touched and gets no space
+constexpr int LS_ROWS = 4;
+__host__ __device__ inline int ws_quad_doubles(int ecap, int lanes) { return ecap > LS_ROWS * lanes ? 3 * ecap : 0; }
+
+__host__ __device__ inline int ws_doubles(const DM& m, int ecap, int lanes) {
   int nb = m.nbody, nv = m.nv, ne = ecap, nc = m.maxcontact;
   int P = m.nq + 3 * nv + m.nu + 3 * nb + 3 * nb + 10 * nb + 6 * nv + 2 * nv * nv + 2 * nv + 12 * nv + ne * nv + 4 * ne;
-  int ints = nc + 3 * ne + ws_imax(m.njnt, m.npair) + 4;
-  int A = 3 * nb + 4 * nb + ws_imax(ws_imax(6 * m.njnt, 10 * nb), 13 * nc) + 2 * ne + (ints + 1) / 2;
-  int B = nv * nv + ws_imax(18 * nb + 6 * nv, 6 * ne);
+  int ints = nc + ne + ws_imax(m.njnt, m.npair) + 4;
+  int A = 3 * nb + 4 * nb + ws_imax(ws_imax(6 * m.njnt, 10 * nb), 10 * nc) + (ints + 1) / 2;
+  int B = ws_imax(18 * nb + 6 * nv, nv * nv + 3 * ne + ws_quad_doubles(ne, lanes));
   return P + ws_imax(A, B);
 }
 
-TK_DEV void ws_init(WS& w, double* base, const DM& m, int ecap) {
+TK_DEV void ws_init(WS& w, double* base, const DM& m, int ecap, int lanes) {
   int nb = m.nbody, nv = m.nv, ne = ecap, nc = m.maxcontact;
   double* p = base;
   auto take = [&](int n) { double* r = p; p += n; return r; };
@@ -209,22 +214,20 @@ TK_DEV void ws_init(WS& w, double* base, const DM& m, int ecap) {
   double* u2 = p;
   w.xanchor = u2; w.xaxis = u2 + 3 * m.njnt;
   w.crb = u2;
-  w.con_dist = u2; w.con_pos = u2 + nc; w.con_frame = u2 + 4 * nc;
-  p = u2 + ws_imax(ws_imax(6 * m.njnt, 10 * nb), 13 * nc);
-  w.efc_pos = take(ne); w.efc_margin = take(ne);
+  w.con_dist = u2; w.con_pos = u2 + nc; w.con_frame = u2 + 4 * nc;  // frame: normal + first tangent (6 per contact)
+  p = u2 + ws_imax(ws_imax(6 * m.njnt, 10 * nb), 10 * nc);
+  // efc_pos / efc_margin only live until the row's impedance is computed: they borrow the slots of efc_aref / efc_kterm
+  w.efc_pos = w.efc_aref; w.efc_margin = w.efc_kterm;
   int* ip = reinterpret_cast<int*>(p);
   w.con_pair = ip; ip += nc;
-  w.row_type = ip; ip += ne;
-  w.row_id = ip; ip += ne;
-  w.row_sub = ip; ip += ne;
+  w.row_info = ip; ip += ne;
   w.cnt = ip;
   // B
   p = u;
-  w.H = take(nv * nv);
-  double* u3 = p;
   w.cvel = take(6 * nb); w.cacc = take(6 * nb); w.cfrc = take(6 * nb); w.cdof_dot = take(6 * nv);
-  p = u3;
-  w.jar = take(ne); w.jv = take(ne); w.quad = take(3 * ne); w.efc_force = take(ne);
+  p = u;
+  w.H = take(nv * nv);
+  w.jar = take(ne); w.jv = take(ne); w.efc_force = take(ne); w.quad = take(ws_quad_doubles(ne, lanes));
   w.ncon = 0; w.nefc = 0; w.ecap = ecap;
 }
 

@@ -43,7 +43,14 @@ TK_DEV int pair_slots(int t1, int t2) {
   return 1;
 }
 
-// complete frame[0:3] to an orthonormal frame (mju_makeFrame)
+// row table entry
+TK_DEV int row_pack(int type, int id, int sub) { return type | ((sub + 1) << 2) | (id << 5); }
+TK_DEV int row_type_of(int info) { return info & 3; }
+TK_DEV int row_sub_of(int info) { return ((info >> 2) & 7) - 1; }
+TK_DEV int row_id_of(int info) { return info >> 5; }
+
+// complete frame[0:3] (normal) and the tangent hint frame[3:6] to an orthonormal pair (mju_makeFrame); the third axis
+// is cross(normal, tangent1), formed where it is used
 TK_DEV void make_frame(double* f) {
   normalize3(f);
   double yn = sqrt(dot3(f + 3, f + 3));
@@ -54,7 +61,6 @@ TK_DEV void make_frame(double* f) {
   double t = dot3(f, f + 3);
   f[3] -= t * f[0]; f[4] -= t * f[1]; f[5] -= t * f[2];
   normalize3(f + 3);
-  cross3(f + 6, f, f + 3);
 }
 
 // plane vs sphere of given centre/radius; writes dist, pos, frame[0:9] (tangents zero); returns 1 on contact
@@ -67,7 +73,7 @@ TK_DEV int plane_sphere(double margin, const double* ppos, const double* pmat, c
   *dist = cd - radius;
   double s = -(*dist) * 0.5 - radius;
   for (int k = 0; k < 3; k++) { pos[k] = c[k] + nrm[k] * s; frame[k] = nrm[k]; }
-  for (int k = 3; k < 9; k++) frame[k] = 0.0;
+  for (int k = 3; k < 6; k++) frame[k] = 0.0;
   return 1;
 }
 
@@ -90,17 +96,17 @@ TK_DEV void collision(const DM& m, WS& w, const Grp<G, NV>& g, int& status) {
       double d[3] = {pos2[0] - pos1[0], pos2[1] - pos1[1], pos2[2] - pos1[2]};
       if (dot3(d, nrm) <= margin + m.geom_rbound[g2]) {
         if (t2 == GEOM_SPHERE) {
-          n = plane_sphere(margin, pos1, mat1, pos2, m.geom_size[3 * g2], &w.con_dist[slot], &w.con_pos[3 * slot], &w.con_frame[9 * slot]);
+          n = plane_sphere(margin, pos1, mat1, pos2, m.geom_size[3 * g2], &w.con_dist[slot], &w.con_pos[3 * slot], &w.con_frame[6 * slot]);
         } else if (t2 == GEOM_CAPSULE) {
           double axis[3] = {mat2[2], mat2[5], mat2[8]}, c[3];
           double hl = m.geom_size[3 * g2 + 1], r = m.geom_size[3 * g2];
           for (int k = 0; k < 3; k++) c[k] = pos2[k] + axis[k] * hl;
-          int n1 = plane_sphere(margin, pos1, mat1, c, r, &w.con_dist[slot], &w.con_pos[3 * slot], &w.con_frame[9 * slot]);
+          int n1 = plane_sphere(margin, pos1, mat1, c, r, &w.con_dist[slot], &w.con_pos[3 * slot], &w.con_frame[6 * slot]);
           for (int k = 0; k < 3; k++) c[k] = pos2[k] - axis[k] * hl;
-          int n2 = plane_sphere(margin, pos1, mat1, c, r, &w.con_dist[slot + n1], &w.con_pos[3 * (slot + n1)], &w.con_frame[9 * (slot + n1)]);
+          int n2 = plane_sphere(margin, pos1, mat1, c, r, &w.con_dist[slot + n1], &w.con_pos[3 * (slot + n1)], &w.con_frame[6 * (slot + n1)]);
           n = n1 + n2;
           for (int i = 0; i < n; i++)
-            for (int k = 0; k < 3; k++) w.con_frame[9 * (slot + i) + 3 + k] = axis[k];
+            for (int k = 0; k < 3; k++) w.con_frame[6 * (slot + i) + 3 + k] = axis[k];
         } else if (t2 == GEOM_BOX) {
           double nrm2[3] = {mat1[2], mat1[5], mat1[8]};
           double dist0 = dot3(d, nrm2);
@@ -115,8 +121,8 @@ TK_DEV void collision(const DM& m, WS& w, const Grp<G, NV>& g, int& status) {
             double cd = dist0 + ld;
             int s = slot + n;
             w.con_dist[s] = cd;
-            for (int k = 0; k < 3; k++) { w.con_pos[3 * s + k] = corner[k] + pos2[k] - nrm2[k] * cd * 0.5; w.con_frame[9 * s + k] = nrm2[k]; }
-            for (int k = 3; k < 9; k++) w.con_frame[9 * s + k] = 0.0;
+            for (int k = 0; k < 3; k++) { w.con_pos[3 * s + k] = corner[k] + pos2[k] - nrm2[k] * cd * 0.5; w.con_frame[6 * s + k] = nrm2[k]; }
+            for (int k = 3; k < 6; k++) w.con_frame[6 * s + k] = 0.0;
             n++;
           }
         } else {
@@ -126,7 +132,7 @@ TK_DEV void collision(const DM& m, WS& w, const Grp<G, NV>& g, int& status) {
     } else {
       status |= ST_UNSUPPORTED;
     }
-    for (int i = 0; i < n; i++) make_frame(&w.con_frame[9 * (slot + i)]);
+    for (int i = 0; i < n; i++) make_frame(&w.con_frame[6 * (slot + i)]);
     w.cnt[p] = n;
   }
   g.sync();
@@ -140,7 +146,7 @@ TK_DEV void collision(const DM& m, WS& w, const Grp<G, NV>& g, int& status) {
         if (s != dst) {
           w.con_dist[dst] = w.con_dist[s];
           for (int k = 0; k < 3; k++) w.con_pos[3 * dst + k] = w.con_pos[3 * s + k];
-          for (int k = 0; k < 9; k++) w.con_frame[9 * dst + k] = w.con_frame[9 * s + k];
+          for (int k = 0; k < 6; k++) w.con_frame[6 * dst + k] = w.con_frame[6 * s + k];
         }
         w.con_pair[dst] = p;
         dst++;
@@ -196,7 +202,7 @@ TK_DEV void make_constraint(const DM& m, WS& w, const Grp<G, NV>& g, int& status
         double dist = side * (m.jnt_range[2 * j + (side + 1) / 2] - value);
         if (dist < margin) {
           if (r >= w.ecap) { status |= ST_OVERFLOW; continue; }
-          w.row_type[r] = ROW_LIMIT; w.row_id[r] = j; w.row_sub[r] = side;
+          w.row_info[r] = row_pack(ROW_LIMIT, j, side);
           w.efc_pos[r] = dist; w.efc_margin[r] = margin;
           r++;
         }
@@ -213,8 +219,7 @@ TK_DEV void make_constraint(const DM& m, WS& w, const Grp<G, NV>& g, int& status
       if (rows < 0) { status |= ST_UNSUPPORTED; continue; }
       if (r + rows > w.ecap) { status |= ST_OVERFLOW; continue; }
       for (int k = 0; k < rows; k++) {
-        w.row_type[r] = rows == 1 ? ROW_FRICTIONLESS : ROW_PYRAMIDAL;
-        w.row_id[r] = c; w.row_sub[r] = k;
+        w.row_info[r] = row_pack(rows == 1 ? ROW_FRICTIONLESS : ROW_PYRAMIDAL, c, k);
         w.efc_pos[r] = w.con_dist[c]; w.efc_margin[r] = inc;
         r++;
       }
@@ -228,23 +233,25 @@ TK_DEV void make_constraint(const DM& m, WS& w, const Grp<G, NV>& g, int& status
   for (int e = g.gl; e < nefc * nv; e += G) {
     int r = e / nv, i = e - r * nv;
     double val = 0.0;
-    if (w.row_type[r] == ROW_LIMIT) {
-      int j = w.row_id[r];
-      if (m.jnt_dofadr[j] == i) val = (double)(-w.row_sub[r]);
+    const int info = w.row_info[r], rtype = row_type_of(info);
+    if (rtype == ROW_LIMIT) {
+      int j = row_id_of(info);
+      if (m.jnt_dofadr[j] == i) val = (double)(-row_sub_of(info));
     } else {
-      int c = w.row_id[r], p = w.con_pair[c];
+      int c = row_id_of(info), p = w.con_pair[c];
       int g1 = m.pair_geom1[p], g2 = m.pair_geom2[p];
       double c1[3], c2[3], d[3];
       jac_col(m, w, c1, &w.con_pos[3 * c], m.geom_bodyid[g1], i);
       jac_col(m, w, c2, &w.con_pos[3 * c], m.geom_bodyid[g2], i);
       d[0] = c2[0] - c1[0]; d[1] = c2[1] - c1[1]; d[2] = c2[2] - c1[2];
-      const double* f = &w.con_frame[9 * c];
+      const double* f = &w.con_frame[6 * c];
       double jn = f[0] * d[0] + f[1] * d[1] + f[2] * d[2];
-      if (w.row_type[r] == ROW_FRICTIONLESS) {
+      if (rtype == ROW_FRICTIONLESS) {
         val = jn;
       } else {
-        int k = w.row_sub[r];          // 0:+t1 1:-t1 2:+t2 3:-t2
-        const double* ft = f + 3 * (1 + k / 2);
+        int k = row_sub_of(info);      // 0:+t1 1:-t1 2:+t2 3:-t2
+        double ft[3] = {f[3], f[4], f[5]};
+        if (k >= 2) cross3(ft, f, f + 3);
         double jt = ft[0] * d[0] + ft[1] * d[1] + ft[2] * d[2];
         double mu = fmax(m.geom_friction[3 * g1], m.geom_friction[3 * g2]);
         if (m.geom_priority[g1] != m.geom_priority[g2])
@@ -257,20 +264,21 @@ TK_DEV void make_constraint(const DM& m, WS& w, const Grp<G, NV>& g, int& status
   // 3. per-row impedance and regularisation
   for (int r = g.gl; r < nefc; r += G) {
     double K, B, imp, diag, Rr;
-    if (w.row_type[r] == ROW_LIMIT) {
-      int j = w.row_id[r];
+    const int info = w.row_info[r], rtype = row_type_of(info);
+    if (rtype == ROW_LIMIT) {
+      int j = row_id_of(info);
       make_kbip(m, &m.jnt_solref[2 * j], &m.jnt_solimp[5 * j], w.efc_pos[r], w.efc_margin[r], K, B, imp);
       diag = m.dof_invweight0[m.jnt_dofadr[j]];
       Rr = fmax(kMinVal, (1.0 - imp) * diag / imp);
     } else {
-      int c = w.row_id[r], p = w.con_pair[c];
+      int c = row_id_of(info), p = w.con_pair[c];
       int g1 = m.pair_geom1[p], g2 = m.pair_geom2[p];
       ConParam cp;
       contact_param(m, g1, g2, cp);
       make_kbip(m, cp.solref, cp.solimp, w.efc_pos[r], w.efc_margin[r], K, B, imp);
       int b1 = m.geom_bodyid[g1], b2 = m.geom_bodyid[g2];
       double tran = m.body_invweight0[2 * b1] + m.body_invweight0[2 * b2];
-      if (w.row_type[r] == ROW_FRICTIONLESS) {
+      if (rtype == ROW_FRICTIONLESS) {
         Rr = fmax(kMinVal, (1.0 - imp) * tran / imp);
       } else {
         // all pyramid edges share R = 2 mu^2 R(first edge); the first edge has diagApprox = tran + mu^2 tran

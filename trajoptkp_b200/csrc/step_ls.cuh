@@ -13,7 +13,7 @@ enum { LS_P0 = 0, LS_P1, LS_ONESIDED, LS_P1NEXT, LS_MID, LS_UB1, LS_UB2, LS_DONE
 // Rows of the search that one lane keeps in registers (row r = lane + k*G): with nefc <= LS_ROWS*G every cost
 // evaluation runs without touching shared memory.  Same per-row terms and the same lane-local summation order as
 // primal_eval, so both paths return identical values.
-constexpr int LS_ROWS = 4;
+// (LS_ROWS is defined in step.cuh next to the workspace layout that depends on it)
 
 template <int G, int NV>
 TK_DEV Pnt primal_eval_reg(const Grp<G, NV>& g, const double qg[3], double alpha, int& lsiter, const double (&rj)[LS_ROWS],

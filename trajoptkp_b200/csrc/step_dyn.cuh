@@ -188,6 +188,7 @@ struct TriMap {
 // division, no wasted upper-triangle iterations); identical arithmetic per entry
 template <int G, int NV>
 TK_DEV void chol_factor_tri(double* H, int n, const Grp<G, NV>& g, const TriMap<G, NV>& tm) {
+#pragma unroll 1
   for (int j = 0; j < n; j++) {
     double d = H[j * n + j];
     if (d < kMinVal) d = kMinVal;
@@ -206,6 +207,7 @@ TK_DEV void chol_factor_tri(double* H, int n, const Grp<G, NV>& g, const TriMap<
 // in-place dense Cholesky (lower) of the nv x nv matrix in w.H, right-looking, lanes over the trailing block
 template <int G, int NV>
 TK_DEV void chol_factor(double* H, int n, const Grp<G, NV>& g) {
+#pragma unroll 1
   for (int j = 0; j < n; j++) {
     double d = H[j * n + j];
     if (d < kMinVal) d = kMinVal;
@@ -228,6 +230,7 @@ template <int G, int NV>
 TK_DEV void chol_solve(const double* L, int n, double* x, const double* b, const Grp<G, NV>& g) {
   for (int i = g.gl; i < n; i += G) x[i] = b[i];
   g.sync();
+#pragma unroll 1
   for (int j = 0; j < n; j++) {
     double xj = x[j] / L[j * n + j];
     g.sync();
@@ -235,6 +238,7 @@ TK_DEV void chol_solve(const double* L, int n, double* x, const double* b, const
     for (int i = j + 1 + g.gl; i < n; i += G) x[i] -= L[i * n + j] * xj;
     g.sync();
   }
+#pragma unroll 1
   for (int j = n - 1; j >= 0; j--) {
     double xj = x[j] / L[j * n + j];
     g.sync();

@@ -196,6 +196,7 @@ TK_DEV void factor_ldl(const DM& m, const double* A, double* LD, double* dinv, c
   const int nv = NV ? NV : m.nv;
   for (int e = g.gl; e < nv * nv; e += G) LD[e] = A[e];
   g.sync();
+#pragma unroll 1
   for (int k = nv - 1; k >= 0; k--) {
     double Mkk = LD[k * nv + k];
     if (Mkk < kMinVal) Mkk = kMinVal;
@@ -219,6 +220,7 @@ template <int G, int NV>
 TK_DEV void solve_ldl(const DM& m, const double* LD, const double* dinv, double* x, const Grp<G, NV>& g) {
   const int nv = NV ? NV : m.nv;
   // x <- inv(L') x : once x[i] is final, push it to its ancestors
+#pragma unroll 1
   for (int i = nv - 1; i > 0; i--) {
     double xi = x[i];
     if (xi != 0.0) {
@@ -231,6 +233,7 @@ TK_DEV void solve_ldl(const DM& m, const double* LD, const double* dinv, double*
   for (int i = g.gl; i < nv; i += G) x[i] *= dinv[i];
   g.sync();
   // x <- inv(L) x : row i needs the final values of its ancestors
+#pragma unroll 1
   for (int i = 1; i < nv; i++) {
     if (g.gl == 0) {
       double s = x[i];

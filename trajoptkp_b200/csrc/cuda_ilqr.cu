@@ -123,10 +123,9 @@ __device__ bool matrix_pd(const double* A, int n) {
 }
 
 // Eigen's pivoted LDLT followed by solve(I) (iLQR.cpp:597-600); column-major n x n, n <= kMaxCtrl
-__device__ void ldlt_inverse(const double* Ain, int n, double* Ainv) {
-  double mat[kMaxCtrl * kMaxCtrl];
-  int tr[kMaxCtrl];
-  for (int i = 0; i < n * n; i++) mat[i] = Ain[i];
+// split in two so that the n columns of solve(I) run on n threads: ldlt_factor (one thread, in place in shared
+// memory) then ldlt_solve_col (thread c solves column c); per-column arithmetic identical to the serial form
+__device__ bool ldlt_factor(double* mat, int n, int* tr) {
 #define MM(r, c) mat[(c) * n + (r)]
   bool zero_matrix = false;
   for (int k = 0; k < n; k++) {
@@ -161,8 +160,14 @@ __device__ void ldlt_inverse(const double* Ain, int n, double* Ainv) {
     if (rs > 0 && valid)
       for (int i = 0; i < rs; i++) MM(k + 1 + i, k) /= akk;
   }
+  return zero_matrix;
+#undef MM
+}
+
+__device__ void ldlt_solve_col(const double* mat, int n, const int* tr, bool zero_matrix, int c, double* Ainv) {
+#define MM(r, c) mat[(c) * n + (r)]
   const double tol = 2.2250738585072014e-308;
-  for (int c = 0; c < n; c++) {
+  {
     double x[kMaxCtrl];
     for (int i = 0; i < n; i++) x[i] = 0.0;
     if (!zero_matrix) {
@@ -200,8 +205,12 @@ __global__ void k_riccati(const double* __restrict__ A, const double* __restrict
   double* Kt = kt + m;
   double* tm = Kt + m * nx;    // Quu * k
   double* tmx = tm + m;        // Quu * K
-  __shared__ int s_fail;
+  double* sA = tmx + m * nx;   // A_t, B_t staged per step (coalesced) instead of strided global reads in the products
+  double* sB = sA + nx * nx;
+  __shared__ int s_fail, s_zero;
   __shared__ double s_dJ;
+  __shared__ double s_mat[kMaxCtrl * kMaxCtrl];
+  __shared__ int s_tr[kMaxCtrl];
   const double* Ab = A + (size_t)b * T * nx * nx;
   const double* Bb = Bm + (size_t)b * T * nx * m;
   const double* lxb = lx + (size_t)b * (T + 1) * nx;
@@ -217,8 +226,11 @@ __global__ void k_riccati(const double* __restrict__ A, const double* __restrict
   int pd_counter = 0;
   for (int t = T - 1; t >= 0; t--) {
     pd_counter++;
-    const double* At = Ab + (size_t)t * nx * nx;
-    const double* Bt = Bb + (size_t)t * nx * m;
+    for (int i = tid; i < nx * nx; i += nt) sA[i] = Ab[(size_t)t * nx * nx + i];
+    for (int i = tid; i < nx * m; i += nt) sB[i] = Bb[(size_t)t * nx * m + i];
+    __syncthreads();
+    const double* At = sA;
+    const double* Bt = sB;
     for (int i = tid; i < nx + m; i += nt) {
       double s = 0;
       if (i < nx) { for (int r = 0; r < nx; r++) s += At[i * nx + r] * Vx[r]; Qx[i] = lxb[(size_t)t * nx + i] + s; }
@@ -248,14 +260,18 @@ __global__ void k_riccati(const double* __restrict__ A, const double* __restrict
     }
     __syncthreads();
     if (tid == 0) {
-      double reg[kMaxCtrl * kMaxCtrl];
-      for (int i = 0; i < m * m; i++) reg[i] = Quu[i];
-      for (int i = 0; i < m; i++) reg[i * m + i] += lam;
+      for (int i = 0; i < m * m; i++) s_mat[i] = Quu[i];
+      for (int i = 0; i < m; i++) s_mat[i * m + i] += lam;
       if (pd_counter >= 100) {
-        if (!matrix_pd(reg, m)) s_fail = 1;
+        if (!matrix_pd(s_mat, m)) s_fail = 1;
       }
+      if (!s_fail) s_zero = ldlt_factor(s_mat, m, s_tr) ? 1 : 0;
+    }
+    __syncthreads();
+    if (!s_fail && tid < m) ldlt_solve_col(s_mat, m, s_tr, s_zero != 0, tid, Qinv);
+    __syncthreads();
+    if (tid == 0) {
       if (!s_fail) {
-        ldlt_inverse(reg, m, Qinv);
         for (int r = 0; r < m; r++) {
           double s = 0;
           for (int q = 0; q < m; q++) s += Qinv[q * m + r] * Qu[q];
@@ -386,7 +402,7 @@ static int generate_derivatives(tokp_traj* tr) {
 static int backward_pass(tokp_traj* tr) {
   int nx = tr->nx, m = tr->m;
   if (m > kMaxCtrl || m < 1) { set_error("backward pass supports 1..8 controls"); return TOKP_ERR_UNSUPPORTED; }
-  size_t smem = (size_t)(3 * nx * nx + 2 * nx + 4 * m * nx + 2 * m * m + 3 * m) * 8;
+  size_t smem = (size_t)(4 * nx * nx + 2 * nx + 5 * m * nx + 2 * m * m + 3 * m) * 8;
   if (smem > 227 * 1024) { set_error("state dimension too large for the backward-pass workspace"); return TOKP_ERR_UNSUPPORTED; }
   TOKP_CUDA(cudaFuncSetAttribute(k_riccati, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int threads = nx * nx >= 1024 ? 256 : 128;

@@ -35,6 +35,7 @@ struct FdArgs {
   int ecap, pass;                   // constraint-row capacity of this pass; pass 1 redoes overflowed worlds only
   int *list0, *list1;               // compacted world lists (gidx = row index * W + slot): all running / overflowed
   int* counts;                      // [0] |list0|, [1] |list1|, [2] cursor of pass 0, [3] cursor of pass 1
+  int blocksync;                    // Grp::bsync level of this launch (0 = warps run independently)
 };
 
 // which perturbation a world slot carries: kind 0 nominal, 1 control, 2 velocity, 3 position
@@ -109,20 +110,39 @@ __global__ void k_fd_worlds(DM dm, FdArgs a, int wsd) {
   int nq = dm.nq, nv = dm.nv;
   tk::WS w;
   tk::ws_init(w, smem + (size_t)slot_s * wsd, dm, a.ecap, G);
+  __shared__ int s_base;
   for (;;) {
     int base = 0;
-    if (lane == 0) base = atomicAdd(cursor, GPW);
-    base = __shfl_sync(0xffffffffu, base, 0);
-    if (base >= count) break;
+    if (a.blocksync) {
+      // the whole block fetches one chunk of worlds and walks the two halves of the step together
+      __syncthreads();
+      if (threadIdx.x == 0) s_base = atomicAdd(cursor, GPW * (int)(blockDim.x >> 5));
+      __syncthreads();
+      base = s_base;
+      if (base >= count) break;
+      base += warp * GPW;
+      g.bsync = a.blocksync;
+    } else {
+      if (lane == 0) base = atomicAdd(cursor, GPW);
+      base = __shfl_sync(0xffffffffu, base, 0);
+      if (base >= count) break;
+    }
     int li = base + lane / G;
+    // block-synchronous mode: groups past the end of the list re-run the last world (every thread must reach the
+    // block barriers inside the step) and drop the result
+    const bool real = li < count;
+    if (a.blocksync && !real) li = count - 1;
     bool run = li < count;
     g.wmask = __ballot_sync(0xffffffffu, run);
+    long long gidx = 0;
+    FdWorld wd;
+    double time = 0.0;
+    int st = 0;
     if (run) {
-      long long gidx = list[li];
-      FdWorld wd;
+      gidx = list[li];
       fd_decode(dm, a, gidx, wd);
       const double* s = a.snap + ((size_t)wd.b * (a.T + 1) + wd.t) * a.SD;
-      double time = s[0];
+      time = s[0];
       for (int i = g.gl; i < nq; i += G) w.qpos[i] = s[1 + i];
       for (int i = g.gl; i < nv; i += G) {
         w.qvel[i] = s[1 + nq + i];
@@ -156,8 +176,9 @@ __global__ void k_fd_worlds(DM dm, FdArgs a, int wsd) {
         }
       }
       g.sync();
-      int st = 0;
       tk::step(dm, w, g, a.iterations, a.tolerance, time, st);
+    }
+    if (run && real) {
       double* o = a.fd_out + ((size_t)wd.row * a.W + wd.slot) * (nq + nv);
       for (int i = g.gl; i < nq; i += G) o[i] = w.qpos[i];
       for (int i = g.gl; i < nv; i += G) o[nq + i] = w.qvel[i];
@@ -257,6 +278,10 @@ int launch_fd(tokp_traj* tr, const unsigned long long* mask, const int* rows, in
     // persistent grid: as many blocks as stay resident, never more than the worlds need
     long long need = (worlds + lp.worlds_per_block - 1) / lp.worlds_per_block;
     int blocks = (int)(need < (long long)lp.resident_blocks ? need : (long long)lp.resident_blocks);
+    // block-synchronous walk of the step (see Grp::bsync): the warps of a block stay in the same region of the step
+    // code, which is several times the instruction cache.  TOKP_FD_BLOCKSYNC=0 lets the warps run independently.
+    a.blocksync = 1;
+    if (const char* e = getenv("TOKP_FD_BLOCKSYNC")) a.blocksync = atoi(e) < 0 ? 0 : (atoi(e) > 2 ? 2 : atoi(e));
 #define LAUNCH(GG, NN)                                                                                               \
   TOKP_CUDA(cudaFuncSetAttribute(k_fd_worlds<GG, NN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lp.smem));   \
   k_fd_worlds<GG, NN><<<blocks, lp.warps * 32, lp.smem, tr->stream>>>(dm, a, lp.wsd);

@@ -48,12 +48,12 @@ int plan_launch(const DM& dm, int G, int pass, LaunchPlan* out) {
   const size_t sm_bytes = 227 * 1024, block_overhead = 1024;
   // warps per block: the choice that keeps the most worlds resident per SM (ties -> larger blocks)
   int best = 0, best_worlds = -1;
-  for (int w = 4; w >= 1; w >>= 1) {
+  for (int w = 4; w >= 1; w--) {
     size_t blk = per_world * w * p.gpw;
     if (blk > sm_bytes) continue;
     int resident = (int)(sm_bytes / (blk + block_overhead));
     if (resident > 32) resident = 32;
-    if (resident * w > 64) resident = 64 / w;
+    if (resident * w > 8) resident = 8 / w;  // <= 255-register kernels: 8 warps per SM
     int worlds = resident * w * p.gpw;
     if (worlds > best_worlds) { best_worlds = worlds; best = w; }
   }

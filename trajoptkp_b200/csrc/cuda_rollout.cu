@@ -27,6 +27,7 @@ struct RollArgs {
   int* flags;          // [nworlds] overflow flags written by pass 0, consumed by pass 1
   int ecap, pass;
   int spread;          // 1: one world per warp (first group only) - latency layout for small batches
+  int bsync;           // Grp::bsync level: the block walks the stages of every step together
 };
 
 template <int G, int NV>
@@ -38,11 +39,15 @@ __global__ void k_rollout(DM dm, RollArgs a, int wsd) {
   int widx = a.spread ? blockIdx.x * (blockDim.x >> 5) + warp : (blockIdx.x * (blockDim.x >> 5) + warp) * GPW + lane / G;
   int slot = a.spread ? warp : warp * GPW + lane / G;
   int nworlds = a.mode == 0 ? a.B : a.B * a.NA;
+  // block-synchronous launches keep every thread: groups past the end repeat the last world (same values to the
+  // same addresses)
+  if (a.bsync && widx >= nworlds) widx = nworlds - 1;
   bool run = widx < nworlds && !(a.spread && lane / G != 0);
   if (run && a.pass == 1 && !a.flags[widx]) run = false;
   unsigned wm = __ballot_sync(0xffffffffu, run);
   if (!run) return;
   g.wmask = wm;
+  g.bsync = a.bsync;
   int b = a.mode == 0 ? widx : widx / a.NA;
   int ai = a.mode == 0 ? 0 : widx - b * a.NA;
   tk::WS w;
@@ -153,6 +158,9 @@ int launch_rollout(tokp_traj* tr, int mode, const double* d_Uin, const double* d
     int rc = plan_launch(dm, G, pass, &lp);
     if (rc) return rc;
     a.ecap = lp.ecap; a.pass = pass;
+    // the redo pass runs a sparse subset of the worlds and the latency layout has one warp per block: no block walk
+    a.bsync = (pass == 0 && !a.spread) ? 1 : 0;
+    if (const char* e = getenv("TOKP_ROLL_BLOCKSYNC")) if (a.bsync) a.bsync = atoi(e) > 2 ? 2 : (atoi(e) < 0 ? 0 : atoi(e));
     int warps = lp.warps;
     int blocks = (nworlds + lp.worlds_per_block - 1) / lp.worlds_per_block;
     if (a.spread) { warps = 1; blocks = nworlds; lp.smem = (size_t)lp.wsd * 8; }

@@ -34,6 +34,10 @@ struct Grp {
   unsigned mask;
   unsigned wmask;  // lanes of every group of this warp that runs a world (set by the kernel with a full-warp ballot)
   int gl;  // lane index inside the group
+  // block-synchronous mode (set by the kernel, uniform over the block): 0 = warps run independently; >= 1 = every
+  // thread of the block runs a world and the block passes the stages of a step and the Newton iterations together
+  // (one hot region of the large step code in the instruction cache at a time); >= 2 also the line-search iterations
+  int bsync = 0;
   TK_DEV Grp() {
     int lane = threadIdx.x & 31;
     gl = lane % G;
@@ -44,6 +48,11 @@ struct Grp {
   // groups must reach every any_warp() call; it doubles as the point where the groups of a warp reconverge, so that
   // the worlds sharing a warp execute the solver's loops in lock-step instead of one after the other.
   TK_DEV int any_warp(int p) const { return __any_sync(wmask, p); }
+  // the same for a loop the whole block walks together in block-synchronous mode
+  TK_DEV int any_block(int p) const { return bsync ? __syncthreads_or(p) : __any_sync(wmask, p); }
+  TK_DEV int any_block_ls(int p) const { return bsync >= 2 ? __syncthreads_or(p) : __any_sync(wmask, p); }
+  // stage boundary of a step
+  TK_DEV void phase() const { if (bsync) __syncthreads(); }
   TK_DEV void sync() const { __syncwarp(mask); }
   TK_DEV double sum(double v) const {
 #pragma unroll

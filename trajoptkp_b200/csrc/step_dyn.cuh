@@ -351,7 +351,7 @@ TK_DEV void fwd_constraint(const DM& m, WS& w, const Grp<G, NV>& g, int iteratio
   int iter = -1;
   bool run = has;
   double alpha = 1.0, oldcost = 0.0;
-  while (g.any_warp(run)) {
+  while (g.any_block(run)) {
     if (run) {
       if (iter >= 0 && alpha == 0.0) {
         run = false;
@@ -416,24 +416,46 @@ TK_DEV void euler(const DM& m, WS& w, const Grp<G, NV>& g, double& time) {
   g.sync();
 }
 
-// one full step (mj_step).  `iterations`/`tolerance`: solver options of this launch.
+// one full step (mj_step) in two halves, so that a kernel can put a block barrier between them (all warps of an SM
+// then run the same region of this large code at the same time and share the instruction cache):
+//   step_smooth      position + velocity stages, actuation, smooth acceleration
+//   step_constrained constraint solver, acceleration check, Euler
 template <int G, int NV>
-TK_DEV void step(const DM& m, WS& w, const Grp<G, NV>& g, int iterations, double tolerance, double& time, int& status) {
+TK_DEV void step_smooth(const DM& m, WS& w, const Grp<G, NV>& g, int& status) {
   for (int i = g.gl; i < m.nq; i += G) if (bad_value(w.qpos[i])) status |= ST_BAD_QPOS;
   for (int i = g.gl; i < m.nv; i += G) if (bad_value(w.qvel[i])) status |= ST_BAD_QVEL;
   kinematics(m, w, g);
   com_pos(m, w, g);
+  g.phase();
   crb_factor(m, w, g);
   factor_ldl(m, w.M, w.LD, w.LDinv, g);
+  g.phase();
   collision(m, w, g, status);
+  g.phase();
   make_constraint(m, w, g, status);
+  g.phase();
   com_vel(m, w, g);
   passive_and_bias(m, w, g);
+  g.phase();
   reference_constraint(m, w, g);
   actuation_acceleration(m, w, g);
+}
+
+template <int G, int NV>
+TK_DEV void step_constrained(const DM& m, WS& w, const Grp<G, NV>& g, int iterations, double tolerance, double& time,
+                             int& status) {
   fwd_constraint(m, w, g, iterations, tolerance);
+  g.phase();
   for (int i = g.gl; i < m.nv; i += G) if (bad_value(w.qacc[i])) status |= ST_BAD_QACC;
   euler(m, w, g, time);
+}
+
+// one full step (mj_step).  `iterations`/`tolerance`: solver options of this launch.
+template <int G, int NV>
+TK_DEV void step(const DM& m, WS& w, const Grp<G, NV>& g, int iterations, double tolerance, double& time, int& status) {
+  step_smooth(m, w, g, status);
+  g.phase();
+  step_constrained(m, w, g, iterations, tolerance, time, status);
 }
 
 }  // namespace tk

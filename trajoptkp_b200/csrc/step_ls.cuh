@@ -96,7 +96,7 @@ TK_DEV double primal_search(const DM& m, WS& w, const Grp<G, NV>& g, double gaus
   int lsiter = 0, p2update = 0, b2 = 0;
   double dir = 0.0, a_eval = 0.0;
   Pnt p0 = {0, 0, 0, 0}, p1 = p0, p2 = p0, p1next = p0, p2next = p0;
-  while (g.any_warp(state != LS_DONE)) {
+  while (g.any_block_ls(state != LS_DONE)) {
     if (state == LS_DONE) continue;
     Pnt pe = regpath ? primal_eval_reg(g, qg, a_eval, lsiter, rj, rv, r0, r1, r2) : primal_eval(w, g, qg, a_eval, lsiter);
     enum { C_NONE = 0, C_ONESIDED, C_AFTER, C_BRACKET, C_FINAL };

@@ -98,7 +98,7 @@ __global__ void k_fd_plan(DM dm, FdArgs a) {
 // G lanes per world.  pass 0 reads list0 and appends the worlds that overflow the fast constraint-row capacity to
 // list1; pass 1 re-runs list1 with ecap = maxefc.
 template <int G, int NV>
-__global__ void k_fd_worlds(DM dm, FdArgs a, int wsd) {
+__global__ void __launch_bounds__(G == 16 ? 384 : 128, G == 16 ? 1 : 2) k_fd_worlds(DM dm, FdArgs a, int wsd) {
   extern __shared__ double smem[];
   constexpr int GPW = 32 / G;
   tk::Grp<G, NV> g;
@@ -280,8 +280,8 @@ int launch_fd(tokp_traj* tr, const unsigned long long* mask, const int* rows, in
     int blocks = (int)(need < (long long)lp.resident_blocks ? need : (long long)lp.resident_blocks);
     // block-synchronous walk of the step (see Grp::bsync): the warps of a block stay in the same region of the step
     // code, which is several times the instruction cache.  TOKP_FD_BLOCKSYNC=0 lets the warps run independently.
-    a.blocksync = 1;
-    if (const char* e = getenv("TOKP_FD_BLOCKSYNC")) a.blocksync = atoi(e) < 0 ? 0 : (atoi(e) > 2 ? 2 : atoi(e));
+    a.blocksync = 2;
+    if (const char* e = getenv("TOKP_FD_BLOCKSYNC")) a.blocksync = atoi(e) < 0 ? 0 : (atoi(e) > 3 ? 3 : atoi(e));
 #define LAUNCH(GG, NN)                                                                                               \
   TOKP_CUDA(cudaFuncSetAttribute(k_fd_worlds<GG, NN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lp.smem));   \
   k_fd_worlds<GG, NN><<<blocks, lp.warps * 32, lp.smem, tr->stream>>>(dm, a, lp.wsd);

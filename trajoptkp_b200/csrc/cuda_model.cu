@@ -24,8 +24,10 @@ int lanes_for_model(const DM& dm) {
     int v = atoi(e);
     if (v == 4 || v == 8 || v == 16 || v == 32) return v;
   }
+  // 16 lanes from nv = 8: half the worlds per warp of the 8-lane layout, but 168 registers instead of 255 and half
+  // the shared memory per warp, i.e. twice the resident warps (walker: 12 per SM)
   int k = dm.nv > dm.nbody ? dm.nv : dm.nbody;
-  if (k <= 10) return 8;
+  if (k < 8) return 8;
   if (k <= 20) return 16;
   return 32;
 }
@@ -45,19 +47,20 @@ int plan_launch(const DM& dm, int G, int pass, LaunchPlan* out) {
   // workspaces spreads a unit-stride fp64 access of the whole warp over all 32 banks (2 wavefronts, the minimum)
   if (p.gpw > 1) while (p.wsd % 16 != 8) p.wsd++;
   size_t per_world = (size_t)p.wsd * 8;
+  const int reg_warps = 4 * reg_blocks(G);  // warps per SM the register budget allows
   const size_t sm_bytes = 227 * 1024, block_overhead = 1024;
-  // warps per block: the choice that keeps the most worlds resident per SM (ties -> larger blocks)
-  int best = 0, best_worlds = -1;
-  for (int w = 4; w >= 1; w--) {
-    size_t blk = per_world * w * p.gpw;
-    if (blk > sm_bytes) continue;
-    int resident = (int)(sm_bytes / (blk + block_overhead));
-    if (resident > 32) resident = 32;
-    if (resident * w > 8) resident = 8 / w;  // <= 255-register kernels: 8 warps per SM
-    int worlds = resident * w * p.gpw;
-    if (worlds > best_worlds) { best_worlds = worlds; best = w; }
+  // warps per block: two blocks per SM that together hold as many warps as shared memory and registers allow.  The
+  // kernels walk the step block-synchronously (Grp::bsync), so the warps of a block share the instruction cache; two
+  // such blocks per SM measured faster than one (barrier waits overlap) and faster than three or four.
+  int best = 0;
+  {
+    size_t per_warp = per_world * p.gpw;
+    int total = (int)((sm_bytes - 2 * block_overhead) / per_warp);
+    if (total > reg_warps) total = reg_warps;
+    best = total / 2;
+    if (best < 1 && per_warp <= sm_bytes) best = 1;
   }
-  if (const char* e = getenv("TOKP_WARPS")) { int v = atoi(e); if (v > 0 && per_world * v * p.gpw <= sm_bytes) best = v; }
+  if (const char* e = getenv("TOKP_WARPS")) { int v = atoi(e); if (v > 0 && v <= (G == 16 ? 12 : 4) && per_world * v * p.gpw <= sm_bytes) best = v; }
   if (best == 0) { set_error("model too large for the shared-memory workspace"); return TOKP_ERR_UNSUPPORTED; }
   p.warps = best; p.worlds_per_block = best * p.gpw; p.smem = per_world * best * p.gpw;
   {
@@ -69,7 +72,7 @@ int plan_launch(const DM& dm, int G, int pass, LaunchPlan* out) {
     }
     int resident = (int)(sm_bytes / (p.smem + block_overhead));
     if (resident > 32) resident = 32;
-    if (resident * best > 8) resident = 8 / best;  // <= 255-register kernels: 8 warps per SM
+    if (resident * best > reg_warps) resident = reg_warps / best;
     if (resident < 1) resident = 1;
     p.resident_blocks = resident * sm_count;
   }

@@ -31,7 +31,7 @@ struct RollArgs {
 };
 
 template <int G, int NV>
-__global__ void k_rollout(DM dm, RollArgs a, int wsd) {
+__global__ void __launch_bounds__(G == 16 ? 384 : 128, G == 16 ? 1 : 2) k_rollout(DM dm, RollArgs a, int wsd) {
   extern __shared__ double smem[];
   tk::Grp<G, NV> g;
   int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -159,8 +159,8 @@ int launch_rollout(tokp_traj* tr, int mode, const double* d_Uin, const double* d
     if (rc) return rc;
     a.ecap = lp.ecap; a.pass = pass;
     // the redo pass runs a sparse subset of the worlds and the latency layout has one warp per block: no block walk
-    a.bsync = (pass == 0 && !a.spread) ? 1 : 0;
-    if (const char* e = getenv("TOKP_ROLL_BLOCKSYNC")) if (a.bsync) a.bsync = atoi(e) > 2 ? 2 : (atoi(e) < 0 ? 0 : atoi(e));
+    a.bsync = (pass == 0 && !a.spread) ? 2 : 0;
+    if (const char* e = getenv("TOKP_ROLL_BLOCKSYNC")) if (a.bsync) a.bsync = atoi(e) > 3 ? 3 : (atoi(e) < 0 ? 0 : atoi(e));
     int warps = lp.warps;
     int blocks = (nworlds + lp.worlds_per_block - 1) / lp.worlds_per_block;
     if (a.spread) { warps = 1; blocks = nworlds; lp.smem = (size_t)lp.wsd * 8; }

@@ -35,8 +35,8 @@ struct Grp {
   unsigned wmask;  // lanes of every group of this warp that runs a world (set by the kernel with a full-warp ballot)
   int gl;  // lane index inside the group
   // block-synchronous mode (set by the kernel, uniform over the block): 0 = warps run independently; >= 1 = every
-  // thread of the block runs a world and the block passes the stages of a step and the Newton iterations together
-  // (one hot region of the large step code in the instruction cache at a time); >= 2 also the line-search iterations
+  // thread of the block runs a world and the block passes the stages of a step together (one hot region of the large
+  // step code in the instruction cache at a time); >= 2 also the Newton iterations; >= 3 also the line-search trips
   int bsync = 0;
   TK_DEV Grp() {
     int lane = threadIdx.x & 31;
@@ -49,8 +49,8 @@ struct Grp {
   // the worlds sharing a warp execute the solver's loops in lock-step instead of one after the other.
   TK_DEV int any_warp(int p) const { return __any_sync(wmask, p); }
   // the same for a loop the whole block walks together in block-synchronous mode
-  TK_DEV int any_block(int p) const { return bsync ? __syncthreads_or(p) : __any_sync(wmask, p); }
-  TK_DEV int any_block_ls(int p) const { return bsync >= 2 ? __syncthreads_or(p) : __any_sync(wmask, p); }
+  TK_DEV int any_block(int p) const { return bsync >= 2 ? __syncthreads_or(p) : __any_sync(wmask, p); }
+  TK_DEV int any_block_ls(int p) const { return bsync >= 3 ? __syncthreads_or(p) : __any_sync(wmask, p); }
   // stage boundary of a step
   TK_DEV void phase() const { if (bsync) __syncthreads(); }
   TK_DEV void sync() const { __syncwarp(mask); }
@@ -60,6 +60,7 @@ struct Grp {
     return v;
   }
   TK_DEV int any(int p) const { return __any_sync(mask, p); }
+  TK_DEV int all(int p) const { return __all_sync(mask, p); }
 };
 
 // ---- small vector helpers ---------------------------------------------------------------------------
@@ -191,8 +192,8 @@ __host__ __device__ inline int ws_imax(int a, int b) { return a > b ? a : b; }
 
 // rows of the line search that one lane keeps in registers (step_ls.cuh); with ecap <= LS_ROWS * lanes the quad[]
 // array of the shared-memory path is never touched and gets no space
-constexpr int LS_ROWS = 4;
-__host__ __device__ inline int ws_quad_doubles(int ecap, int lanes) { return ecap > LS_ROWS * lanes ? 3 * ecap : 0; }
+__host__ __device__ constexpr int ls_rows(int lanes) { return lanes >= 32 ? 1 : (lanes >= 16 ? 2 : 4); }
+__host__ __device__ inline int ws_quad_doubles(int ecap, int lanes) { return ecap > ls_rows(lanes) * lanes ? 3 * ecap : 0; }
 
 __host__ __device__ inline int ws_doubles(const DM& m, int ecap, int lanes) {
   int nb = m.nbody, nv = m.nv, ne = ecap, nc = m.maxcontact;

@@ -161,9 +161,10 @@ TK_DEV Pnt primal_eval(const WS& w, const Grp<G, NV>& g, const double qg[3], dou
 
 // Lower-triangle entries of an nv x nv matrix owned by one lane (entry idx = lane + k*G, row-major over the triangle):
 // used by the Hessian assembly and the Cholesky trailing update when nv(nv+1)/2 <= TRI_MAX*G.
-constexpr int TRI_MAX = 8;
+__host__ __device__ constexpr int tri_max(int lanes, int nv) { return nv ? (nv * (nv + 1) / 2 + lanes - 1) / lanes : 8; }
 template <int G, int NV>
 struct TriMap {
+  static constexpr int TRI_MAX = tri_max(G, NV);
   int cnt;             // entries of this lane
   int ei[TRI_MAX], ej[TRI_MAX];
   TK_DEV void init(int nv, int gl) {
@@ -188,6 +189,7 @@ struct TriMap {
 // division, no wasted upper-triangle iterations); identical arithmetic per entry
 template <int G, int NV>
 TK_DEV void chol_factor_tri(double* H, int n, const Grp<G, NV>& g, const TriMap<G, NV>& tm) {
+  constexpr int TRI_MAX = TriMap<G, NV>::TRI_MAX;
 #pragma unroll 1
   for (int j = 0; j < n; j++) {
     double d = H[j * n + j];
@@ -259,18 +261,30 @@ TK_DEV void fwd_constraint(const DM& m, WS& w, const Grp<G, NV>& g, int iteratio
   const int nv = NV ? NV : m.nv, nefc = w.nefc;
   const bool has = nefc > 0;
   double cost = 0.0, gauss = 0.0;
+  constexpr int TRI_MAX = TriMap<G, NV>::TRI_MAX;
   const bool tri = nv * (nv + 1) / 2 <= TRI_MAX * G;
   TriMap<G, NV> tm;
   tm.cnt = 0;
   if (tri && has) tm.init(nv, g.gl);
+  // rows of this lane that entered the last assembled Hessian (bit k = row gl + k*G); 64 bits cover maxefc <= 64*G
+  unsigned long long hess_rows = 0ull;
+  bool have_factor = false;
   auto update = [&]() {
     // forces, cost, qfrc_constraint, gradient, Hessian, Newton direction
     double c = 0.0;
-    for (int r = g.gl; r < nefc; r += G) {
+    unsigned long long rows = 0ull;
+    int kbit = 0;
+    for (int r = g.gl; r < nefc; r += G, kbit++) {
       double x = w.jar[r];
       if (x < 0.0) { c += 0.5 * w.efc_D[r] * x * x; w.efc_force[r] = -w.efc_D[r] * x; }
       else w.efc_force[r] = 0.0;
+      if (w.efc_force[r] != 0.0) rows |= 1ull << (kbit & 63);
     }
+    // H = M + J' diag(D over the rows with a force) J depends on the state only through that row set: when the set is
+    // the one of the previous Newton iteration the factor in w.H is still the factor of this H, bit for bit
+    const bool same_factor = have_factor && nefc <= 64 * G && g.all(rows == hess_rows);
+    hess_rows = rows;
+    have_factor = true;
     c = g.sum(c);
     g.sync();
     double gsum = 0.0;
@@ -283,7 +297,9 @@ TK_DEV void fwd_constraint(const DM& m, WS& w, const Grp<G, NV>& g, int iteratio
     }
     gauss = 0.5 * g.sum(gsum);
     cost = c + gauss;
-    if (tri) {
+    if (same_factor) {
+      // keep the factor
+    } else if (tri) {
       // rows outermost, the lane's triangle entries in registers: inactive rows cost one broadcast load
       double h[TRI_MAX];
 #pragma unroll

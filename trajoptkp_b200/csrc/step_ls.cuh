@@ -13,12 +13,13 @@ enum { LS_P0 = 0, LS_P1, LS_ONESIDED, LS_P1NEXT, LS_MID, LS_UB1, LS_UB2, LS_DONE
 // Rows of the search that one lane keeps in registers (row r = lane + k*G): with nefc <= LS_ROWS*G every cost
 // evaluation runs without touching shared memory.  Same per-row terms and the same lane-local summation order as
 // primal_eval, so both paths return identical values.
-// (LS_ROWS is defined in step.cuh next to the workspace layout that depends on it)
+// (ls_rows(G) is defined in step.cuh next to the workspace layout that depends on it)
 
 template <int G, int NV>
-TK_DEV Pnt primal_eval_reg(const Grp<G, NV>& g, const double qg[3], double alpha, int& lsiter, const double (&rj)[LS_ROWS],
-                           const double (&rv)[LS_ROWS], const double (&r0)[LS_ROWS], const double (&r1)[LS_ROWS],
-                           const double (&r2)[LS_ROWS]) {
+TK_DEV Pnt primal_eval_reg(const Grp<G, NV>& g, const double qg[3], double alpha, int& lsiter,
+                           const double (&rj)[ls_rows(G)], const double (&rv)[ls_rows(G)], const double (&r0)[ls_rows(G)],
+                           const double (&r1)[ls_rows(G)], const double (&r2)[ls_rows(G)]) {
+  constexpr int LS_ROWS = ls_rows(G);
   lsiter++;
   double q0 = 0.0, q1 = 0.0, q2 = 0.0;
 #pragma unroll
@@ -39,6 +40,7 @@ TK_DEV Pnt primal_eval_reg(const Grp<G, NV>& g, const double qg[3], double alpha
 template <int G, int NV>
 TK_DEV double primal_search(const DM& m, WS& w, const Grp<G, NV>& g, double gauss, double tolerance, bool run) {
   const int nv = NV ? NV : m.nv;
+  constexpr int LS_ROWS = ls_rows(G);
   int state = LS_DONE;
   double result = 0.0, gtol = 0.0;
   double qg[3] = {0.0, 0.0, 0.0};
@@ -101,9 +103,14 @@ TK_DEV double primal_search(const DM& m, WS& w, const Grp<G, NV>& g, double gaus
     Pnt pe = regpath ? primal_eval_reg(g, qg, a_eval, lsiter, rj, rv, r0, r1, r2) : primal_eval(w, g, qg, a_eval, lsiter);
     enum { C_NONE = 0, C_ONESIDED, C_AFTER, C_BRACKET, C_FINAL };
     int ctl = C_NONE;
+    // the next evaluation point is often a Newton step alpha - d0/d1 from p0, p1 or p2: the transitions only pick
+    // the point (nsel), the division is done once for all worlds of the warp after them
+    enum { N_NONE = 0, N_P0, N_P1, N_P2 };
+    int nsel = N_NONE;
+    bool fixed_point_check = false;
     if (state == LS_P0) {
       p0 = pe;
-      a_eval = p0.alpha - p0.d0 / p0.d1;
+      nsel = N_P0;
       state = LS_P1;
     } else if (state == LS_P1) {
       p1 = pe;
@@ -135,13 +142,13 @@ TK_DEV double primal_search(const DM& m, WS& w, const Grp<G, NV>& g, double gaus
         TK_BRACKET(p1, c0, b1) TK_BRACKET(p1, c1, b1) TK_BRACKET(p1, c2, b1)
         TK_BRACKET(p2, c0, b2) TK_BRACKET(p2, c1, b2) TK_BRACKET(p2, c2, b2)
 #undef TK_BRACKET
-        if (b1) { a_eval = p1.alpha - p1.d0 / p1.d1; state = LS_UB1; }
-        else if (b2) { a_eval = p2.alpha - p2.d0 / p2.d1; state = LS_UB2; }
+        if (b1) { nsel = N_P1; state = LS_UB1; }
+        else if (b2) { nsel = N_P2; state = LS_UB2; }
         else { result = pe.alpha; state = LS_DONE; }
       }
     } else if (state == LS_UB1) {
       p1next = pe;
-      if (b2) { a_eval = p2.alpha - p2.d0 / p2.d1; state = LS_UB2; }
+      if (b2) { nsel = N_P2; state = LS_UB2; }
       else ctl = C_BRACKET;
     } else {  // LS_UB2
       p2next = pe;
@@ -151,18 +158,19 @@ TK_DEV double primal_search(const DM& m, WS& w, const Grp<G, NV>& g, double gaus
       if (p1.d0 * dir <= -gtol && lsiter < LS) {
         p2 = p1;
         p2update = 1;
-        a_eval = p1.alpha - p1.d0 / p1.d1;
+        nsel = N_P1;
+        fixed_point_check = true;
+        state = LS_ONESIDED;
         // Fixed point of the Newton iteration in floating point (the step no longer changes alpha): every further
         // evaluation would return p1 again, the loop would spin until lsiter reaches the cap and then return
         // p1.alpha.  With the FD solver options (tolerance 0 => gtol 0) 4 of 5 evaluations of the reference schedule
-        // are such repeats (measured with an instrumented oracle); skipping them changes no result bit.
-        if (a_eval == p1.alpha) { result = p1.alpha; state = LS_DONE; }
-        else state = LS_ONESIDED;
+        // are such repeats (measured with an instrumented oracle); skipping them changes no result bit.  (The test
+        // follows the division below.)
       } else ctl = C_AFTER;
     }
     if (ctl == C_AFTER) {
       if (lsiter >= LS || !p2update) { result = p1.alpha; state = LS_DONE; }
-      else { p2next = p1; a_eval = p1.alpha - p1.d0 / p1.d1; state = LS_P1NEXT; }
+      else { p2next = p1; nsel = N_P1; state = LS_P1NEXT; }
     }
     if (ctl == C_BRACKET) {
       if (lsiter < LS) { a_eval = 0.5 * (p1.alpha + p2.alpha); state = LS_MID; }
@@ -173,6 +181,13 @@ TK_DEV double primal_search(const DM& m, WS& w, const Grp<G, NV>& g, double gaus
       else if (p2.cost <= p1.cost && p2.cost < p0.cost) result = p2.alpha;
       else result = 0.0;
       state = LS_DONE;
+    }
+    if (nsel != N_NONE) {
+      const double al = nsel == N_P0 ? p0.alpha : (nsel == N_P1 ? p1.alpha : p2.alpha);
+      const double d0 = nsel == N_P0 ? p0.d0 : (nsel == N_P1 ? p1.d0 : p2.d0);
+      const double d1 = nsel == N_P0 ? p0.d1 : (nsel == N_P1 ? p1.d1 : p2.d1);
+      a_eval = al - d0 / d1;
+      if (fixed_point_check && a_eval == p1.alpha) { result = p1.alpha; state = LS_DONE; }
     }
   }
   return result;

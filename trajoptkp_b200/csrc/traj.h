@@ -43,10 +43,14 @@ int fast_ecap(const DM& dm);
   if ((G) == 8 && (NVV) == 9) { LAUNCH(8, 9) }                                          \
   else if ((G) == 8 && (NVV) == 2) { LAUNCH(8, 2) }                                     \
   else if ((G) == 32 && (NVV) == 9) { LAUNCH(32, 9) }                                   \
+  else if ((G) == 16 && (NVV) == 9) { LAUNCH(16, 9) }                                   \
   else if ((G) == 4) { LAUNCH(4, 0) }                                                   \
   else if ((G) == 8) { LAUNCH(8, 0) }                                                   \
   else if ((G) == 16) { LAUNCH(16, 0) }                                                 \
   else { LAUNCH(32, 0) }
+// register budget of the world kernels: 128-thread blocks per SM that __launch_bounds__ asks for (2 -> 255 registers,
+// 8 warps; 16-lane groups trade registers for residency: 3 -> 168 registers, 12 warps)
+constexpr int reg_blocks(int lanes) { return lanes == 16 ? 3 : 2; }
 inline bool needs_redo_pass(const DM& dm) { return fast_ecap(dm) < dm.maxefc; }
 // returns TOKP_OK or TOKP_ERR_UNSUPPORTED (workspace does not fit shared memory)
 int plan_launch(const DM& dm, int G, int pass, LaunchPlan* out);

@@ -46,6 +46,9 @@ enum {
   TOKP_KP_VELOCITY_CHANGE = 4
 };
 
+/* Optimiser::filteringMethod "none" | "low_pass" | "FIR" (include/Optimiser/Optimiser.h:173) */
+enum { TOKP_FILTER_NONE = 0, TOKP_FILTER_LOW_PASS = 1, TOKP_FILTER_FIR = 2 };
+
 /* mjSTAGE_* as used by mj_stepSkip (Differentiator.cpp:118,253,357) */
 enum { TOKP_STAGE_NONE = 0, TOKP_STAGE_POS = 1, TOKP_STAGE_VEL = 2 };
 
@@ -125,7 +128,17 @@ int tokp_interpolate(tokp_traj* tr);
 /* Optimiser::ComputeCostDerivatives (Optimiser.cpp:197-236): residual FD (Differentiator.cpp:464-663) for
  * t = 0..T and Gauss-Newton l_x, l_xx, l_u, l_uu (ModelTranslator.cpp:552-583), terminal at T-1 */
 int tokp_cost_derivs(tokp_traj* tr, int central_diff, double eps);
-/* Optimiser::GenerateDerivatives (Optimiser.cpp:80-108): the four calls above in order */
+/* Differentiator::ResidualDerivatives (Differentiator.cpp:464-663) exact drop-in for one (b, t), t = 0..T:
+ * r_x[nx][nr] and r_u[m][nr] (entry [column][residual], i.e. the reference's r_x[j](column, 0)); r_u may be NULL */
+int tokp_residual_derivs(tokp_traj* tr, int b, int t, int central_diff, double eps, double* r_x, double* r_u);
+/* Optimiser::filteringMethod / lowPassACoefficient / setFIRFilter (include/Optimiser/Optimiser.h:151,173,219-220):
+ * method TOKP_FILTER_*; fir == NULL keeps the current taps (default {0.1, 0.15, 0.5, 0.15, 0.1}); at most 16 taps */
+int tokp_traj_set_filter(tokp_traj* tr, int method, double low_pass_a, const double* fir, int nfir);
+/* Optimiser::FilterDynamicsMatrices (Optimiser.cpp:340-406): filters the velocity rows of A[0..T-1] along t in place;
+ * TOKP_ERR_STATE when no method is set (the reference prints "Filtering method not recognised") */
+int tokp_filter_dynamics(tokp_traj* tr);
+/* Optimiser::GenerateDerivatives (Optimiser.cpp:80-108): key-points, dynamics derivatives, interpolation, cost
+ * derivatives and (when a filter is set) FilterDynamicsMatrices, in the reference's order */
 int tokp_generate_derivatives(tokp_traj* tr);
 /* iLQR::BackwardsPassQuuRegularisation (iLQR.cpp:535-634): lambda[B] in; ok[B], delta_J[B] out */
 int tokp_backward_pass(tokp_traj* tr, const double* lambda, int* ok, double* delta_J);

@@ -188,6 +188,13 @@ ILQR* ok_ilqr_create(const Model* m, const TaskDesc* td, int T, int threads) {
 }
 void ok_ilqr_destroy(ILQR* o) { delete o; }
 void ok_ilqr_set_lambda(ILQR* o, double lambda) { o->lambda = lambda; }
+void ok_ilqr_set_filter(ILQR* o, int method, double low_pass_a, const double* fir, int nfir) {
+  o->filter_method = method;
+  o->low_pass_a = low_pass_a;
+  if (fir && nfir > 0) o->fir.assign(fir, fir + nfir);
+}
+void ok_ilqr_filter(ILQR* o) { o->filter_dynamics_matrices(); }
+void ok_ilqr_set_A(ILQR* o, const double* A) { std::memcpy(o->A.data(), A, sizeof(double) * o->A.size()); }
 void ok_ilqr_set_fd_model_opts(ILQR* o, int flag) { o->fd_use_model_opts = flag != 0; }
 double ok_ilqr_rollout(ILQR* o, const double* snapshot0, const double* U) {
   o->old_cost = o->rollout_trajectory(snapshot0, U);

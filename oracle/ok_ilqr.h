@@ -266,6 +266,36 @@ struct ILQR {
     }
   }
 
+  // Optimiser::FilterDynamicsMatrices (Optimiser.cpp:340-372): every entry of the velocity rows of A is treated as a
+  // signal over t = 0..T-1 and replaced by its filtered version.  low_pass (Optimiser.cpp:374-390):
+  // y_t = (1-a) y_{t-1} + a (x_t + x_{t-1})/2 with y_{-1} = x_{-1} = x_0.  FIR (Optimiser.cpp:392-406): causal
+  // convolution, taps that would reach before t = 0 are dropped.
+  int filter_method = 0;  // 0 none, 1 low_pass, 2 FIR
+  double low_pass_a = 0.25;                               // include/Optimiser/Optimiser.h:219
+  std::vector<double> fir = {0.1, 0.15, 0.5, 0.15, 0.1};  // include/Optimiser/Optimiser.h:220
+  void filter_dynamics_matrices() {
+    std::vector<double> x(T), y(T);
+    for (int row = n; row < nx; row++)
+      for (int col = 0; col < nx; col++) {
+        for (int t = 0; t < T; t++) x[t] = A[(size_t)t * nx * nx + (size_t)col * nx + row];
+        if (filter_method == 1) {
+          double yprev = x[0], xprev = x[0];
+          for (int t = 0; t < T; t++) {
+            y[t] = ((1 - low_pass_a) * yprev) + low_pass_a * ((x[t] + xprev) / 2);
+            xprev = x[t];
+            yprev = y[t];
+          }
+        } else {
+          for (int t = 0; t < T; t++) {
+            double acc = 0;
+            for (int j = 0; j < (int)fir.size() && j <= t; j++) acc += x[t - j] * fir[j];
+            y[t] = acc;
+          }
+        }
+        for (int t = 0; t < T; t++) A[(size_t)t * nx * nx + (size_t)col * nx + row] = y[t];
+      }
+  }
+
   // Optimiser::GenerateDerivatives
   void generate_derivatives() {
     generate_keypoints();
@@ -277,6 +307,7 @@ struct ILQR {
     double avg = 0.0;
     for (int i = 0; i < n; i++) avg += last_percentages[i];
     pct_derivs.push_back(avg / n);
+    if (filter_method != 0) filter_dynamics_matrices();
   }
 
   // iLQR::BackwardsPassQuuRegularisation

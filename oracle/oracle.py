@@ -88,6 +88,9 @@ def lib():
         L.ok_ilqr_destroy.argtypes = [C.c_void_p]
         L.ok_ilqr_set_lambda.argtypes = [C.c_void_p, C.c_double]
         L.ok_ilqr_set_fd_model_opts.argtypes = [C.c_void_p, C.c_int]
+        L.ok_ilqr_set_filter.argtypes = [C.c_void_p, C.c_int, C.c_double, _dp, C.c_int]
+        L.ok_ilqr_filter.argtypes = [C.c_void_p]
+        L.ok_ilqr_set_A.argtypes = [C.c_void_p, _dp]
         L.ok_ilqr_rollout.restype = C.c_double
         L.ok_ilqr_rollout.argtypes = [C.c_void_p, _dp, _dp]
         for f in ("ok_ilqr_generate_keypoints", "ok_ilqr_dynamics_derivs", "ok_ilqr_generate_derivatives"):
@@ -263,6 +266,18 @@ class ILQR:
 
     def set_lambda(self, lam):
         lib().ok_ilqr_set_lambda(self.h, lam)
+
+    def set_filter(self, method, low_pass_a=0.25, fir=(0.1, 0.15, 0.5, 0.15, 0.1)):
+        """Optimiser::filteringMethod: 0 none, 1 low_pass, 2 FIR."""
+        fir = np.ascontiguousarray(fir, dtype=np.float64)
+        lib().ok_ilqr_set_filter(self.h, int(method), float(low_pass_a), _d(fir), len(fir))
+
+    def filter(self):
+        lib().ok_ilqr_filter(self.h)
+
+    def set_A(self, A):
+        A = np.ascontiguousarray(A, dtype=np.float64)
+        lib().ok_ilqr_set_A(self.h, _d(A))
 
     def rollout(self, snap0, U):
         snap0 = np.ascontiguousarray(snap0, dtype=np.float64)

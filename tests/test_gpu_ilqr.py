@@ -147,3 +147,75 @@ def test_optimise_final_cost(built, name, T, max_it):
         assert abs(stats[b, 1] - sc["new_cost"]) <= 0.01 * abs(sc["new_cost"]), (stats[b], sc)   # final cost within 1 %
         assert int(stats[b, 2]) == int(sc["num_iterations"])
     assert stats[0, 1] < stats[0, 0]
+
+
+@pytest.mark.parametrize("method", ["low_pass", "FIR"])
+@pytest.mark.parametrize("name", ["acrobot", "walker_run"])
+def test_filter_dynamics_bit_exact(built, name, method):
+    """Optimiser::FilterDynamicsMatrices (a17): device kernel == oracle == numpy restatement, bit for bit, on the same A;
+    batch entries are filtered independently."""
+    import filter_numpy as fnp
+    T = 33
+    tc, snap0, U, _ = _setup(name, T, capi.KP_SET_INTERVAL, 2, 2)
+    tr = capi.Traj(tc, T, 2)
+    rng = np.random.default_rng(11)
+    A = rng.standard_normal((2, T * (2 * tc.n) ** 2))
+    for b in range(2):
+        tr.set(b, "A", A[b])
+    with pytest.raises(capi.TokpError):
+        tr.filter_dynamics()                     # "Filtering method not recognised": no method set
+    tr.set_filter(method)
+    tr.filter_dynamics()
+    ref = oracle.ILQR(oracle_model(tc), oracle_task(tc), T, threads=1)
+    ref.set_filter(capi.Traj.FILTERS[method])
+    for b in range(2):
+        ref.set_A(A[b])
+        ref.filter()
+        got = tr.get(b, "A")
+        assert np.array_equal(got, ref.get("A"))
+        assert np.array_equal(got, fnp.filter_dynamics(A[b], tc.n, method))
+    # custom coefficients
+    tr.set(0, "A", A[0])
+    tr.set_filter("FIR", fir=[0.3, 0.4, 0.3])
+    tr.filter_dynamics()
+    assert np.array_equal(tr.get(0, "A"), fnp.filter_dynamics(A[0], tc.n, "FIR", taps=(0.3, 0.4, 0.3)))
+
+
+def test_generate_derivatives_with_filter(built):
+    """GenerateDerivatives applies the filter after the cost derivatives (Optimiser.cpp:104-107)."""
+    import filter_numpy as fnp
+    T = 30
+    tc, snap0, U, tr = _setup("acrobot", T, capi.KP_SET_INTERVAL, 2, 2)
+    tr.rollout(snap0, U)
+    tr.generate_derivatives()
+    A_plain, lxx = tr.get(0, "A"), tr.get(0, "l_xx")
+    tr.set_filter("low_pass", low_pass_a=0.25)
+    tr.generate_derivatives()
+    assert np.array_equal(tr.get(0, "A"), fnp.filter_dynamics(A_plain, tc.n, "low_pass"))
+    assert np.array_equal(tr.get(0, "l_xx"), lxx)
+    tr.set_filter("none")
+    tr.generate_derivatives()
+    assert np.array_equal(tr.get(0, "A"), A_plain)
+
+
+@pytest.mark.parametrize("name", ["acrobot", "walker_run"])
+def test_residual_derivs_per_call(built, name):
+    """Differentiator::ResidualDerivatives drop-in (a2): one (b, t) per call == the batched phase == the oracle."""
+    T = 20
+    tc, snap0, U, tr = _setup(name, T, capi.KP_SET_INTERVAL, 2, 2)
+    tr.rollout(snap0, U)
+    tr.cost_derivs()
+    rx_all = tr.get(0, "r_x").reshape(T + 1, 2 * tc.n, tc.nr)
+    ru_all = tr.get(0, "r_u").reshape(T + 1, tc.m, tc.nr)
+    om, ot = oracle_model(tc), oracle_task(tc)
+    for t in (0, 7, T):
+        rx, ru = tr.residual_derivs(0, t)
+        assert np.array_equal(rx, rx_all[t]) and np.array_equal(ru, ru_all[t])
+        rx_ref, ru_ref = oracle.residual_derivs(om, ot, tr.get_snapshot(0, t))
+        assert rel_fro(rx.ravel(), np.asarray(rx_ref).T.ravel()) < 1e-9
+        assert rel_fro(ru.ravel(), np.asarray(ru_ref).T.ravel()) < 1e-9
+    # forward differences estimate the same derivative (identical for residuals linear in the state)
+    rx_f, _ = tr.residual_derivs(0, 7, central=False)
+    assert np.allclose(rx_f, rx_all[7], atol=1e-4)
+    with pytest.raises(capi.TokpError):
+        tr.residual_derivs(0, T + 1)

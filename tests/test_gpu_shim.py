@@ -34,9 +34,21 @@ def test_shim_call_sequence_matches_ctypes_and_oracle(built):
     assert np.array_equal(pct[0], out["percentages"])
     assert out["cols_vs_batched_maxabs"] == 0.0
     assert out["interpolation_identity_exact"] == 1
+    # Differentiator::ResidualDerivatives through the shim == ctypes path at the same saved state
+    tr.cost_derivs()
+    rx5 = tr.get(0, "r_x").reshape(T + 1, 4, tc.nr)[5]          # [column][residual]
+    ru5 = tr.get(0, "r_u").reshape(T + 1, 1, tc.nr)[5]
+    assert np.array_equal(np.array(out["r_x5"]).reshape(tc.nr, 4), rx5.T)
+    assert np.array_equal(np.array(out["r_u5"]), ru5[0])
     tr.generate_derivatives()
     A5 = tr.get(0, "A").reshape(T, 4, 4)[5]
     assert np.array_equal(A5.ravel(), np.array(out["A5"]))
+    # Optimiser::FilterDynamicsMatrices through the shim == numpy restatement of the reference filters
+    import filter_numpy as fnp
+    assert out["filter_position_rows_untouched"] == 1
+    assert np.array_equal(np.array(out["A_lowpass_21"]), fnp.low_pass(np.array(out["A_raw_21"])))
+    assert np.array_equal(np.array(out["A_fir_32"]), fnp.fir(np.array(out["A_raw_32"])))
+    assert np.array_equal(np.array(out["A_raw_21"]), tr.get(0, "A").reshape(T, 4, 4)[:, 1, 2])
     # oracle: Differentiator::DynamicsDerivatives at the same saved state
     om, ot = oracle_model(tc), oracle_task(tc)
     A_ref, _ = oracle.dynamics_derivs(om, ot, tr.get_snapshot(0, 5), [0, 1])

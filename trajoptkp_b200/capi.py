@@ -84,6 +84,9 @@ def lib():
         L.tokp_interpolate.argtypes = [vp]
         L.tokp_cost_derivs.argtypes = [vp, C.c_int, C.c_double]
         L.tokp_generate_derivatives.argtypes = [vp]
+        L.tokp_residual_derivs.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_double, _dp, _dp]
+        L.tokp_traj_set_filter.argtypes = [vp, C.c_int, C.c_double, _dp, C.c_int]
+        L.tokp_filter_dynamics.argtypes = [vp]
         L.tokp_backward_pass.argtypes = [vp, _dp, _ip, _dp]
         L.tokp_forward_pass.argtypes = [vp, _dp, C.c_int, _dp]
         L.tokp_accept.argtypes = [vp, C.c_int, C.c_int]
@@ -246,6 +249,27 @@ class Traj:
 
     def generate_derivatives(self):
         check(lib().tokp_generate_derivatives(self.h))
+
+    def residual_derivs(self, b, t, central=True, eps=1e-6):
+        """Differentiator::ResidualDerivatives at (b, t): r_x [nx][nr], r_u [m][nr]."""
+        rx = np.zeros((self.nx, self.nr))
+        ru = np.zeros((max(self.m, 1), self.nr))
+        check(lib().tokp_residual_derivs(self.h, b, t, int(central), eps, _d(rx), _d(ru)))
+        return rx, ru[:self.m]
+
+    FILTERS = {"none": 0, "low_pass": 1, "FIR": 2}
+
+    def set_filter(self, method, low_pass_a=0.25, fir=None):
+        """Optimiser::filteringMethod ("none" | "low_pass" | "FIR"), lowPassACoefficient, setFIRFilter."""
+        code = self.FILTERS[method] if isinstance(method, str) else int(method)
+        if fir is None:
+            check(lib().tokp_traj_set_filter(self.h, code, float(low_pass_a), None, 0))
+        else:
+            f = np.ascontiguousarray(fir, dtype=np.float64)
+            check(lib().tokp_traj_set_filter(self.h, code, float(low_pass_a), _d(f), len(f)))
+
+    def filter_dynamics(self):
+        check(lib().tokp_filter_dynamics(self.h))
 
     def backward_pass(self, lam):
         lam = np.ascontiguousarray(np.broadcast_to(np.asarray(lam, dtype=np.float64), (self.B,)))

@@ -12,9 +12,10 @@ namespace tokp {
 // one thread per (b, t), t = 0..T: literal residual finite differences
 __global__ void k_resid_derivs(DM dm, TaskDev tk_, const double* __restrict__ snap, const double* __restrict__ target,
                                double* __restrict__ rx, double* __restrict__ ru, int B, int T, int SD, int central, double eps,
-                               double* __restrict__ scratch) {
+                               double* __restrict__ scratch, int first, int count) {
   int gid = blockIdx.x * blockDim.x + threadIdx.x;
-  if (gid >= B * (T + 1)) return;
+  if (gid >= count) return;
+  gid += first;  // (b, t) pair first .. first+count-1
   int b = gid / (T + 1);
   int nq = dm.nq, nv = dm.nv, nu = dm.nu, n = tk_.n, m = tk_.m, nr = tk_.nr, nx = 2 * n;
   const double* s = snap + (size_t)gid * SD;
@@ -375,12 +376,60 @@ static int cost_derivs(tokp_traj* tr, int central, double eps) {
   int B = tr->B, T = tr->T;
   if (tr->nr > kMaxResid) { set_error("too many residuals"); return TOKP_ERR_UNSUPPORTED; }
   k_resid_derivs<<<(B * (T + 1) + 63) / 64, 64, 0, tr->stream>>>(tr->dm, tr->task, tr->snap, tr->target, tr->rx, tr->ru, B, T,
-                                                                 tr->SD, central, eps, tr->fd_out);
+                                                                 tr->SD, central, eps, tr->fd_out, 0, B * (T + 1));
   int per = tr->nx + tr->nx * tr->nx + tr->m + tr->m * tr->m;
   long long tot = (long long)B * T * per;
   k_cost_derivs<<<(int)((tot + 255) / 256), 256, 0, tr->stream>>>(tr->task, tr->resid, tr->rx, tr->ru, tr->lx, tr->lxx, tr->lu,
                                                                     tr->luu, B, T);
   g_launches += 2;
+  TOKP_CUDA(cudaGetLastError());
+  return TOKP_OK;
+}
+
+// Optimiser::FilterDynamicsMatrices (Optimiser.cpp:340-406): one thread per (b, velocity row, column) walks the entry's
+// signal over t = 0..T-1.  low_pass is a first-order recursion (sequential in t); FIR is a short causal convolution,
+// computed back to front so that it can run in place.
+struct FilterArgs {
+  int method, nfir;
+  double a;
+  double fir[16];
+};
+
+__global__ void k_filter(double* __restrict__ A, int B, int T, int n, FilterArgs f) {
+  int nx = 2 * n;
+  int gid = blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= B * n * nx) return;
+  int b = gid / (n * nx);
+  int e = gid - b * n * nx;
+  int col = e / n, row = n + (e - col * n);
+  double* x = A + (size_t)b * T * nx * nx + (size_t)col * nx + row;
+  const size_t st = (size_t)nx * nx;
+  if (f.method == TOKP_FILTER_LOW_PASS) {
+    double yprev = x[0], xprev = x[0];
+    for (int t = 0; t < T; t++) {
+      double xt = x[t * st];
+      double y = __dadd_rn(__dmul_rn(1 - f.a, yprev), __dmul_rn(f.a, __dadd_rn(xt, xprev) / 2));
+      x[t * st] = y;
+      xprev = xt;
+      yprev = y;
+    }
+  } else {
+    for (int t = T - 1; t >= 0; t--) {
+      double acc = 0;
+      for (int j = 0; j < f.nfir && j <= t; j++) acc = __dadd_rn(acc, __dmul_rn(x[(t - j) * st], f.fir[j]));
+      x[t * st] = acc;
+    }
+  }
+}
+
+static int filter_dynamics(tokp_traj* tr) {
+  if (tr->filter_method == TOKP_FILTER_NONE) return TOKP_OK;
+  FilterArgs f;
+  f.method = tr->filter_method; f.nfir = tr->nfir; f.a = tr->low_pass_a;
+  for (int i = 0; i < 16; i++) f.fir[i] = tr->fir[i];
+  int tot = tr->B * tr->n * tr->nx;
+  k_filter<<<(tot + 127) / 128, 128, 0, tr->stream>>>(tr->A, tr->B, tr->T, tr->n, f);
+  g_launches++;
   TOKP_CUDA(cudaGetLastError());
   return TOKP_OK;
 }
@@ -396,7 +445,9 @@ static int generate_derivatives(tokp_traj* tr) {
   }
   rc = interpolate(tr);
   if (rc) return rc;
-  return cost_derivs(tr, 1, 1e-6);
+  rc = cost_derivs(tr, 1, 1e-6);
+  if (rc) return rc;
+  return filter_dynamics(tr);  // Optimiser.cpp:104-107: after the cost derivatives, before the backward pass
 }
 
 static int backward_pass(tokp_traj* tr) {
@@ -482,6 +533,41 @@ extern "C" int tokp_cost_derivs(tokp_traj* tr, int central_diff, double eps) {
   if (!tr->have_rollout) { set_error("tokp_cost_derivs: no nominal trajectory yet"); return TOKP_ERR_STATE; }
   int rc = cost_derivs(tr, central_diff, eps);
   if (rc) return rc;
+  TOKP_CUDA(cudaStreamSynchronize(tr->stream));
+  return TOKP_OK;
+}
+
+extern "C" int tokp_traj_set_filter(tokp_traj* tr, int method, double low_pass_a, const double* fir, int nfir) {
+  if (!tr || method < TOKP_FILTER_NONE || method > TOKP_FILTER_FIR || nfir < 0 || nfir > 16) {
+    set_error("tokp_traj_set_filter: bad argument (method 0..2, at most 16 FIR taps)");
+    return TOKP_ERR_ARG;
+  }
+  tr->filter_method = method;
+  tr->low_pass_a = low_pass_a;
+  if (fir && nfir > 0) { tr->nfir = nfir; for (int i = 0; i < nfir; i++) tr->fir[i] = fir[i]; }
+  return TOKP_OK;
+}
+
+extern "C" int tokp_filter_dynamics(tokp_traj* tr) {
+  if (!tr) { set_error("tokp_filter_dynamics: null trajectory"); return TOKP_ERR_ARG; }
+  if (tr->filter_method == TOKP_FILTER_NONE) { set_error("tokp_filter_dynamics: filtering method not recognised (none set)"); return TOKP_ERR_STATE; }
+  int rc = filter_dynamics(tr);
+  if (rc) return rc;
+  TOKP_CUDA(cudaStreamSynchronize(tr->stream));
+  return TOKP_OK;
+}
+
+extern "C" int tokp_residual_derivs(tokp_traj* tr, int b, int t, int central_diff, double eps, double* r_x, double* r_u) {
+  if (!tr || b < 0 || b >= tr->B || t < 0 || t > tr->T || !(eps > 0) || !r_x) { set_error("tokp_residual_derivs: bad argument"); return TOKP_ERR_ARG; }
+  if (tr->nr > kMaxResid) { set_error("too many residuals"); return TOKP_ERR_UNSUPPORTED; }
+  int first = b * (tr->T + 1) + t;
+  k_resid_derivs<<<1, 64, 0, tr->stream>>>(tr->dm, tr->task, tr->snap, tr->target, tr->rx, tr->ru, tr->B, tr->T, tr->SD,
+                                           central_diff, eps, tr->fd_out, first, 1);
+  g_launches++;
+  TOKP_CUDA(cudaGetLastError());
+  TOKP_CUDA(cudaMemcpyAsync(r_x, tr->rx + (size_t)first * tr->nr * tr->nx, (size_t)tr->nr * tr->nx * 8, cudaMemcpyDeviceToHost, tr->stream));
+  if (r_u && tr->m)
+    TOKP_CUDA(cudaMemcpyAsync(r_u, tr->ru + (size_t)first * tr->nr * tr->m, (size_t)tr->nr * tr->m * 8, cudaMemcpyDeviceToHost, tr->stream));
   TOKP_CUDA(cudaStreamSynchronize(tr->stream));
   return TOKP_OK;
 }

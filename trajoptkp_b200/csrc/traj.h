@@ -103,4 +103,9 @@ struct tokp_traj {
   double timers[3] = {0, 0, 0};
   int64_t counters[4] = {0, 0, 0, 0};
   std::vector<double> h_stage;  // host staging
+  // Optimiser::filteringMethod / lowPassACoefficient / FIRCoefficients (include/Optimiser/Optimiser.h:173,219-220)
+  int filter_method = 0;  // TOKP_FILTER_*
+  double low_pass_a = 0.25;
+  int nfir = 5;
+  double fir[16] = {0.1, 0.15, 0.5, 0.15, 0.1};
 };

@@ -79,6 +79,40 @@ int main(int argc, char** argv) {
         if (A2[1](i, j) != opt.A[0](i, j) + 1 * add || A2[2](i, j) != opt.A[0](i, j) + 2 * add) exact = 0;
       }
     std::printf("\"interpolation_identity_exact\": %d,\n", exact);
+    // Differentiator::ResidualDerivatives drop-in at t = 5 (r_x[j] nx x 1, r_u[j] m x 1)
+    std::vector<MatrixXd> r_x, r_u;
+    diff->ResidualDerivatives(r_x, r_u, 5, 0, true, 1e-6);
+    std::vector<double> rxf, ruf;
+    for (auto& r : r_x) for (int c = 0; c < 4; c++) rxf.push_back(r(c, 0));
+    for (auto& r : r_u) ruf.push_back(r(0, 0));
+    print_vec("r_x5", rxf);
+    print_vec("r_u5", ruf);
+    // Optimiser::FilterDynamicsMatrices on a copy of A (low_pass, then FIR with the default taps)
+    {
+      std::vector<MatrixXd> keep = opt.A;
+      opt.filteringMethod = "low_pass";
+      opt.FilterDynamicsMatrices();
+      std::vector<double> lp;
+      for (int t = 0; t < T; t++) lp.push_back(opt.A[t](2, 1));
+      print_vec("A_lowpass_21", lp);
+      int untouched = 1;
+      for (int t = 0; t < T; t++) for (int j = 0; j < 4; j++) if (opt.A[t](0, j) != keep[t](0, j) || opt.A[t](1, j) != keep[t](1, j)) untouched = 0;
+      std::printf("\"filter_position_rows_untouched\": %d,\n", untouched);
+      opt.A = keep;
+      opt.filteringMethod = "FIR";
+      opt.FilterDynamicsMatrices();
+      std::vector<double> fr;
+      for (int t = 0; t < T; t++) fr.push_back(opt.A[t](3, 2));
+      print_vec("A_fir_32", fr);
+      std::vector<double> raw;
+      for (int t = 0; t < T; t++) raw.push_back(keep[t](3, 2));
+      print_vec("A_raw_32", raw);
+      std::vector<double> raw21;
+      for (int t = 0; t < T; t++) raw21.push_back(keep[t](2, 1));
+      print_vec("A_raw_21", raw21);
+      opt.A = keep;
+      opt.filteringMethod = "none";
+    }
     opt.lambda = 0.1;
     auto Uopt = opt.Optimise(&start, U0, 3, 1, T);
     std::vector<double> uo;

@@ -11,6 +11,7 @@
 // (define TOKP_SHIM_USE_EIGEN to use the real one); errors throw std::runtime_error instead of exit(1).
 #pragma once
 #include <cstring>
+#include <iostream>
 #include <memory>
 #include <stdexcept>
 #include <string>

@@ -102,6 +102,24 @@ class Differentiator {
     tokp_shim::check(tokp_dynamics_derivs_cols(traj->h, 0, data_index, cols.data(), (int)cols.size(), central_diff ? 1 : 0,
                                                eps, A.data(), A.rows(), B.data(), B.rows()), "DynamicsDerivatives");
   }
+  // Differentiator::ResidualDerivatives (Differentiator.cpp:464-663): r_x[j] is nx x 1 and r_u[j] is m x 1 for every
+  // residual j, finite differences of MT::Residuals at saved_systems_state_list[data_index]
+  void ResidualDerivatives(std::vector<MatrixXd>& r_x, std::vector<MatrixXd>& r_u, int data_index, int /*tid*/,
+                           bool central_diff, double eps) {
+    const int nx = 2 * model_translator->dof, m = model_translator->num_ctrl;
+    const int nr = (int)model_translator->resid_target.size();
+    const auto& s = MuJoCo_helper->saved_systems_state_list.at(data_index)->v;
+    tokp_shim::check(tokp_traj_set_snapshot(traj->h, 0, data_index, s.data()), "set_snapshot");
+    std::vector<double> rx((size_t)nx * nr), ru((size_t)(m ? m : 1) * nr);
+    tokp_shim::check(tokp_residual_derivs(traj->h, 0, data_index, central_diff ? 1 : 0, eps, rx.data(), ru.data()),
+                     "ResidualDerivatives");
+    r_x.assign(nr, MatrixXd(nx, 1));
+    r_u.assign(nr, MatrixXd(m, 1));
+    for (int j = 0; j < nr; j++) {
+      for (int c = 0; c < nx; c++) r_x[j](c, 0) = rx[(size_t)c * nr + j];
+      for (int c = 0; c < m; c++) r_u[j](c, 0) = ru[(size_t)c * nr + j];
+    }
+  }
   std::shared_ptr<ModelTranslator> model_translator;
   std::shared_ptr<MuJoCoHelper> MuJoCo_helper;
   std::shared_ptr<TrajHandle> traj;

@@ -17,6 +17,28 @@ class Optimiser {
                                          int min_iterations, int horizon_length) = 0;
   // Optimiser::SetCurrentKeypointMethod (Optimiser.cpp:47-50)
   void SetCurrentKeypointMethod(keypoint_method m) { keypoint_generator->SetKeypointMethod(m); }
+  // Optimiser::setFIRFilter (Optimiser.cpp:408-414)
+  void setFIRFilter(std::vector<double> _FIRCoefficients) { FIRCoefficients = _FIRCoefficients; }
+  // Optimiser::FilterDynamicsMatrices (Optimiser.cpp:340-372) on the public A: the velocity rows are filtered along t
+  // on the device; an unknown filteringMethod is reported as in the reference and leaves A untouched
+  void FilterDynamicsMatrices() {
+    tokp_traj* h = differentiator->traj->h;
+    if (PushFilter() == TOKP_FILTER_NONE) { std::cerr << "Filtering method not recognised" << std::endl; return; }
+    int nx = 2 * dof, T = (int)A.size();
+    std::vector<double> a((size_t)T * nx * nx);
+    for (int t = 0; t < T; t++) std::memcpy(&a[(size_t)t * nx * nx], A[t].data(), sizeof(double) * nx * nx);
+    tokp_shim::check(tokp_traj_set(h, 0, "A", a.data(), (int)a.size()), "set A");
+    tokp_shim::check(tokp_filter_dynamics(h), "FilterDynamicsMatrices");
+    if (tokp_traj_get(h, 0, "A", a.data(), (int)a.size()) != (int)a.size()) throw std::runtime_error("FilterDynamicsMatrices: readback of A failed");
+    for (int t = 0; t < T; t++) std::memcpy(A[t].data(), &a[(size_t)t * nx * nx], sizeof(double) * nx * nx);
+  }
+  // filteringMethod / lowPassACoefficient / FIRCoefficients -> device handle; returns the TOKP_FILTER_* code in force
+  int PushFilter() {
+    int code = filteringMethod == "low_pass" ? TOKP_FILTER_LOW_PASS : (filteringMethod == "FIR" ? TOKP_FILTER_FIR : TOKP_FILTER_NONE);
+    tokp_shim::check(tokp_traj_set_filter(differentiator->traj->h, code, lowPassACoefficient, FIRCoefficients.data(),
+                                          (int)FIRCoefficients.size()), "set_filter");
+    return code;
+  }
 
   // public storage, names as in include/Optimiser/Optimiser.h:166-242
   std::vector<MatrixXd> A, B, X_old, U_old, l_x, l_xx, l_u, l_uu;
@@ -25,6 +47,9 @@ class Optimiser {
   double lambda = 0.1, new_cost = 0, old_cost = 0;
   int num_iterations = 0, dof = 0, num_ctrl = 0, horizon_length = 0;
   bool verbose_output = false;
+  std::string filteringMethod = "none";                               // include/Optimiser/Optimiser.h:173
+  double lowPassACoefficient = 0.25;                                  // :219
+  std::vector<double> FIRCoefficients = {0.1, 0.15, 0.5, 0.15, 0.1};  // :220
   std::shared_ptr<KeypointGenerator> keypoint_generator;
   std::shared_ptr<ModelTranslator> activeModelTranslator;
   std::shared_ptr<MuJoCoHelper> MuJoCo_helper;
@@ -60,6 +85,7 @@ class iLQR : public Optimiser {
   }
   // Optimiser::GenerateDerivatives (Optimiser.cpp:80-108)
   void GenerateDerivatives() {
+    PushFilter();
     tokp_shim::check(tokp_generate_derivatives(differentiator->traj->h), "GenerateDerivatives");
     keypoint_generator->PullAB(A, B);
   }
@@ -69,6 +95,7 @@ class iLQR : public Optimiser {
     if (horizon != horizon_length) throw std::runtime_error("iLQR::Optimise: horizon differs from Resize()");
     std::vector<double> U = Flatten(initial_controls), Uo((size_t)horizon * num_ctrl);
     double stats[8];
+    PushFilter();
     tokp_shim::check(tokp_optimise(differentiator->traj->h, d->v.data(), U.data(), max_iterations, min_iterations, &lambda,
                                    Uo.data(), stats), "Optimise");
     initial_cost = stats[0]; new_cost = stats[1]; num_iterations = (int)stats[2]; lambda = stats[3];

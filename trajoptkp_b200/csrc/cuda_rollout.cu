@@ -158,12 +158,20 @@ int launch_rollout(tokp_traj* tr, int mode, const double* d_Uin, const double* d
     int rc = plan_launch(dm, G, pass, &lp);
     if (rc) return rc;
     a.ecap = lp.ecap; a.pass = pass;
-    // the redo pass runs a sparse subset of the worlds and the latency layout has one warp per block: no block walk
-    a.bsync = (pass == 0 && !a.spread) ? 2 : 0;
-    if (const char* e = getenv("TOKP_ROLL_BLOCKSYNC")) if (a.bsync) a.bsync = atoi(e) > 3 ? 3 : (atoi(e) < 0 ? 0 : atoi(e));
     int warps = lp.warps;
     int blocks = (nworlds + lp.worlds_per_block - 1) / lp.worlds_per_block;
-    if (a.spread) { warps = 1; blocks = nworlds; lp.smem = (size_t)lp.wsd * 8; }
+    if (a.spread) {
+      // one world per warp; as many warps per block as it takes to cover the worlds with one block per SM (at most 4),
+      // so that the warps of an SM walk the step together
+      warps = (nworlds + 147) / 148;
+      if (warps > 4) warps = 4;
+      if (const char* e = getenv("TOKP_SPREAD_WARPS")) { int v = atoi(e); if (v >= 1 && v <= 4) warps = v; }
+      blocks = (nworlds + warps - 1) / warps;
+      lp.smem = (size_t)lp.wsd * 8 * warps;
+    }
+    // the redo pass runs a sparse subset of the worlds: no block walk; neither for one-warp blocks
+    a.bsync = (pass == 0 && (!a.spread || (warps > 1 && G == 32))) ? 2 : 0;
+    if (const char* e = getenv("TOKP_ROLL_BLOCKSYNC")) if (a.bsync) a.bsync = atoi(e) > 3 ? 3 : (atoi(e) < 0 ? 0 : atoi(e));
 #define LAUNCH(GG, NN)                                                                                              \
   TOKP_CUDA(cudaFuncSetAttribute(k_rollout<GG, NN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lp.smem));    \
   k_rollout<GG, NN><<<blocks, warps * 32, lp.smem, tr->stream>>>(dm, a, lp.wsd);

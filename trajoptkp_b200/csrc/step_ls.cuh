@@ -136,11 +136,25 @@ TK_DEV double primal_search(const DM& m, WS& w, const Grp<G, NV>& g, double gaus
       else {
         int b1 = 0;
         b2 = 0;
-#define TK_BRACKET(P, C, FLAG)                                                        \
-  if (P.d0 < 0.0 && C.d0 < 0.0 && P.d0 < C.d0) { P = C; FLAG = 1; }                   \
-  else if (P.d0 > 0.0 && C.d0 > 0.0 && P.d0 > C.d0) { P = C; FLAG = 2; }
-        TK_BRACKET(p1, c0, b1) TK_BRACKET(p1, c1, b1) TK_BRACKET(p1, c2, b1)
-        TK_BRACKET(p2, c0, b2) TK_BRACKET(p2, c1, b2) TK_BRACKET(p2, c2, b2)
+        // UpdateBracket: P is replaced by every candidate in turn whose derivative has P's sign and lies closer to
+        // zero.  The sign of P.d0 cannot change under these replacements, so the sequential rule is a running
+        // "closest to zero" over the candidates of that sign: pick the winner on the derivatives alone (sgn * d0 is
+        // an exact sign flip, the comparisons are the reference's), then copy one point.
+#define TK_BRACKET(P, FLAG)                                                                     \
+  {                                                                                             \
+    const double sgn = P.d0 < 0.0 ? -1.0 : 1.0;                                                 \
+    double best = sgn * P.d0; /* > 0 unless P.d0 == 0, which admits no candidate */             \
+    int pick = -1;                                                                              \
+    if (P.d0 != 0.0) {                                                                          \
+      double v0 = sgn * c0.d0, v1 = sgn * c1.d0, v2 = sgn * c2.d0;                              \
+      if (v0 > 0.0 && v0 < best) { best = v0; pick = 0; }                                       \
+      if (v1 > 0.0 && v1 < best) { best = v1; pick = 1; }                                       \
+      if (v2 > 0.0 && v2 < best) { best = v2; pick = 2; }                                       \
+    }                                                                                           \
+    if (pick >= 0) { P = pick == 0 ? c0 : (pick == 1 ? c1 : c2); FLAG = 1; }                    \
+  }
+        TK_BRACKET(p1, b1)
+        TK_BRACKET(p2, b2)
 #undef TK_BRACKET
         if (b1) { nsel = N_P1; state = LS_UB1; }
         else if (b2) { nsel = N_P2; state = LS_UB2; }

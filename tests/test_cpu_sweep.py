@@ -77,3 +77,42 @@ def test_gather_world_size_2_gloo(tmp_path):
     p = subprocess.run(cmd, capture_output=True, text=True, timeout=240, env=env)
     assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-2000:]
     assert "rank0-ok" in p.stdout and "rank1-ok" in p.stdout
+
+
+def test_result_files_in_reference_format(built, tmp_path):
+    """summary.csv / summary.yaml / directory naming as GenDataOpenloopOptimisation writes them
+    (GenTestingData.cpp:234-257,827-958), parsed the way TestingData/scripts/plot_iLQR_keypoint_results.py does."""
+    import time
+
+    import pandas as pd
+    import yaml
+
+    from helpers import make
+    from trajoptkp_b200 import capi, sweep
+    tc = make("walker_run", kp_method=capi.KP_VELOCITY_CHANGE, min_N=1, max_N=20)
+    rng = np.random.default_rng(0)
+    recs = np.abs(rng.standard_normal((7, sweep.RECORD_SIZE)))
+    recs[:, 2] = rng.integers(3, 10, 7)
+    when = time.struct_time((2024, 9, 3, 14, 5, 0, 1, 247, -1))
+    d = sweep.write_openloop_results(str(tmp_path), tc, 80, recs, when=when)
+    assert d == str(tmp_path / "TestingData" / "iLQR" / "walker_run_openloop_20240903_1405")
+    df = pd.read_csv(d + "/summary.csv")
+    assert list(df.columns) == ["Cost reduction", "Optimisation time (ms)", "Number iterations", "Average num dofs",
+                                "Average percent derivs", "Average time derivs (ms)", "Average time BP (ms)",
+                                "Average time FP (ms)"]
+    assert len(df) == 7
+    assert np.allclose(df["Cost reduction"].to_numpy(), recs[:, 0], rtol=1e-5)       # %g keeps 6 significant digits
+    assert np.array_equal(df["Number iterations"].to_numpy(), recs[:, 2].astype(int))
+    y = yaml.load(open(d + "/summary.yaml"), Loader=yaml.FullLoader)
+    assert list(y) == ["optimisation horizon", "controls_noise", "model timestep", "keypoint_name", "keypoint_min_N",
+                       "keypoint_max_N", "velocity_change_thresholds"]
+    assert y["keypoint_name"] == "*VC_1_20" and y["optimisation horizon"] == 80
+    assert y["model timestep"] == tc.timestep and y["keypoint_min_N"] == 1 and y["keypoint_max_N"] == 20
+    assert np.allclose(y["velocity_change_thresholds"], tc.vel_thr) and len(y["velocity_change_thresholds"]) == tc.n
+    # the other labels of SaveTestSummaryData
+    assert sweep.keypoint_method_name("set_interval", 5, 5) == "SI_5"
+    assert sweep.keypoint_method_name("adaptive_jerk", 2, 10) == "AJ_2_10"
+    assert sweep.keypoint_method_name("iterative_error", 2, 10) == "*IE_2_10"
+    assert sweep.keypoint_method_name("set_interval", 2, 10, auto_adjust=True) == "AA_2_10"
+    ys = yaml.safe_load(sweep.summary_yaml(40, 0.1, 0.004, "iterative_error", 2, 10, iter_thr=0.5))
+    assert ys["error_threshold"] == 0.5 and ys["keypoint_name"] == "*IE_2_10" and ys["controls_noise"] == 0.1

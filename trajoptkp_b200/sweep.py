@@ -72,6 +72,74 @@ def summary_csv(records):
     return "\n".join(lines) + "\n"
 
 
+def keypoint_method_name(method, min_N, max_N, auto_adjust=False):
+    """Label written to summary.yaml (GenTestingData::SaveTestSummaryData, GenTestingData.cpp:868-892): SI_<min>,
+    *VC_<min>_<max>, AJ_<min>_<max>, *IE_<min>_<max>, AA_<min>_<max> for auto-adjust; other methods get an empty name."""
+    if auto_adjust:
+        return "AA_%d_%d" % (min_N, max_N)
+    if method == "set_interval":
+        return "SI_%d" % min_N
+    prefix = {"velocity_change": "*VC", "adaptive_jerk": "AJ", "iterative_error": "*IE"}.get(method)
+    return "" if prefix is None else "%s_%d_%d" % (prefix, min_N, max_N)
+
+
+def _yaml_scalar(v):
+    if isinstance(v, str):
+        # yaml-cpp quotes scalars that start with an indicator character such as '*'
+        return '"%s"' % v if (v == "" or v[0] in "*&!|>%@`#,[]{}-?:'\"") else v
+    if isinstance(v, bool):
+        return "true" if v else "false"
+    if isinstance(v, int):
+        return "%d" % v
+    return "%.17g" % v if float(v) != int(v) or abs(v) >= 1e15 else "%d" % int(v)
+
+
+def summary_yaml(horizon, controls_noise, timestep, method, min_N, max_N, vel_thr=None, jerk_thr=None, iter_thr=None,
+                 auto_adjust=False):
+    """The reference's summary.yaml (GenTestingData.cpp:894-958): same keys in the same order, block map with flow
+    sequences for the threshold lists, as yaml-cpp's emitter writes them."""
+    rows = [("optimisation horizon", int(horizon)), ("controls_noise", float(controls_noise)),
+            ("model timestep", float(timestep)),
+            ("keypoint_name", keypoint_method_name(method, min_N, max_N, auto_adjust)),
+            ("keypoint_min_N", int(min_N)), ("keypoint_max_N", int(max_N))]
+    lines = ["%s: %s" % (k, _yaml_scalar(v)) for k, v in rows]
+    if method == "velocity_change" and vel_thr is not None:
+        lines.append("velocity_change_thresholds: [%s]" % ", ".join(_yaml_scalar(float(x)) for x in vel_thr))
+    if method == "adaptive_jerk" and jerk_thr is not None:
+        lines.append("jerk_thresholds: [%s]" % ", ".join(_yaml_scalar(float(x)) for x in jerk_thr))
+    if method == "iterative_error" and iter_thr is not None:
+        lines.append("error_threshold: %s" % _yaml_scalar(float(iter_thr)))
+    return "\n".join(lines)
+
+
+def test_directory(root, optimiser_name, task_name, testing_method, when=None):
+    """GenTestingData::CreateTestName (GenTestingData.cpp:827-860):
+    <root>/TestingData/<optimiser>/<task>_<openloop|synchronus_mpc|asynchronus_mpc>_<YYYYMMDD_HHMM>."""
+    import os
+    import time
+    stamp = time.strftime("%Y%m%d_%H%M", time.localtime() if when is None else when)
+    return os.path.join(root, "TestingData", optimiser_name, "%s_%s_%s" % (task_name, testing_method, stamp))
+
+
+def write_openloop_results(root, tc, horizon, records, optimiser_name="iLQR", controls_noise=0.0, when=None):
+    """Writes summary.csv + summary.yaml where and how GenDataOpenloopOptimisation does, so that the reference's
+    TestingData/scripts/plot_iLQR_keypoint_results.py reads them unchanged.  Returns the directory."""
+    import os
+
+    from . import capi
+    d = test_directory(root, optimiser_name, tc.name, "openloop", when)
+    os.makedirs(d, exist_ok=True)
+    with open(os.path.join(d, "summary.csv"), "w") as f:
+        f.write(summary_csv(records))
+    method = {capi.KP_SET_INTERVAL: "set_interval", capi.KP_ADAPTIVE_JERK: "adaptive_jerk",
+              capi.KP_ADAPTIVE_ACCEL: "adaptive_accel", capi.KP_ITERATIVE_ERROR: "iterative_error",
+              capi.KP_VELOCITY_CHANGE: "velocity_change"}[tc.kp_method]
+    with open(os.path.join(d, "summary.yaml"), "w") as f:
+        f.write(summary_yaml(horizon, controls_noise, tc.timestep, method, tc.min_N, tc.max_N, tc.vel_thr, tc.jerk_thr,
+                             tc.iter_thr))
+    return d
+
+
 def run_openloop_sweep(tc, horizon, num_trials=100, rank=0, world=1, dist=None, device=None, max_iter=10, min_iter=3,
                        lam=0.01, init_controls=None, batch=None):
     """GenDataOpenloopOptimisation on the device: this rank's trials as ONE tokp_traj batch (all trials of the rank

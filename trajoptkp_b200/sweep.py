@@ -131,13 +131,18 @@ def write_openloop_results(root, tc, horizon, records, optimiser_name="iLQR", co
     os.makedirs(d, exist_ok=True)
     with open(os.path.join(d, "summary.csv"), "w") as f:
         f.write(summary_csv(records))
-    method = {capi.KP_SET_INTERVAL: "set_interval", capi.KP_ADAPTIVE_JERK: "adaptive_jerk",
-              capi.KP_ADAPTIVE_ACCEL: "adaptive_accel", capi.KP_ITERATIVE_ERROR: "iterative_error",
-              capi.KP_VELOCITY_CHANGE: "velocity_change"}[tc.kp_method]
     with open(os.path.join(d, "summary.yaml"), "w") as f:
-        f.write(summary_yaml(horizon, controls_noise, tc.timestep, method, tc.min_N, tc.max_N, tc.vel_thr, tc.jerk_thr,
-                             tc.iter_thr))
+        f.write(summary_yaml(horizon, controls_noise, tc.timestep, method_name_of(tc), tc.min_N, tc.max_N, tc.vel_thr,
+                             tc.jerk_thr, tc.iter_thr))
     return d
+
+
+def method_name_of(tc):
+    """keypoint_method.name of a task config."""
+    from . import capi
+    return {capi.KP_SET_INTERVAL: "set_interval", capi.KP_ADAPTIVE_JERK: "adaptive_jerk",
+            capi.KP_ADAPTIVE_ACCEL: "adaptive_accel", capi.KP_ITERATIVE_ERROR: "iterative_error",
+            capi.KP_VELOCITY_CHANGE: "velocity_change"}[tc.kp_method]
 
 
 def run_openloop_sweep(tc, horizon, num_trials=100, rank=0, world=1, dist=None, device=None, max_iter=10, min_iter=3,

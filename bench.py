@@ -273,6 +273,10 @@ def main():
             "phase_ms": {"derivs": phase[0] / args.steps, "backward": phase[1] / args.steps, "forward": phase[2] / args.steps},
             "jacobians_per_step": jac / args.steps,
             "replan_latency_ms_b1": lat_ms,   # one trajectory alone on the GPU (serial rollouts / Riccati: latency-bound)
+            # context only (never a ratio input): the reference's own published per-replan times for walker_run
+            # synchronous MPC at H = 80 (PaperData, hardware not stated)
+            "published_reference_ms_per_replan_h80": {"SI_1": 8.474, "SI_5": 5.364, "AJ_2_20": 5.708, "VC_2_20": 5.674,
+                                                       "IE_2_20": 16.570} if args.task == "walker_run" else None,
             "e2e": {"value": e2e_value, "unit": "jacobians/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                     "ms_per_step": 1e3 * dt_e / args.steps},
             "gpu_launches": int(l1 - l0), "clocks": sampler.summary(),

@@ -28,6 +28,26 @@ int main(int argc, char** argv) {
     mt->InitModelTranslator(helper, TOKP_TASK_ACROBOT, {"shoulder", "elbow"}, {"shoulder"},
                             {0.0, 0.0, 0.0, 0.0, 0.0}, {0.0, 0.0, 0.001, 0.001, 100.0}, {100.0, 100.0, 1.0, 1.0, 100.0}, kp);
     std::printf("{\"dof\": %d, \"num_ctrl\": %d, \"nq\": %d, \"S\": %d,\n", mt->dof, mt->num_ctrl, helper->nq, helper->S);
+    {
+      // ModelTranslator gather / scatter and host residuals (no device needed)
+      mjData d = *helper->master_reset_data;
+      MatrixXd x(4, 1);
+      x(0, 0) = 0.5; x(1, 0) = -0.25; x(2, 0) = 1.5; x(3, 0) = -2.0;
+      MatrixXd u(1, 1);
+      u(0, 0) = 0.75;
+      bool ok = mt->SetStateVector(x, &d) && mt->SetControlVector(u, &d);
+      MatrixXd xr = mt->ReturnStateVector(&d), pr = mt->ReturnPositionVector(&d), vr = mt->ReturnVelocityVector(&d);
+      MatrixXd lim = mt->ReturnControlLimits();
+      MatrixXd r;
+      mt->Residuals(&d, r);
+      MatrixXd bad(3, 1);
+      bool rejected = !mt->SetStateVector(bad, &d);
+      std::printf("\"scatter_ok\": %d, \"size_mismatch_rejected\": %d,\n", ok ? 1 : 0, rejected ? 1 : 0);
+      print_vec("state_roundtrip", {xr(0, 0), xr(1, 0), xr(2, 0), xr(3, 0), pr(1, 0), vr(1, 0), mt->ReturnControlVector(&d)(0, 0)});
+      print_vec("ctrl_limits", {lim(0, 0), lim(1, 0)});
+      print_vec("residuals", {r(0, 0), r(1, 0), r(2, 0), r(3, 0), r(4, 0)});
+      std::printf("\"cost_running\": %.17g, \"cost_terminal\": %.17g,\n", mt->CostFunction(r, false), mt->CostFunction(r, true));
+    }
     if (no_gpu) {
       // without a device the arena cannot be created: the error must surface, nothing falls back to the host
       try {

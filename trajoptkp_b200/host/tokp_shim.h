@@ -10,6 +10,7 @@
 // MuJoCoHelper.cpp:732-741); Eigen's MatrixXd becomes the minimal column-major stand-in below when Eigen is absent
 // (define TOKP_SHIM_USE_EIGEN to use the real one); errors throw std::runtime_error instead of exit(1).
 #pragma once
+#include <cmath>
 #include <cstring>
 #include <iostream>
 #include <memory>

@@ -64,6 +64,85 @@ class ModelTranslator {
     for (int i = 0; i < num_ctrl; i++) u(i, 0) = MuJoCo_helper->ctrl(d)[ctrl_adr[i]];
     return u;
   }
+  // ReturnStateVectorQuaternions (ModelTranslator.cpp:899-950): the supported state vectors hold joint DoFs only, so
+  // dof_quat == dof and the quaternion form is the plain state vector
+  MatrixXd ReturnStateVectorQuaternions(mjData* d) const { return ReturnStateVector(d); }
+  // ReturnPositionVector / ReturnVelocityVector (ModelTranslator.cpp:1014, :1173)
+  MatrixXd ReturnPositionVector(mjData* d) const {
+    MatrixXd p(dof, 1);
+    for (int i = 0; i < dof; i++) p(i, 0) = MuJoCo_helper->qpos(d)[qpos_adr[i]];
+    return p;
+  }
+  MatrixXd ReturnVelocityVector(mjData* d) const {
+    MatrixXd v(dof, 1);
+    for (int i = 0; i < dof; i++) v(i, 0) = MuJoCo_helper->qvel(d)[state_dof_adr_indices[i]];
+    return v;
+  }
+  // SetControlVector (:989), SetPositionVector / SetVelocityVector (:1466), SetStateVector: scatter with a size check
+  // (the reference prints and returns false on a size mismatch)
+  bool SetControlVector(const MatrixXd& u, mjData* d) const {
+    if (u.rows() != num_ctrl) { std::cerr << "ERROR: control vector size does not match the size of the control vector in the state vector list!" << std::endl; return false; }
+    for (int i = 0; i < num_ctrl; i++) MuJoCo_helper->ctrl(d)[ctrl_adr[i]] = u(i, 0);
+    return true;
+  }
+  bool SetPositionVector(const MatrixXd& p, mjData* d) const {
+    if (p.rows() != dof) { std::cerr << "ERROR: position vector size does not match the size of the state vector list!" << std::endl; return false; }
+    for (int i = 0; i < dof; i++) MuJoCo_helper->qpos(d)[qpos_adr[i]] = p(i, 0);
+    return true;
+  }
+  bool SetVelocityVector(const MatrixXd& v, mjData* d) const {
+    if (v.rows() != dof) { std::cerr << "ERROR: velocity vector size does not match the size of the state vector list!" << std::endl; return false; }
+    for (int i = 0; i < dof; i++) MuJoCo_helper->qvel(d)[state_dof_adr_indices[i]] = v(i, 0);
+    return true;
+  }
+  bool SetStateVector(const MatrixXd& x, mjData* d) const {
+    if (x.rows() != 2 * dof) { std::cerr << "ERROR: state vector size does not match the size of the state vector list!" << std::endl; return false; }
+    for (int i = 0; i < dof; i++) {
+      MuJoCo_helper->qpos(d)[qpos_adr[i]] = x(i, 0);
+      MuJoCo_helper->qvel(d)[state_dof_adr_indices[i]] = x(i + dof, 0);
+    }
+    return true;
+  }
+  // ReturnControlLimits (:971-987): [lo_0, hi_0, lo_1, hi_1, ...] read from actuator_ctrlrange (MuJoCoHelper.cpp:262-264)
+  MatrixXd ReturnControlLimits() const {
+    std::vector<double> r(2 * (size_t)MuJoCo_helper->nu + 2);
+    tokp_model_get_real(MuJoCo_helper->model, "actuator_ctrlrange", r.data(), (int)r.size());
+    MatrixXd lim(2 * num_ctrl, 1);
+    for (int i = 0; i < num_ctrl; i++) { lim(2 * i, 0) = r[2 * ctrl_adr[i]]; lim(2 * i + 1, 0) = r[2 * ctrl_adr[i] + 1]; }
+    return lim;
+  }
+  // MT::Residuals overrides (Acrobot.cpp:26-55, Walker.cpp:59-90) and MT::CostFunction (ModelTranslator.cpp:314-327) on
+  // the host, for harness code that scores recorded states (SingleMPCRun's final-cost replay, GenTestingData.cpp:565-585);
+  // the optimiser itself evaluates them on the device
+  void Residuals(mjData* d, MatrixXd& residuals) const {
+    const double* q = MuJoCo_helper->qpos(d);
+    const double* v = MuJoCo_helper->qvel(d);
+    const double* u = MuJoCo_helper->ctrl(d);
+    const std::vector<double>& t = resid_target;
+    if ((int)residuals.rows() != (int)t.size()) residuals.resize((int)t.size(), 1);
+    int k = 0;
+    if (kind == TOKP_TASK_ACROBOT) {
+      residuals(k++, 0) = q[qpos_adr[0]] - t[0];
+      residuals(k++, 0) = q[qpos_adr[1]] - t[1];
+      residuals(k++, 0) = v[state_dof_adr_indices[0]] - t[2];
+      residuals(k++, 0) = v[state_dof_adr_indices[1]] - -t[3];  // the double minus is the reference's (Acrobot.cpp:45)
+      residuals(k++, 0) = u[ctrl_adr[0]] - t[4];
+    } else if (kind == TOKP_TASK_WALKER) {
+      residuals(k++, 0) = q[qpos_adr[0]] - t[0];                // body height
+      residuals(k++, 0) = q[qpos_adr[2]] - t[1];                // body rotation
+      residuals(k++, 0) = v[state_dof_adr_indices[1]] - t[2];   // forward velocity
+      for (int i = 0; i < num_ctrl; i++, k++) residuals(k, 0) = u[ctrl_adr[i]] - t[3 + i];
+    } else {
+      throw std::runtime_error("residuals not implemented for this model");
+    }
+    if (k != (int)t.size()) throw std::runtime_error("Error: Residuals size mismatch");
+  }
+  double CostFunction(const MatrixXd& residuals, bool terminal) const {
+    double cost = 0.0;
+    for (size_t i = 0; i < resid_target.size(); i++)
+      cost += (terminal ? resid_weight_terminal[i] : resid_weight[i]) * std::pow(residuals((int)i, 0), 2);
+    return cost;
+  }
 
   std::shared_ptr<MuJoCoHelper> MuJoCo_helper;
   int kind = 0, dof = 0, num_ctrl = 0;

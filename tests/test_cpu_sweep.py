@@ -116,3 +116,13 @@ def test_result_files_in_reference_format(built, tmp_path):
     assert sweep.keypoint_method_name("set_interval", 2, 10, auto_adjust=True) == "AA_2_10"
     ys = yaml.safe_load(sweep.summary_yaml(40, 0.1, 0.004, "iterative_error", 2, 10, iter_thr=0.5))
     assert ys["error_threshold"] == 0.5 and ys["keypoint_name"] == "*IE_2_10" and ys["controls_noise"] == 0.1
+
+
+def test_summary_yaml_is_byte_identical_to_a_published_file():
+    """The VC_2_20, H = 80 walker file of PaperData (walker_run_synchronus_mpc_20240918_0118/summary.yaml), verbatim."""
+    from trajoptkp_b200 import sweep
+    want = ("optimisation horizon: 80\ncontrols_noise: 0.5\nmodel timestep: 0.005\nkeypoint_name: \"*VC_2_20\"\n"
+            "keypoint_min_N: 2\nkeypoint_max_N: 20\nvelocity_change_thresholds:\n  - 2\n  - 2\n  - 2\n  - 10\n  - 10\n"
+            "  - 10\n  - 10\n  - 10\n  - 10")
+    got = sweep.summary_yaml(80, 0.5, 0.005, "velocity_change", 2, 20, vel_thr=[2, 2, 2, 10, 10, 10, 10, 10, 10])
+    assert got == want

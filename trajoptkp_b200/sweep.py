@@ -91,22 +91,24 @@ def _yaml_scalar(v):
         return "true" if v else "false"
     if isinstance(v, int):
         return "%d" % v
-    return "%.17g" % v if float(v) != int(v) or abs(v) >= 1e15 else "%d" % int(v)
+    # yaml-cpp writes doubles with digits10 + 1 = 16 significant digits (0.005 stays "0.005")
+    return "%.16g" % v if float(v) != int(v) or abs(v) >= 1e15 else "%d" % int(v)
 
 
 def summary_yaml(horizon, controls_noise, timestep, method, min_N, max_N, vel_thr=None, jerk_thr=None, iter_thr=None,
                  auto_adjust=False):
-    """The reference's summary.yaml (GenTestingData.cpp:894-958): same keys in the same order, block map with flow
-    sequences for the threshold lists, as yaml-cpp's emitter writes them."""
+    """The reference's summary.yaml (GenTestingData.cpp:894-958): same keys in the same order, block map with block
+    sequences for the threshold lists and no trailing newline, byte for byte what yaml-cpp's emitter writes (checked
+    against PaperData/.../walker_run_synchronus_mpc_20240918_0118/summary.yaml)."""
     rows = [("optimisation horizon", int(horizon)), ("controls_noise", float(controls_noise)),
             ("model timestep", float(timestep)),
             ("keypoint_name", keypoint_method_name(method, min_N, max_N, auto_adjust)),
             ("keypoint_min_N", int(min_N)), ("keypoint_max_N", int(max_N))]
     lines = ["%s: %s" % (k, _yaml_scalar(v)) for k, v in rows]
     if method == "velocity_change" and vel_thr is not None:
-        lines.append("velocity_change_thresholds: [%s]" % ", ".join(_yaml_scalar(float(x)) for x in vel_thr))
+        lines += ["velocity_change_thresholds:"] + ["  - %s" % _yaml_scalar(float(x)) for x in vel_thr]
     if method == "adaptive_jerk" and jerk_thr is not None:
-        lines.append("jerk_thresholds: [%s]" % ", ".join(_yaml_scalar(float(x)) for x in jerk_thr))
+        lines += ["jerk_thresholds:"] + ["  - %s" % _yaml_scalar(float(x)) for x in jerk_thr]
     if method == "iterative_error" and iter_thr is not None:
         lines.append("error_threshold: %s" % _yaml_scalar(float(iter_thr)))
     return "\n".join(lines)

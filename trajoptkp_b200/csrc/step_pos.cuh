@@ -205,17 +205,7 @@ TK_DEV void factor_ldl(const DM& m, const double* A, double* LD, double* dinv, c
     for (int i = g.gl; i < k; i += G) {
       if (!in_mask(lo, hi, i)) continue;
       double a = LD[k * nv + i] / Mkk;
-      if constexpr (NV > 0 && NV <= 32) {
-        // dof i and its ancestors as a bit set, walked from the highest dof down: the order of the dof_parentid chain
-        // without its dependent loads
-        for (unsigned set = m.dof_ancmask_lo[i]; set;) {
-          const int j = 31 - __clz((int)set);
-          set ^= 1u << j;
-          LD[i * nv + j] -= a * LD[k * nv + j];
-        }
-      } else {
-        for (int j = i; j >= 0; j = m.dof_parentid[j]) LD[i * nv + j] -= a * LD[k * nv + j];
-      }
+      for (int j = i; j >= 0; j = m.dof_parentid[j]) LD[i * nv + j] -= a * LD[k * nv + j];
     }
     g.sync();
     for (int i = g.gl; i < k; i += G)
@@ -247,15 +237,7 @@ TK_DEV void solve_ldl(const DM& m, const double* LD, const double* dinv, double*
   for (int i = 1; i < nv; i++) {
     if (g.gl == 0) {
       double s = x[i];
-      if constexpr (NV > 0 && NV <= 32) {
-        for (unsigned set = m.dof_ancmask_lo[i] & ~(1u << i); set;) {
-          const int j = 31 - __clz((int)set);
-          set ^= 1u << j;
-          s -= LD[i * nv + j] * x[j];
-        }
-      } else {
-        for (int j = m.dof_parentid[i]; j >= 0; j = m.dof_parentid[j]) s -= LD[i * nv + j] * x[j];
-      }
+      for (int j = m.dof_parentid[i]; j >= 0; j = m.dof_parentid[j]) s -= LD[i * nv + j] * x[j];
       x[i] = s;
     }
     g.sync();

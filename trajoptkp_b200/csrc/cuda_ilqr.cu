@@ -243,36 +243,31 @@ __global__ void k_riccati(const double* __restrict__ A, const double* __restrict
       else { int e2 = e - nx * nx, c = e2 / nx, r = e2 - c * nx; for (int q = 0; q < nx; q++) s += Vxx[q * nx + r] * Bt[c * nx + q]; VB[e2] = s; }
     }
     __syncthreads();
-    for (int e = tid; e < nx * nx + m * m + m * nx; e += nt) {
-      double s = 0;
-      if (e < nx * nx) {
-        int c = e / nx, r = e - c * nx;
-        for (int q = 0; q < nx; q++) s += At[r * nx + q] * VA[c * nx + q];
-        Qxx[e] = lxxb[(size_t)t * nx * nx + e] + s;
-      } else if (e < nx * nx + m * m) {
-        int e2 = e - nx * nx, c = e2 / m, r = e2 - c * m;
+    // Warp 0 takes the small-matrix chain (Q_uu, its regularised pivoted LDLT, inv(Q_uu) by m column solves, k, Q_uu k,
+    // delta_J - mostly single-lane work) while the other warps compute the two large products Q_xx = l_xx + A' (V_xx A)
+    // and Q_ux = B' (V_xx A): the serial chain hides behind the 18 x 18 x 18 product instead of standing between
+    // block barriers.  Same arithmetic per entry as the straight sequence.
+    if (tid < 32) {
+      const int lane = tid;
+      for (int e2 = lane; e2 < m * m; e2 += 32) {
+        int c = e2 / m, r = e2 - c * m;
+        double s = 0;
         for (int q = 0; q < nx; q++) s += Bt[r * nx + q] * VB[c * nx + q];
         Quu[e2] = luub[(size_t)t * m * m + e2] + s;
-      } else {
-        int e2 = e - nx * nx - m * m, c = e2 / m, r = e2 - c * m;
-        for (int q = 0; q < nx; q++) s += Bt[r * nx + q] * VA[c * nx + q];
-        Qux[e2] = s;
       }
-    }
-    __syncthreads();
-    if (tid == 0) {
-      for (int i = 0; i < m * m; i++) s_mat[i] = Quu[i];
-      for (int i = 0; i < m; i++) s_mat[i * m + i] += lam;
-      if (pd_counter >= 100) {
-        if (!matrix_pd(s_mat, m)) s_fail = 1;
+      __syncwarp();
+      if (lane == 0) {
+        for (int i = 0; i < m * m; i++) s_mat[i] = Quu[i];
+        for (int i = 0; i < m; i++) s_mat[i * m + i] += lam;
+        if (pd_counter >= 100) {
+          if (!matrix_pd(s_mat, m)) s_fail = 1;
+        }
+        if (!s_fail) s_zero = ldlt_factor(s_mat, m, s_tr) ? 1 : 0;
       }
-      if (!s_fail) s_zero = ldlt_factor(s_mat, m, s_tr) ? 1 : 0;
-    }
-    __syncthreads();
-    if (!s_fail && tid < m) ldlt_solve_col(s_mat, m, s_tr, s_zero != 0, tid, Qinv);
-    __syncthreads();
-    if (tid == 0) {
-      if (!s_fail) {
+      __syncwarp();
+      if (!s_fail && lane < m) ldlt_solve_col(s_mat, m, s_tr, s_zero != 0, lane, Qinv);
+      __syncwarp();
+      if (lane == 0 && !s_fail) {
         for (int r = 0; r < m; r++) {
           double s = 0;
           for (int q = 0; q < m; q++) s += Qinv[q * m + r] * Qu[q];
@@ -287,6 +282,19 @@ __global__ void k_riccati(const double* __restrict__ A, const double* __restrict
         for (int r = 0; r < m; r++) { d1 += kt[r] * Qu[r]; d2 += kt[r] * tm[r]; }
         s_dJ += d1;
         s_dJ += d2;
+      }
+    } else {
+      for (int e = tid - 32; e < nx * nx + m * nx; e += nt - 32) {
+        double s = 0;
+        if (e < nx * nx) {
+          int c = e / nx, r = e - c * nx;
+          for (int q = 0; q < nx; q++) s += At[r * nx + q] * VA[c * nx + q];
+          Qxx[e] = lxxb[(size_t)t * nx * nx + e] + s;
+        } else {
+          int e2 = e - nx * nx, c = e2 / m, r = e2 - c * m;
+          for (int q = 0; q < nx; q++) s += Bt[r * nx + q] * VA[c * nx + q];
+          Qux[e2] = s;
+        }
       }
     }
     if (pd_counter >= 100) pd_counter = 0;

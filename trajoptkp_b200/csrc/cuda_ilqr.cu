@@ -165,6 +165,63 @@ __device__ bool ldlt_factor(double* mat, int n, int* tr) {
 #undef MM
 }
 
+// ldlt_factor with the lanes of one warp on the independent elements of every elimination step (row/column swaps,
+// the rows of the trailing column, their division by the pivot); the sums run in the same order per element, so the
+// factor is bit-identical to the one-thread form.  Called by all 32 lanes; mat / tr in shared memory.
+__device__ bool ldlt_factor_warp(double* mat, int n, int* tr, int lane) {
+#define MM(r, c) mat[(c) * n + (r)]
+  bool zero_matrix = false;
+  for (int k = 0; k < n; k++) {
+    int big = k;
+    double bigv = fabs(MM(k, k));
+    for (int i = k + 1; i < n; i++)
+      if (fabs(MM(i, i)) > bigv) { bigv = fabs(MM(i, i)); big = i; }
+    __syncwarp();
+    if (lane == 0) tr[k] = big;
+    if (k != big) {
+      // four disjoint element sets (columns < k; columns k / big below row big; the two diagonal entries; the stretch
+      // between k and big): no ordering between them
+      int s = n - big - 1;
+      if (lane < k) { double t = MM(k, lane); MM(k, lane) = MM(big, lane); MM(big, lane) = t; }
+      if (lane < s) { double t = MM(big + 1 + lane, k); MM(big + 1 + lane, k) = MM(big + 1 + lane, big); MM(big + 1 + lane, big) = t; }
+      if (lane == 31) { double t = MM(k, k); MM(k, k) = MM(big, big); MM(big, big) = t; }
+      if (lane > k && lane < big) { double t = MM(lane, k); MM(lane, k) = MM(big, lane); MM(big, lane) = t; }
+      __syncwarp();
+    }
+    int rs = n - k - 1;
+    if (k > 0) {
+      double temp[kMaxCtrl];
+#pragma unroll
+      for (int j = 0; j < kMaxCtrl; j++) temp[j] = j < k ? MM(j, j) * MM(k, j) : 0.0;
+      if (lane == rs) {  // the diagonal entry, on the first lane that has no row
+        double sum = 0;
+#pragma unroll
+        for (int j = 0; j < kMaxCtrl; j++) if (j < k) sum += MM(k, j) * temp[j];
+        MM(k, k) -= sum;
+      }
+      if (lane < rs) {
+        double t = 0;
+#pragma unroll
+        for (int j = 0; j < kMaxCtrl; j++) if (j < k) t += MM(k + 1 + lane, j) * temp[j];
+        MM(k + 1 + lane, k) -= t;
+      }
+      __syncwarp();
+    }
+    double akk = MM(k, k);
+    bool valid = fabs(akk) > 0.0;
+    if (k == 0 && !valid) {
+      if (lane < n) tr[lane] = lane;
+      zero_matrix = true;
+      break;
+    }
+    if (valid && lane < rs) MM(k + 1 + lane, k) /= akk;
+    __syncwarp();
+  }
+  __syncwarp();
+  return zero_matrix;
+#undef MM
+}
+
 __device__ void ldlt_solve_col(const double* mat, int n, const int* tr, bool zero_matrix, int c, double* Ainv) {
 #define MM(r, c) mat[(c) * n + (r)]
   const double tol = 2.2250738585072014e-308;
@@ -208,7 +265,7 @@ __global__ void k_riccati(const double* __restrict__ A, const double* __restrict
   double* tmx = tm + m;        // Quu * K
   double* sA = tmx + m * nx;   // A_t, B_t staged per step (coalesced) instead of strided global reads in the products
   double* sB = sA + nx * nx;
-  __shared__ int s_fail, s_zero;
+  __shared__ int s_fail;
   __shared__ double s_dJ;
   __shared__ double s_mat[kMaxCtrl * kMaxCtrl];
   __shared__ int s_tr[kMaxCtrl];
@@ -256,32 +313,38 @@ __global__ void k_riccati(const double* __restrict__ A, const double* __restrict
         Quu[e2] = luub[(size_t)t * m * m + e2] + s;
       }
       __syncwarp();
-      if (lane == 0) {
-        for (int i = 0; i < m * m; i++) s_mat[i] = Quu[i];
-        for (int i = 0; i < m; i++) s_mat[i * m + i] += lam;
-        if (pd_counter >= 100) {
-          if (!matrix_pd(s_mat, m)) s_fail = 1;
-        }
-        if (!s_fail) s_zero = ldlt_factor(s_mat, m, s_tr) ? 1 : 0;
+      for (int i = lane; i < m * m; i += 32) {
+        double v = Quu[i];
+        if ((i / m) == (i - (i / m) * m)) v += lam;
+        s_mat[i] = v;
       }
       __syncwarp();
-      if (!s_fail && lane < m) ldlt_solve_col(s_mat, m, s_tr, s_zero != 0, lane, Qinv);
-      __syncwarp();
-      if (lane == 0 && !s_fail) {
-        for (int r = 0; r < m; r++) {
-          double s = 0;
-          for (int q = 0; q < m; q++) s += Qinv[q * m + r] * Qu[q];
-          kt[r] = -s;
+      if (pd_counter >= 100) {
+        if (lane == 0 && !matrix_pd(s_mat, m)) s_fail = 1;
+        __syncwarp();
+      }
+      if (!s_fail) {
+        bool zero = ldlt_factor_warp(s_mat, m, s_tr, lane);
+        if (lane < m) ldlt_solve_col(s_mat, m, s_tr, zero, lane, Qinv);
+        __syncwarp();
+        if (lane < m) {
+          double sum = 0;
+          for (int q = 0; q < m; q++) sum += Qinv[q * m + lane] * Qu[q];
+          kt[lane] = -sum;
         }
-        for (int r = 0; r < m; r++) {
-          double s = 0;
-          for (int q = 0; q < m; q++) s += Quu[q * m + r] * kt[q];
-          tm[r] = s;
+        __syncwarp();
+        if (lane < m) {
+          double sum = 0;
+          for (int q = 0; q < m; q++) sum += Quu[q * m + lane] * kt[q];
+          tm[lane] = sum;
         }
-        double d1 = 0, d2 = 0;
-        for (int r = 0; r < m; r++) { d1 += kt[r] * Qu[r]; d2 += kt[r] * tm[r]; }
-        s_dJ += d1;
-        s_dJ += d2;
+        __syncwarp();
+        if (lane == 0) {
+          double d1 = 0, d2 = 0;
+          for (int r = 0; r < m; r++) { d1 += kt[r] * Qu[r]; d2 += kt[r] * tm[r]; }
+          s_dJ += d1;
+          s_dJ += d2;
+        }
       }
     } else {
       for (int e = tid - 32; e < nx * nx + m * nx; e += nt - 32) {

@@ -93,6 +93,71 @@ def convert_model(src, dst, header):
         f.write(ET.tostring(root, encoding="unicode"))
 
 
+def needed_meshes(root):
+    """Mesh names used by geoms that take part in the dynamics (they collide or carry mass).  Visual-only geoms
+    (contype = conaffinity = 0 and mass = 0) keep their place in the geom list but their mesh files are not shipped."""
+    classes = {"main": {}}
+
+    def walk_defaults(node, parent):
+        name = node.get("class", "main")
+        attrs = dict(classes.get(name, {})) if name == "main" else dict(parent)
+        for ch in node:
+            if ch.tag == "geom":
+                attrs.update(ch.attrib)
+        classes[name] = attrs
+        for ch in node:
+            if ch.tag == "default":
+                walk_defaults(ch, attrs)
+
+    for d in root.findall("default"):
+        walk_defaults(d, classes["main"])
+    used = set()
+
+    def walk_body(node, childclass):
+        childclass = node.get("childclass", childclass)
+        for ch in node:
+            if ch.tag == "geom":
+                a = dict(classes.get(ch.get("class", childclass or "main"), {}))
+                a.update(ch.attrib)
+                if "mesh" not in a:
+                    continue
+                collides = int(a.get("contype", 1)) != 0 or int(a.get("conaffinity", 1)) != 0
+                massive = float(a.get("mass", 1)) != 0
+                if collides or massive:
+                    used.add(a["mesh"])
+            elif ch.tag == "body":
+                walk_body(ch, childclass)
+
+    for wb in root.findall("worldbody"):
+        walk_body(wb, None)
+    return used
+
+
+def convert_franka_scene(src, dst, header):
+    """Franka scenes: as convert_model, plus the mesh files the dynamics needs (copied next to the model, keeping
+    the paths the <mesh file=...> attributes name; unused <mesh> assets stay listed but are never opened)."""
+    import shutil
+    root = ET.parse(src).getroot()
+    resolve_includes(root, os.path.dirname(src))
+    strip(root)
+    prune_empty(root)
+    used = needed_meshes(root)
+    for asset in root.findall("asset"):
+        for mesh in asset.findall("mesh"):
+            name = mesh.get("name") or os.path.splitext(os.path.basename(mesh.get("file")))[0]
+            if name in used:
+                f = mesh.get("file")
+                out = os.path.join(os.path.dirname(dst), f)
+                os.makedirs(os.path.dirname(out), exist_ok=True)
+                shutil.copyfile(os.path.join(os.path.dirname(src), f), out)
+                os.chmod(out, 0o644)
+    indent(root)
+    os.makedirs(os.path.dirname(dst), exist_ok=True)
+    with open(dst, "w") as f:
+        f.write("<!-- %s -->\n" % header)
+        f.write(ET.tostring(root, encoding="unicode"))
+
+
 def copy_yaml(src, dst):
     import yaml
     with open(src) as f:
@@ -127,6 +192,19 @@ def main():
                   "dynamics-only normalisation of mujoco_models/walker/walker_plane.xml (tools/make_assets.py)")
     copy_yaml(os.path.join(REF, "TaskConfigs/toys/acrobot.yaml"), os.path.join(OUT, "tasks/acrobot.yaml"))
     copy_yaml(os.path.join(REF, "TaskConfigs/locomotion/run_plane.yaml"), os.path.join(OUT, "tasks/walker_run.yaml"))
+    fr = os.path.join(mm, "Franka_emika_scenes_V1")
+    for scene in ("reaching_scene", "boxSweep", "cylinder_pushing", "cylinder_pushing_lowClutter",
+                  "cylinder_pushing_heavyClutter"):
+        convert_franka_scene(os.path.join(fr, scene + ".xml"), os.path.join(OUT, "models/franka/%s.xml" % scene),
+                             "dynamics-only normalisation of mujoco_models/Franka_emika_scenes_V1/%s.xml "
+                             "(tools/make_assets.py)" % scene)
+    for src, name in (("free_motion/reaching.yaml", "reaching"), ("rigid_body_manipulation/box_sweep.yaml", "box_sweep"),
+                      ("rigid_body_manipulation/twoD_push_no_clutter.yaml", "push_ncl"),
+                      ("rigid_body_manipulation/twoD_push_light_clutter.yaml", "push_lcl"),
+                      ("rigid_body_manipulation/twoD_push_heavy_clutter.yaml", "push_mcl")):
+        copy_yaml(os.path.join(REF, "TaskConfigs", src), os.path.join(OUT, "tasks/%s.yaml" % name))
+    for task in ("reaching", "box_sweep", "push_ncl", "push_lcl", "push_mcl"):
+        pack_test_tasks(task, os.path.join(OUT, "test_tasks/%s.csv" % task))
     pack_test_tasks("acrobot", os.path.join(OUT, "test_tasks/acrobot.csv"))
     pack_test_tasks("walker_run", os.path.join(OUT, "test_tasks/walker_run.csv"))
     print("assets written to", os.path.normpath(OUT))

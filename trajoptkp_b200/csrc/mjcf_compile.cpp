@@ -7,6 +7,8 @@
 // inertia-from-geoms, motors / position actuators, joint limits, per-geom contact parameters, and the
 // compile-time constants MuJoCo derives at qpos0 (dof_invweight0, body_invweight0, stat.meaninertia).
 #include <algorithm>
+#include <array>
+#include <cctype>
 #include <cmath>
 #include <cstring>
 #include <fstream>
@@ -69,6 +71,7 @@ struct Compiler {
   void parse_default(const XmlNode& node, const DefaultClass* parent, bool top) {
     DefaultClass cls;
     if (parent) cls = *parent;
+    else if (top && classes.count("main")) cls = classes["main"];  // several top-level <default> blocks merge
     const std::string* nm = node.attr("class");
     cls.name = (top || !nm) ? (nm ? *nm : "main") : *nm;
     if (top && !nm) cls.name = "main";
@@ -129,6 +132,167 @@ struct Compiler {
     }
     auto e = it->second.elems.find(default_key(tag));
     return Getter{&node, e == it->second.elems.end() ? nullptr : &e->second};
+  }
+
+  // ---- mesh assets (MuJoCo: mjCMesh::LoadSTL / LoadOBJ / Process) -----------------------------
+  // A mesh is loaded lazily, the first time a geom that collides or carries mass refers to it.  Processing follows
+  // MuJoCo's compiler: repeated vertices are merged, volume / centre of mass / inertia come from the faces
+  // (tetrahedra about the vertex centroid, absolute volumes), and the vertices are re-expressed in the frame that
+  // is centred at the centre of mass and aligned with the principal axes; the geom frame absorbs that transform.
+  // Collision uses the convex hull, which a support function over all vertices reproduces, so no hull is built.
+  struct MeshAsset {
+    std::string file;
+    double scale[3] = {1, 1, 1};
+    bool loaded = false;
+    std::vector<double> vert;  // processed vertices (mesh frame), 3 per vertex
+    double pos[3] = {0, 0, 0}, quat[4] = {1, 0, 0, 0};  // mesh frame in the file's coordinates
+    double volume = 0, inertia_unit[3] = {0, 0, 0};      // principal inertia at unit density
+    double half[3] = {0, 0, 0};                          // half-extents of the axis-aligned box in the mesh frame
+    int vertadr = -1;                                    // offset (vertices) into Model::mesh_vert once used
+  };
+  std::map<std::string, MeshAsset> meshes;
+  std::string meshdir;
+
+  void parse_assets(const XmlNode& node) {
+    for (auto& ch : node.children) {
+      if (ch->tag != "mesh") continue;
+      const std::string* file = ch->attr("file");
+      if (!file) throw std::runtime_error("mjcf: <mesh> without file (inline vertex data is outside the subset)");
+      std::string name;
+      if (auto* n = ch->attr("name")) name = *n;
+      else {
+        size_t s0 = file->find_last_of('/'), dot = file->find_last_of('.');
+        s0 = s0 == std::string::npos ? 0 : s0 + 1;
+        name = file->substr(s0, dot == std::string::npos || dot < s0 ? std::string::npos : dot - s0);
+      }
+      MeshAsset a;
+      a.file = *file;
+      if (auto* sc = ch->attr("scale")) {
+        auto v = parse_reals(*sc);
+        if (v.size() == 3) for (int i = 0; i < 3; i++) a.scale[i] = v[i];
+      }
+      meshes[name] = a;
+    }
+  }
+
+  static void read_stl(const std::string& path, std::vector<float>& tri) {
+    std::ifstream f(path, std::ios::binary);
+    if (!f) throw std::runtime_error("mjcf: cannot open mesh '" + path + "'");
+    std::vector<char> buf((std::istreambuf_iterator<char>(f)), std::istreambuf_iterator<char>());
+    if (buf.size() < 84) throw std::runtime_error("mjcf: '" + path + "' is not a binary STL");
+    uint32_t n;
+    std::memcpy(&n, buf.data() + 80, 4);
+    if (buf.size() < 84 + (size_t)n * 50) throw std::runtime_error("mjcf: '" + path + "' is not a binary STL (ASCII STL unsupported)");
+    tri.resize((size_t)n * 9);
+    for (uint32_t t = 0; t < n; t++) std::memcpy(&tri[(size_t)t * 9], buf.data() + 84 + (size_t)t * 50 + 12, 36);
+  }
+
+  static void read_obj(const std::string& path, std::vector<double>& v, std::vector<int>& face) {
+    std::ifstream f(path);
+    if (!f) throw std::runtime_error("mjcf: cannot open mesh '" + path + "'");
+    std::string line;
+    while (std::getline(f, line)) {
+      std::istringstream is(line);
+      std::string key;
+      is >> key;
+      if (key == "v") {
+        double x, y, z;
+        if (is >> x >> y >> z) { v.push_back(x); v.push_back(y); v.push_back(z); }
+      } else if (key == "f") {
+        std::vector<int> idx;
+        std::string tok;
+        while (is >> tok) {
+          int i = std::atoi(tok.c_str());  // "a/b/c": atoi stops at '/'
+          int nvert = (int)v.size() / 3;
+          idx.push_back(i > 0 ? i - 1 : nvert + i);
+        }
+        for (size_t k = 2; k < idx.size(); k++) { face.push_back(idx[0]); face.push_back(idx[k - 1]); face.push_back(idx[k]); }
+      }
+    }
+  }
+
+  MeshAsset& load_mesh(const std::string& name) {
+    auto it = meshes.find(name);
+    if (it == meshes.end()) throw std::runtime_error("mjcf: unknown mesh '" + name + "'");
+    MeshAsset& a = it->second;
+    if (a.loaded) return a;
+    std::string path = base_dir + "/" + (meshdir.empty() ? "" : meshdir + "/") + a.file;
+    std::vector<double> v;
+    std::vector<int> face;
+    std::string ext = a.file.size() >= 4 ? a.file.substr(a.file.size() - 4) : "";
+    for (auto& c : ext) c = (char)std::tolower(c);
+    if (ext == ".stl") {
+      std::vector<float> tri;
+      read_stl(path, tri);
+      // merge repeated vertices (exact float equality, as written by the exporter)
+      std::map<std::array<float, 3>, int> seen;
+      for (size_t k = 0; k < tri.size() / 3; k++) {
+        std::array<float, 3> key = {tri[3 * k], tri[3 * k + 1], tri[3 * k + 2]};
+        auto ins = seen.emplace(key, (int)v.size() / 3);
+        if (ins.second) { v.push_back(key[0]); v.push_back(key[1]); v.push_back(key[2]); }
+        face.push_back(ins.first->second);
+      }
+    } else if (ext == ".obj") {
+      read_obj(path, v, face);
+    } else {
+      throw std::runtime_error("mjcf: mesh format of '" + a.file + "' unsupported (binary STL and OBJ only)");
+    }
+    int nvert = (int)v.size() / 3, nface = (int)face.size() / 3;
+    if (nvert < 4 || nface < 4) throw std::runtime_error("mjcf: mesh '" + name + "' is degenerate");
+    for (int i = 0; i < nvert; i++) for (int k = 0; k < 3; k++) v[3 * i + k] *= a.scale[k];
+    // volume and centre of mass
+    double c0[3] = {0, 0, 0};
+    for (int i = 0; i < nvert; i++) for (int k = 0; k < 3; k++) c0[k] += v[3 * i + k] / nvert;
+    double vol = 0, com[3] = {0, 0, 0};
+    auto tet = [&](int f, const double* o, double p[3][3]) {
+      for (int j = 0; j < 3; j++) for (int k = 0; k < 3; k++) p[j][k] = v[3 * face[3 * f + j] + k] - o[k];
+      double cr[3];
+      hm::cross(cr, p[1], p[2]);
+      return std::fabs(hm::dot3(p[0], cr)) / 6.0;
+    };
+    for (int f = 0; f < nface; f++) {
+      double p[3][3];
+      double tv = tet(f, c0, p);
+      vol += tv;
+      for (int k = 0; k < 3; k++) com[k] += tv * (p[0][k] + p[1][k] + p[2][k]) / 4.0;
+    }
+    if (vol < kMinVal) throw std::runtime_error("mjcf: mesh '" + name + "' has no volume");
+    for (int k = 0; k < 3; k++) com[k] = c0[k] + com[k] / vol;
+    // second moments about the centre of mass: per tetrahedron (apex c0) V/20 (sum p p^T + s s^T)
+    double C[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    for (int f = 0; f < nface; f++) {
+      double p[3][3];
+      double tv = tet(f, c0, p);
+      double q[4][3], sum[3] = {0, 0, 0};
+      for (int k = 0; k < 3; k++) q[3][k] = c0[k] - com[k];
+      for (int j = 0; j < 3; j++) for (int k = 0; k < 3; k++) q[j][k] = p[j][k] + c0[k] - com[k];
+      for (int j = 0; j < 4; j++) for (int k = 0; k < 3; k++) sum[k] += q[j][k];
+      for (int r = 0; r < 3; r++)
+        for (int c = 0; c < 3; c++) {
+          double acc = sum[r] * sum[c];
+          for (int j = 0; j < 4; j++) acc += q[j][r] * q[j][c];
+          C[3 * r + c] += tv / 20.0 * acc;
+        }
+    }
+    double trC = C[0] + C[4] + C[8];
+    double I[9];
+    for (int r = 0; r < 3; r++) for (int c = 0; c < 3; c++) I[3 * r + c] = (r == c ? trC : 0.0) - C[3 * r + c];
+    double ev[3], R[9];
+    hm::eig3(I, ev, R);
+    a.volume = vol;
+    for (int k = 0; k < 3; k++) { a.inertia_unit[k] = ev[k]; a.pos[k] = com[k]; }
+    hm::mat2quat(a.quat, R);
+    a.vert.resize(v.size());
+    for (int i = 0; i < nvert; i++) {
+      double d[3] = {v[3 * i] - com[0], v[3 * i + 1] - com[1], v[3 * i + 2] - com[2]};
+      for (int k = 0; k < 3; k++) {  // mesh frame: columns of R are the principal axes
+        double x = R[k] * d[0] + R[3 + k] * d[1] + R[6 + k] * d[2];
+        a.vert[3 * i + k] = x;
+        a.half[k] = std::max(a.half[k], std::fabs(x));
+      }
+    }
+    a.loaded = true;
+    return a;
   }
 
   // ---- orientation ------------------------------------------------------------------------
@@ -264,7 +428,6 @@ struct Compiler {
     else if (type == "box") gt = GEOM_BOX;
     else if (type == "mesh") gt = GEOM_MESH;
     else throw std::runtime_error("mjcf: geom type '" + type + "' is outside the supported subset");
-    if (gt == GEOM_MESH) throw std::runtime_error("mjcf: mesh geoms are not supported yet");
     double size[3] = {0, 0, 0};
     auto sz = g.reals("size");
     for (size_t i = 0; i < sz.size() && i < 3; i++) size[i] = sz[i];
@@ -281,18 +444,38 @@ struct Compiler {
       hm::z2quat(quat, vec);
       if (gt == GEOM_BOX) size[2] = 0.5 * len; else size[1] = 0.5 * len;
     }
+    // mesh geoms: visual-only ones (no collision bits, zero mass) keep their slot but never open the file
+    MeshAsset* mesh = nullptr;
+    int contype = g.integer("contype", 1), conaffinity = g.integer("conaffinity", 1);
+    if (gt == GEOM_MESH) {
+      bool massless = g.has("mass") && g.real("mass", 0) == 0.0;
+      if (contype != 0 || conaffinity != 0 || !massless) {
+        mesh = &load_mesh(g.str("mesh", ""));
+        if (mesh->vertadr < 0) {
+          mesh->vertadr = (int)m.mesh_vert.size() / 3;
+          m.mesh_vert.insert(m.mesh_vert.end(), mesh->vert.begin(), mesh->vert.end());
+        }
+        // the geom frame absorbs the mesh frame (centre of mass, principal axes)
+        double off[3], q2[4];
+        hm::rot_vec_quat(off, mesh->pos, quat);
+        for (int i = 0; i < 3; i++) pos[i] += off[i];
+        hm::quat_mul(q2, quat, mesh->quat);
+        std::memcpy(quat, q2, sizeof(q2));
+        for (int i = 0; i < 3; i++) size[i] = mesh->half[i];
+      }
+    }
     m.geom_type.push_back(gt);
     m.geom_bodyid.push_back(body);
     m.geom_names.push_back(g.str("name", ""));
     push_n(m.geom_size, size, 3);
     push_n(m.geom_pos, pos, 3);
     push_n(m.geom_quat, quat, 4);
-    m.geom_contype.push_back(g.integer("contype", 1));
-    m.geom_conaffinity.push_back(g.integer("conaffinity", 1));
+    m.geom_contype.push_back(contype);
+    m.geom_conaffinity.push_back(conaffinity);
     m.geom_condim.push_back(g.integer("condim", 3));
     m.geom_priority.push_back(g.integer("priority", 0));
-    m.geom_meshadr.push_back(-1);
-    m.geom_meshnum.push_back(0);
+    m.geom_meshadr.push_back(mesh ? mesh->vertadr : -1);
+    m.geom_meshnum.push_back(mesh ? (int)mesh->vert.size() / 3 : 0);
     double friction[3] = {1, 0.005, 0.0001};
     auto fr = g.reals("friction");
     for (size_t i = 0; i < fr.size() && i < 3; i++) friction[i] = fr[i];
@@ -314,6 +497,7 @@ struct Compiler {
       case GEOM_CAPSULE: rb = size[0] + size[1]; break;
       case GEOM_CYLINDER: rb = std::sqrt(size[0] * size[0] + size[1] * size[1]); break;
       case GEOM_BOX: rb = std::sqrt(size[0] * size[0] + size[1] * size[1] + size[2] * size[2]); break;
+      case GEOM_MESH: rb = std::sqrt(size[0] * size[0] + size[1] * size[1] + size[2] * size[2]); break;  // box bound
       default: rb = 0;
     }
     m.geom_rbound.push_back(rb);
@@ -329,6 +513,7 @@ struct Compiler {
       }
       case GEOM_CYLINDER: vol = kPi * size[0] * size[0] * 2 * size[1]; break;
       case GEOM_BOX: vol = 8 * size[0] * size[1] * size[2]; break;
+      case GEOM_MESH: vol = mesh ? mesh->volume : 0; break;
       default: vol = 0;
     }
     if (g.has("mass")) t.mass = g.real("mass", 0);
@@ -361,6 +546,9 @@ struct Compiler {
         t.inertia[0] = mass * (size[1] * size[1] + size[2] * size[2]) / 3;
         t.inertia[1] = mass * (size[0] * size[0] + size[2] * size[2]) / 3;
         t.inertia[2] = mass * (size[0] * size[0] + size[1] * size[1]) / 3;
+        break;
+      case GEOM_MESH:
+        if (mesh) for (int i = 0; i < 3; i++) t.inertia[i] = mass * mesh->inertia_unit[i] / mesh->volume;
         break;
       default: break;
     }
@@ -807,6 +995,7 @@ struct Compiler {
         if (auto* a = ch->attr("angle")) angle_degree = (*a != "radian");
         if (auto* a = ch->attr("eulerseq")) eulerseq = *a;
         if (auto* a = ch->attr("autolimits")) autolimits = parse_bool(*a);
+        if (auto* a = ch->attr("meshdir")) meshdir = *a;
         if (auto* a = ch->attr("coordinate"))
           if (*a != "local") throw std::runtime_error("mjcf: only coordinate=local is supported");
       } else if (ch->tag == "option") {
@@ -827,9 +1016,11 @@ struct Compiler {
     }
     for (auto& ch : root.children)
       if (ch->tag == "default") parse_default(*ch, nullptr, true);
+    for (auto& ch : root.children)
+      if (ch->tag == "asset") parse_assets(*ch);
     const XmlNode* world = nullptr;
     for (auto& ch : root.children)
-      if (ch->tag == "worldbody") world = ch.get();
+      if (ch->tag == "worldbody") { world = ch.get(); break; }  // compile_mjcf_string merged the others into it
     if (!world) throw std::runtime_error("mjcf: no <worldbody>");
     parse_body(*world, -1, "");
     for (auto& ch : root.children)
@@ -882,6 +1073,15 @@ std::vector<uint8_t> Model::serialize() const {
 Model compile_mjcf_string(const std::string& xml, const std::string& base_dir, double timestep) {
   XmlParser parser(xml);
   auto root = parser.parse();
+  // several <worldbody> elements (resolved <include>s) are one world body, children in document order
+  XmlNode* first = nullptr;
+  for (auto& ch : root->children) {
+    if (ch->tag != "worldbody") continue;
+    if (!first) { first = ch.get(); continue; }
+    for (auto& g : ch->children) first->children.push_back(std::move(g));
+    ch->children.clear();
+    ch->tag = "worldbody_merged";
+  }
   Compiler c;
   c.base_dir = base_dir;
   return c.compile(*root, timestep);

@@ -35,7 +35,7 @@ enum { TOKP_OBJ_BODY = 1, TOKP_OBJ_JOINT = 3, TOKP_OBJ_GEOM = 5, TOKP_OBJ_SITE =
 
 /* task kinds: which MT::Residuals override runs on the device
  * (src/ModelTranslator/Acrobot.cpp:26-55, Walker.cpp:59-90) */
-enum { TOKP_TASK_ACROBOT = 0, TOKP_TASK_WALKER = 1 };
+enum { TOKP_TASK_ACROBOT = 0, TOKP_TASK_WALKER = 1, TOKP_TASK_REACHING = 2 /* pandaReaching, src/ModelTranslator/Reaching.cpp:28-60 */ };
 
 /* key-point methods (include/KeyPointGenerator.h:34-43) */
 enum {

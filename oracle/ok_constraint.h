@@ -102,6 +102,15 @@ void contact_param(const Model* m, Contact<R>* con, int g1, int g2, R* margin, R
   con->friction[3] = R(fri[2]); con->friction[4] = R(fri[2]);
 }
 
+template <class R>
+int plane_convex(const Model* m, Contact<R>* con, R margin, const R* pos1, const R* mat1, int g2, const R* pos2, const R* mat2);
+template <class R>
+int convex_convex(const Model* m, Contact<R>* con, R margin, int g1, const R* pos1, const R* mat1, int g2, const R* pos2,
+                  const R* mat2);
+inline bool is_convex_type(int t) {
+  return t == GEOM_SPHERE || t == GEOM_CAPSULE || t == GEOM_CYLINDER || t == GEOM_BOX || t == GEOM_MESH;
+}
+
 // mj_collision over the statically filtered pair list
 template <class R>
 void collision(const Model* m, Data<R>* d) {
@@ -125,7 +134,14 @@ void collision(const Model* m, Data<R>* d) {
       if (t2 == GEOM_SPHERE) n = plane_sphere(tmp, margin, pos1, mat1, pos2, R(m->geom_size[3 * g2]));
       else if (t2 == GEOM_CAPSULE) n = plane_capsule(tmp, margin, pos1, mat1, pos2, mat2, &m->geom_size[3 * g2]);
       else if (t2 == GEOM_BOX) n = plane_box(tmp, margin, pos1, mat1, pos2, mat2, &m->geom_size[3 * g2]);
+      else if (t2 == GEOM_MESH) n = plane_convex(m, tmp, margin, pos1, mat1, g2, pos2, mat2);
       else { d->warning |= 32; continue; }
+    } else if ((t1 == GEOM_MESH || t2 == GEOM_MESH) && is_convex_type(t1) && is_convex_type(t2)) {
+      // mj_collideGeoms: bounding-sphere filter, then the general convex collider (mjc_Convex)
+      R dif[3] = {pos2[0] - pos1[0], pos2[1] - pos1[1], pos2[2] - pos1[2]};
+      R bound = R(m->geom_rbound[g1]) + R(m->geom_rbound[g2]) + margin;
+      if (dot3(dif, dif) > bound * bound) continue;
+      n = convex_convex(m, tmp, margin, g1, pos1, mat1, g2, pos2, mat2);
     } else {
       d->warning |= 32;  // pair type outside the implemented subset
       continue;
@@ -316,3 +332,5 @@ void reference_constraint(const Model* m, Data<R>* d) {
 }
 
 }  // namespace ok
+
+#include "ok_convex.h"

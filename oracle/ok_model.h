@@ -28,14 +28,14 @@ struct Model {
   const int32_t *body_parentid, *body_rootid, *body_weldid, *body_jntadr, *body_jntnum, *body_dofadr, *body_dofnum;
   const int32_t *jnt_type, *jnt_qposadr, *jnt_dofadr, *jnt_bodyid, *jnt_limited;
   const int32_t *dof_bodyid, *dof_jntid, *dof_parentid;
-  const int32_t *geom_type, *geom_bodyid, *geom_condim, *geom_priority, *pair_geom1, *pair_geom2;
+  const int32_t *geom_type, *geom_bodyid, *geom_condim, *geom_priority, *pair_geom1, *pair_geom2, *geom_meshadr, *geom_meshnum;
   const int32_t *actuator_dofadr, *actuator_ctrllimited, *actuator_forcelimited, *actuator_biastype, *actuator_trnid;
   const double *qpos0, *body_pos, *body_quat, *body_ipos, *body_iquat, *body_mass, *body_inertia, *body_invweight0,
       *body_gravcomp;
   const double *jnt_pos, *jnt_axis, *jnt_range, *jnt_solref, *jnt_solimp, *jnt_margin;
   const double *dof_armature, *dof_damping, *dof_invweight0;
   const double *geom_size, *geom_pos, *geom_quat, *geom_friction, *geom_solref, *geom_solimp, *geom_margin, *geom_gap,
-      *geom_solmix, *geom_rbound;
+      *geom_solmix, *geom_rbound, *mesh_vert;
   const double *actuator_gear, *actuator_ctrlrange, *actuator_forcerange, *actuator_gainprm, *actuator_biasprm;
 
   const int32_t* ip(const char* n) const {
@@ -86,7 +86,7 @@ struct Model {
     P(body_parentid); P(body_rootid); P(body_weldid); P(body_jntadr); P(body_jntnum); P(body_dofadr); P(body_dofnum);
     P(jnt_type); P(jnt_qposadr); P(jnt_dofadr); P(jnt_bodyid); P(jnt_limited);
     P(dof_bodyid); P(dof_jntid); P(dof_parentid);
-    P(geom_type); P(geom_bodyid); P(geom_condim); P(geom_priority); P(pair_geom1); P(pair_geom2);
+    P(geom_type); P(geom_bodyid); P(geom_condim); P(geom_priority); P(pair_geom1); P(pair_geom2); P(geom_meshadr); P(geom_meshnum);
     P(actuator_dofadr); P(actuator_ctrllimited); P(actuator_forcelimited); P(actuator_biastype); P(actuator_trnid);
 #undef P
 #define P(n) n = rp(#n)
@@ -95,7 +95,7 @@ struct Model {
     P(jnt_pos); P(jnt_axis); P(jnt_range); P(jnt_solref); P(jnt_solimp); P(jnt_margin);
     P(dof_armature); P(dof_damping); P(dof_invweight0);
     P(geom_size); P(geom_pos); P(geom_quat); P(geom_friction); P(geom_solref); P(geom_solimp); P(geom_margin);
-    P(geom_gap); P(geom_solmix); P(geom_rbound);
+    P(geom_gap); P(geom_solmix); P(geom_rbound); P(mesh_vert);
     P(actuator_gear); P(actuator_ctrlrange); P(actuator_forcerange); P(actuator_gainprm); P(actuator_biasprm);
 #undef P
   }

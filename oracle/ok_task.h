@@ -10,7 +10,7 @@
 
 namespace ok {
 
-enum { TASK_ACROBOT = 0, TASK_WALKER = 1 };
+enum { TASK_ACROBOT = 0, TASK_WALKER = 1, TASK_REACHING = 2 };
 enum { KP_SET_INTERVAL = 0, KP_ADAPTIVE_JERK = 1, KP_ADAPTIVE_ACCEL = 2, KP_ITERATIVE_ERROR = 3, KP_VELOCITY_CHANGE = 4 };
 
 // Mirrors tokp_task_desc (include/tokp.h) field for field.
@@ -114,6 +114,9 @@ void residuals(const Task& t, const Data<R>* d, R* r) {
       r[1] = q(2) - R(t.target[1]);
       r[2] = v(1) - R(t.target[2]);
       for (int i = 0; i < t.m; i++) r[3 + i] = u(i) - R(t.target[3 + i]);
+      break;
+    case TASK_REACHING:  // Reaching.cpp:28-60: joint positions against the goal configuration, then joint velocities
+      for (int i = 0; i < t.n; i++) { r[i] = q(i) - R(t.target[i]); r[t.n + i] = v(i); }
       break;
     default: break;
   }

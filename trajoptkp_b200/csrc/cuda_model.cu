@@ -108,14 +108,14 @@ int ensure_device_model(const tokp_model* mc, const DM** out) {
   AI(body_depth) AI(body_subtreemask_lo) AI(body_subtreemask_hi)
   AI(jnt_type) AI(jnt_qposadr) AI(jnt_dofadr) AI(jnt_bodyid) AI(jnt_limited)
   AI(dof_bodyid) AI(dof_jntid) AI(dof_parentid) AI(dof_ancmask_lo) AI(dof_ancmask_hi)
-  AI(geom_type) AI(geom_bodyid) AI(geom_condim) AI(geom_priority) AI(pair_geom1) AI(pair_geom2)
+  AI(geom_type) AI(geom_bodyid) AI(geom_condim) AI(geom_priority) AI(pair_geom1) AI(pair_geom2) AI(geom_meshadr) AI(geom_meshnum)
   AI(actuator_trnid) AI(actuator_dofadr) AI(actuator_ctrllimited) AI(actuator_forcelimited) AI(actuator_biastype)
   AR(qpos0) AR(body_pos) AR(body_quat) AR(body_ipos) AR(body_iquat) AR(body_mass) AR(body_inertia) AR(body_invweight0)
   AR(body_gravcomp)
   AR(jnt_pos) AR(jnt_axis) AR(jnt_range) AR(jnt_solref) AR(jnt_solimp) AR(jnt_margin)
   AR(dof_armature) AR(dof_damping) AR(dof_invweight0)
   AR(geom_size) AR(geom_pos) AR(geom_quat) AR(geom_friction) AR(geom_solref) AR(geom_solimp) AR(geom_margin) AR(geom_gap)
-  AR(geom_solmix) AR(geom_rbound)
+  AR(geom_solmix) AR(geom_rbound) AR(mesh_vert)
   AR(actuator_gear) AR(actuator_ctrlrange) AR(actuator_forcerange) AR(actuator_gainprm) AR(actuator_biasprm)
 #undef AI
 #undef AR

@@ -14,7 +14,7 @@ struct DM {
   const int *jnt_type, *jnt_qposadr, *jnt_dofadr, *jnt_bodyid, *jnt_limited;
   const int *dof_bodyid, *dof_jntid, *dof_parentid;
   const unsigned *dof_ancmask_lo, *dof_ancmask_hi;
-  const int *geom_type, *geom_bodyid, *geom_condim, *geom_priority, *pair_geom1, *pair_geom2;
+  const int *geom_type, *geom_bodyid, *geom_condim, *geom_priority, *pair_geom1, *pair_geom2, *geom_meshadr, *geom_meshnum;
   const int *actuator_trnid, *actuator_dofadr, *actuator_ctrllimited, *actuator_forcelimited, *actuator_biastype;
   // real arrays
   const double *qpos0, *body_pos, *body_quat, *body_ipos, *body_iquat, *body_mass, *body_inertia, *body_invweight0,
@@ -22,7 +22,7 @@ struct DM {
   const double *jnt_pos, *jnt_axis, *jnt_range, *jnt_solref, *jnt_solimp, *jnt_margin;
   const double *dof_armature, *dof_damping, *dof_invweight0;
   const double *geom_size, *geom_pos, *geom_quat, *geom_friction, *geom_solref, *geom_solimp, *geom_margin, *geom_gap,
-      *geom_solmix, *geom_rbound;
+      *geom_solmix, *geom_rbound, *mesh_vert;
   const double *actuator_gear, *actuator_ctrlrange, *actuator_forcerange, *actuator_gainprm, *actuator_biasprm;
 };
 

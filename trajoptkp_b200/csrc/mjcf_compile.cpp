@@ -797,6 +797,7 @@ struct Compiler {
         case GEOM_CAPSULE: return 2;
         case GEOM_CYLINDER: return 4;
         case GEOM_BOX: return 4;
+        case GEOM_MESH: return 1;  // deepest vertex only (no hull graph; see step_convex.cuh)
         default: return 4;
       }
     }

@@ -2,6 +2,7 @@
 // mj_referenceConstraint) for joint limits and frictionless / pyramidal contacts.
 #pragma once
 #include "step_pos.cuh"
+#include "step_convex.cuh"
 
 namespace tk {
 
@@ -37,7 +38,7 @@ TK_DEV void contact_param(const DM& m, int g1, int g2, ConParam& c) {
 }
 
 TK_DEV int pair_slots(int t1, int t2) {
-  if (t1 == GEOM_PLANE) return t2 == GEOM_SPHERE ? 1 : (t2 == GEOM_CAPSULE ? 2 : 4);
+  if (t1 == GEOM_PLANE) return (t2 == GEOM_SPHERE || t2 == GEOM_MESH) ? 1 : (t2 == GEOM_CAPSULE ? 2 : 4);
   if (t1 == GEOM_BOX && t2 == GEOM_BOX) return 8;
   if (t1 == GEOM_CAPSULE && t2 == GEOM_BOX) return 2;
   return 1;
@@ -125,10 +126,19 @@ TK_DEV void collision(const DM& m, WS& w, const Grp<G, NV>& g, int& status) {
             for (int k = 3; k < 6; k++) w.con_frame[6 * s + k] = 0.0;
             n++;
           }
+        } else if (NV == 0 && t2 == GEOM_MESH) {
+          n = plane_convex(m, margin, pos1, mat1, g2, pos2, mat2, &w.con_dist[slot], &w.con_pos[3 * slot], &w.con_frame[6 * slot]);
         } else {
           status |= ST_UNSUPPORTED;
         }
       }
+    } else if (NV == 0 && (t1 == GEOM_MESH || t2 == GEOM_MESH) && is_convex_type(t1) && is_convex_type(t2)) {
+      // mj_collideGeoms: bounding-sphere filter, then the general convex collider.  Only the generic (NV = 0)
+      // instantiation carries this code: the specialised walker / acrobot kernels have no mesh geoms
+      double d[3] = {pos2[0] - pos1[0], pos2[1] - pos1[1], pos2[2] - pos1[2]};
+      double bound = m.geom_rbound[g1] + m.geom_rbound[g2] + margin;
+      if (dot3(d, d) <= bound * bound)
+        n = convex_convex(m, margin, g1, pos1, mat1, g2, pos2, mat2, &w.con_dist[slot], &w.con_pos[3 * slot], &w.con_frame[6 * slot]);
     } else {
       status |= ST_UNSUPPORTED;
     }

@@ -1,0 +1,261 @@
+// General convex collider of the batched step: mesh (convex hull) / box / sphere / capsule / cylinder pairs and
+// plane-mesh, for the Franka scenes (reaching, box_sweep, push_*).
+//
+// MuJoCo: engine_collision_convex.c (mjc_Convex, mjc_PlaneConvex, mjccd_support / mjccd_center) on top of libccd's
+// ccdMPRPenetration - Minkowski Portal Refinement (G. Snethen, XenoCollide, 2008) with tolerance 1e-6, at most 50
+// refinement steps, each geom inflated by margin / 2; contact = {dist = margin - depth, normal = dir (geom1 ->
+// geom2), pos = midpoint of the witnesses}; one contact per pair (mjENBL_MULTICCD is off by default).  Call sites on
+// the reference path: every mj_step / mj_stepSkip (src/Differentiator/Differentiator.cpp:69,118; iLQR.cpp:222,914).
+//
+// One lane runs one pair (the lanes of a group take the pairs of the world in turn, as the primitive colliders do);
+// the support function of a mesh scans its merged vertices, whose maximiser is the hull's.  plane-mesh yields the
+// deepest vertex only (MuJoCo adds up to three hull neighbours; no hull graph is built).
+#pragma once
+#include "step.cuh"
+
+namespace tk {
+
+constexpr double kMprTol = 1e-6;
+constexpr int kMprIter = 50;
+constexpr double kCcdEps = 2.220446049250313e-16;
+
+TK_DEV bool ccd_zero(double x) { return fabs(x) < kCcdEps; }
+TK_DEV bool ccd_zero3(const double* v) { return ccd_zero(v[0]) && ccd_zero(v[1]) && ccd_zero(v[2]); }
+TK_DEV bool is_convex_type(int t) {
+  return t == GEOM_SPHERE || t == GEOM_CAPSULE || t == GEOM_CYLINDER || t == GEOM_BOX || t == GEOM_MESH;
+}
+
+struct CvxObj {
+  int geom, type;
+  const double* pos;
+  const double* mat;
+  double margin;
+};
+
+// mjccd_support: farthest point of the inflated geom along the unit world direction dir
+TK_DEV void convex_support(const DM& m, const CvxObj& o, const double* dir, double* res) {
+  const double* size = &m.geom_size[3 * o.geom];
+  double ld[3], lp[3] = {0.0, 0.0, 0.0};
+  for (int k = 0; k < 3; k++) ld[k] = o.mat[k] * dir[0] + o.mat[3 + k] * dir[1] + o.mat[6 + k] * dir[2];
+  if (o.type == GEOM_MESH) {
+    const double* v = &m.mesh_vert[3 * m.geom_meshadr[o.geom]];
+    int n = m.geom_meshnum[o.geom], best = 0;
+    double bd = v[0] * ld[0] + v[1] * ld[1] + v[2] * ld[2];
+    for (int i = 1; i < n; i++) {
+      double dd = v[3 * i] * ld[0] + v[3 * i + 1] * ld[1] + v[3 * i + 2] * ld[2];
+      if (dd > bd) { bd = dd; best = i; }
+    }
+    for (int k = 0; k < 3; k++) lp[k] = v[3 * best + k];
+  } else if (o.type == GEOM_BOX) {
+    for (int k = 0; k < 3; k++) lp[k] = ld[k] >= 0.0 ? size[k] : -size[k];
+  } else if (o.type == GEOM_SPHERE) {
+    for (int k = 0; k < 3; k++) lp[k] = ld[k] * size[0];
+  } else if (o.type == GEOM_CAPSULE) {
+    for (int k = 0; k < 3; k++) lp[k] = ld[k] * size[0];
+    lp[2] = lp[2] + (ld[2] >= 0.0 ? size[1] : -size[1]);
+  } else if (o.type == GEOM_CYLINDER) {
+    double r2 = ld[0] * ld[0] + ld[1] * ld[1];
+    if (r2 > kMinVal * kMinVal) {
+      double s = size[0] / sqrt(r2);
+      lp[0] = ld[0] * s; lp[1] = ld[1] * s;
+    }
+    lp[2] = ld[2] >= 0.0 ? size[1] : -size[1];
+  }
+  for (int k = 0; k < 3; k++)
+    res[k] = o.pos[k] + o.mat[3 * k] * lp[0] + o.mat[3 * k + 1] * lp[1] + o.mat[3 * k + 2] * lp[2] + dir[k] * o.margin;
+}
+
+struct MprPt { double v[3], v1[3], v2[3]; };
+
+TK_DEV void mpr_support(const DM& m, const CvxObj& a, const CvxObj& b, const double* dir, MprPt& p) {
+  double nd[3] = {-dir[0], -dir[1], -dir[2]};
+  convex_support(m, a, dir, p.v1);
+  convex_support(m, b, nd, p.v2);
+  for (int k = 0; k < 3; k++) p.v[k] = p.v1[k] - p.v2[k];
+}
+
+// closest point of triangle (a, b, c) to the origin (Ericson, Real-Time Collision Detection, 5.1.5)
+TK_DEV void closest_on_triangle_to_origin(const double* a, const double* b, const double* c, double* out) {
+  double ab[3], ac[3], ap[3], bp[3], cp[3];
+  for (int k = 0; k < 3; k++) { ab[k] = b[k] - a[k]; ac[k] = c[k] - a[k]; ap[k] = -a[k]; bp[k] = -b[k]; cp[k] = -c[k]; }
+  double d1 = dot3(ab, ap), d2 = dot3(ac, ap);
+  if (d1 <= 0.0 && d2 <= 0.0) { for (int k = 0; k < 3; k++) out[k] = a[k]; return; }
+  double d3 = dot3(ab, bp), d4 = dot3(ac, bp);
+  if (d3 >= 0.0 && d4 <= d3) { for (int k = 0; k < 3; k++) out[k] = b[k]; return; }
+  double vc = d1 * d4 - d3 * d2;
+  if (vc <= 0.0 && d1 >= 0.0 && d3 <= 0.0) {
+    double v = d1 / (d1 - d3);
+    for (int k = 0; k < 3; k++) out[k] = a[k] + v * ab[k];
+    return;
+  }
+  double d5 = dot3(ab, cp), d6 = dot3(ac, cp);
+  if (d6 >= 0.0 && d5 <= d6) { for (int k = 0; k < 3; k++) out[k] = c[k]; return; }
+  double vb = d5 * d2 - d1 * d6;
+  if (vb <= 0.0 && d2 >= 0.0 && d6 <= 0.0) {
+    double w = d2 / (d2 - d6);
+    for (int k = 0; k < 3; k++) out[k] = a[k] + w * ac[k];
+    return;
+  }
+  double va = d3 * d6 - d5 * d4;
+  if (va <= 0.0 && (d4 - d3) >= 0.0 && (d5 - d6) >= 0.0) {
+    double w = (d4 - d3) / ((d4 - d3) + (d5 - d6));
+    for (int k = 0; k < 3; k++) out[k] = b[k] + w * (c[k] - b[k]);
+    return;
+  }
+  double denom = 1.0 / (va + vb + vc);
+  double v = vb * denom, w = vc * denom;
+  for (int k = 0; k < 3; k++) out[k] = a[k] + ab[k] * v + ac[k] * w;
+}
+
+TK_DEV void mpr_portal_dir(const MprPt* p, double* dir) {
+  double e1[3], e2[3];
+  for (int k = 0; k < 3; k++) { e1[k] = p[2].v[k] - p[1].v[k]; e2[k] = p[3].v[k] - p[1].v[k]; }
+  cross3(dir, e1, e2);
+  normalize3(dir);
+}
+
+TK_DEV bool mpr_reach_tolerance(const MprPt* p, const MprPt& v4, const double* dir) {
+  double dv4 = dot3(v4.v, dir);
+  double d1 = dv4 - dot3(p[1].v, dir), d2 = dv4 - dot3(p[2].v, dir), d3 = dv4 - dot3(p[3].v, dir);
+  double mn = d1 < d2 ? d1 : d2;
+  if (d3 < mn) mn = d3;
+  return mn <= kMprTol;
+}
+
+TK_DEV void mpr_expand(MprPt* p, const MprPt& v4) {
+  double v4v0[3];
+  cross3(v4v0, v4.v, p[0].v);
+  if (dot3(p[1].v, v4v0) > 0.0) {
+    if (dot3(p[2].v, v4v0) > 0.0) p[1] = v4; else p[3] = v4;
+  } else {
+    if (dot3(p[3].v, v4v0) > 0.0) p[2] = v4; else p[1] = v4;
+  }
+}
+
+// ccdMPRPenetration: 1 and depth / dir / pos when the inflated geoms intersect, else 0
+TK_DEV int mpr_penetration(const DM& m, const CvxObj& a, const CvxObj& b, double* depth, double* dir_out, double* pos_out) {
+  MprPt p[4];  // p[0] = interior point, p[1..3] = portal
+  double dir[3], va[3], vb[3];
+  for (int k = 0; k < 3; k++) { p[0].v1[k] = a.pos[k]; p[0].v2[k] = b.pos[k]; p[0].v[k] = a.pos[k] - b.pos[k]; }
+  if (ccd_zero3(p[0].v)) p[0].v[0] = p[0].v[0] + 10.0 * kCcdEps;
+  for (int k = 0; k < 3; k++) dir[k] = -p[0].v[k];
+  normalize3(dir);
+  mpr_support(m, a, b, dir, p[1]);
+  double d = dot3(p[1].v, dir);
+  if (ccd_zero(d) || d < 0.0) return 0;
+  cross3(dir, p[0].v, p[1].v);
+  if (ccd_zero3(dir)) {
+    if (ccd_zero3(p[1].v)) {
+      *depth = 0.0;
+      for (int k = 0; k < 3; k++) { dir_out[k] = 0.0; pos_out[k] = 0.5 * (p[1].v1[k] + p[1].v2[k]); }
+      return 1;
+    }
+    for (int k = 0; k < 3; k++) { dir_out[k] = p[1].v[k]; pos_out[k] = 0.5 * (p[1].v1[k] + p[1].v2[k]); }
+    double nn = sqrt(dot3(dir_out, dir_out));
+    *depth = nn;
+    for (int k = 0; k < 3; k++) dir_out[k] = dir_out[k] / nn;
+    return 1;
+  }
+  normalize3(dir);
+  mpr_support(m, a, b, dir, p[2]);
+  d = dot3(p[2].v, dir);
+  if (ccd_zero(d) || d < 0.0) return 0;
+  for (int k = 0; k < 3; k++) { va[k] = p[1].v[k] - p[0].v[k]; vb[k] = p[2].v[k] - p[0].v[k]; }
+  cross3(dir, va, vb);
+  normalize3(dir);
+  if (dot3(dir, p[0].v) > 0.0) {
+    MprPt t = p[1]; p[1] = p[2]; p[2] = t;
+    for (int k = 0; k < 3; k++) dir[k] = -dir[k];
+  }
+  for (int guard = 0;; guard++) {
+    if (guard > 100) return 0;
+    mpr_support(m, a, b, dir, p[3]);
+    d = dot3(p[3].v, dir);
+    if (ccd_zero(d) || d < 0.0) return 0;
+    bool cont = false;
+    cross3(va, p[1].v, p[3].v);
+    d = dot3(va, p[0].v);
+    if (d < 0.0 && !ccd_zero(d)) { p[2] = p[3]; cont = true; }
+    if (!cont) {
+      cross3(va, p[3].v, p[2].v);
+      d = dot3(va, p[0].v);
+      if (d < 0.0 && !ccd_zero(d)) { p[1] = p[3]; cont = true; }
+    }
+    if (!cont) break;
+    for (int k = 0; k < 3; k++) { va[k] = p[1].v[k] - p[0].v[k]; vb[k] = p[2].v[k] - p[0].v[k]; }
+    cross3(dir, va, vb);
+    normalize3(dir);
+  }
+  MprPt v4;
+  for (int guard = 0;; guard++) {
+    mpr_portal_dir(p, dir);
+    d = dot3(dir, p[1].v);
+    if (ccd_zero(d) || d > 0.0) break;
+    mpr_support(m, a, b, dir, v4);
+    d = dot3(v4.v, dir);
+    if (!(ccd_zero(d) || d > 0.0) || mpr_reach_tolerance(p, v4, dir) || guard > 1000) return 0;
+    mpr_expand(p, v4);
+  }
+  for (int it = 0;; it++) {
+    mpr_portal_dir(p, dir);
+    mpr_support(m, a, b, dir, v4);
+    if (mpr_reach_tolerance(p, v4, dir) || it > kMprIter) {
+      double w[3];
+      closest_on_triangle_to_origin(p[1].v, p[2].v, p[3].v, w);
+      *depth = sqrt(dot3(w, w));
+      if (ccd_zero3(w)) for (int k = 0; k < 3; k++) w[k] = dir[k];
+      normalize3(w);
+      for (int k = 0; k < 3; k++) dir_out[k] = w[k];
+      double b4[4], t[3];
+      cross3(t, p[1].v, p[2].v); b4[0] = dot3(t, p[3].v);
+      cross3(t, p[3].v, p[2].v); b4[1] = dot3(t, p[0].v);
+      cross3(t, p[0].v, p[1].v); b4[2] = dot3(t, p[3].v);
+      cross3(t, p[2].v, p[1].v); b4[3] = dot3(t, p[0].v);
+      double sum = b4[0] + b4[1] + b4[2] + b4[3];
+      if (ccd_zero(sum) || sum < 0.0) {
+        b4[0] = 0.0;
+        cross3(t, p[2].v, p[3].v); b4[1] = dot3(t, dir);
+        cross3(t, p[3].v, p[1].v); b4[2] = dot3(t, dir);
+        cross3(t, p[1].v, p[2].v); b4[3] = dot3(t, dir);
+        sum = b4[1] + b4[2] + b4[3];
+      }
+      double inv = 1.0 / sum;
+      for (int k = 0; k < 3; k++) {
+        double p1 = 0.0, p2 = 0.0;
+        for (int i = 0; i < 4; i++) { p1 = p1 + b4[i] * p[i].v1[k]; p2 = p2 + b4[i] * p[i].v2[k]; }
+        pos_out[k] = 0.5 * (p1 + p2) * inv;
+      }
+      return 1;
+    }
+    mpr_expand(p, v4);
+  }
+}
+
+// mjc_Convex: writes dist, pos[3], frame[0:6] (tangent hint zero); returns the number of contacts (0 or 1)
+TK_DEV int convex_convex(const DM& m, double margin, int g1, const double* pos1, const double* mat1, int g2, const double* pos2,
+                         const double* mat2, double* dist, double* pos, double* frame) {
+  CvxObj a{g1, m.geom_type[g1], pos1, mat1, 0.5 * margin};
+  CvxObj b{g2, m.geom_type[g2], pos2, mat2, 0.5 * margin};
+  double depth, dir[3], cp[3];
+  if (!mpr_penetration(m, a, b, &depth, dir, cp)) return 0;
+  if (dir[0] == 0.0 && dir[1] == 0.0 && dir[2] == 0.0) return 0;
+  *dist = margin - depth;
+  for (int k = 0; k < 3; k++) { frame[k] = dir[k]; pos[k] = cp[k]; frame[3 + k] = 0.0; }
+  return 1;
+}
+
+// mjc_PlaneConvex, deepest point only
+TK_DEV int plane_convex(const DM& m, double margin, const double* pos1, const double* mat1, int g2, const double* pos2,
+                        const double* mat2, double* dist, double* pos, double* frame) {
+  double nrm[3] = {mat1[2], mat1[5], mat1[8]}, nd[3] = {-mat1[2], -mat1[5], -mat1[8]}, vec[3], dif[3];
+  CvxObj o{g2, m.geom_type[g2], pos2, mat2, 0.0};
+  convex_support(m, o, nd, vec);
+  for (int k = 0; k < 3; k++) dif[k] = vec[k] - pos1[k];
+  double dd = dot3(dif, nrm);
+  if (dd > margin) return 0;
+  *dist = dd;
+  for (int k = 0; k < 3; k++) { pos[k] = vec[k] - 0.5 * dd * nrm[k]; frame[k] = nrm[k]; frame[3 + k] = 0.0; }
+  return 1;
+}
+
+}  // namespace tk

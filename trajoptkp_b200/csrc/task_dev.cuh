@@ -1,5 +1,5 @@
 // Device restatement of the task residuals / cost (MT::Residuals overrides:
-// src/ModelTranslator/Acrobot.cpp:26-55, src/ModelTranslator/Walker.cpp:59-90;
+// src/ModelTranslator/Acrobot.cpp:26-55, src/ModelTranslator/Walker.cpp:59-90, src/ModelTranslator/Reaching.cpp:28-60;
 // MT::CostFunction src/ModelTranslator/ModelTranslator.cpp:314-327).
 #pragma once
 #include "traj.h"
@@ -22,6 +22,9 @@ __device__ inline void task_residuals(const TaskDev& t, const double* q, const d
       r[1] = q[t.qpos_adr[2]] - target[1];
       r[2] = v[t.dof_adr[1]] - target[2];
       for (int i = 0; i < t.m; i++) r[3 + i] = u[t.ctrl_adr[i]] - target[3 + i];
+      break;
+    case TOKP_TASK_REACHING:  // Reaching.cpp:28-60: joint positions against the goal configuration, then velocities
+      for (int i = 0; i < t.n; i++) { r[i] = q[t.qpos_adr[i]] - target[i]; r[t.n + i] = v[t.dof_adr[i]]; }
       break;
     default:
       for (int i = 0; i < t.nr; i++) r[i] = 0.0;

@@ -15,6 +15,7 @@ ASSETS = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "assets"
 TASKS = {
     "acrobot": ("tasks/acrobot.yaml", "models/acrobot.xml", capi.TASK_ACROBOT),
     "walker_run": ("tasks/walker_run.yaml", "models/walker_plane.xml", capi.TASK_WALKER),
+    "reaching": ("tasks/reaching.yaml", "models/franka/reaching_scene.xml", capi.TASK_REACHING),
 }
 
 
@@ -55,8 +56,10 @@ class TaskConfig:
         self.resid_target_sizes = []
         for rn, r in cfg["residuals"].items():
             dim = int(r.get("resid_dimension", 1))
-            for _ in range(dim):  # FileHandler.cpp:276-287 replicates the entry resid_dimension times
-                target.append(float(r["target"][0]))
+            for k in range(dim):  # FileHandler.cpp:276-287 replicates the entry resid_dimension times
+                # pandaReaching::Residuals reads residual_list[0].target[i] for its i-th residual (Reaching.cpp:46)
+                first_group = kind == capi.TASK_REACHING and len(target) < dim
+                target.append(float(r["target"][k if first_group else 0]))
                 weight.append(float(r["weight"]))
                 weight_t.append(float(r["weight_terminal"]))
                 self.resid_target_sizes.append(len(r["target"]))
@@ -100,8 +103,11 @@ class TaskConfig:
         start = np.array(vals[:self.n])
         rest = vals[self.n:]
         targets, p = [], 0
-        for sz in self.resid_target_sizes:
-            targets.append(rest[p])  # residual_list[k].target[0]
+        for k, sz in enumerate(self.resid_target_sizes):
+            if self.kind == capi.TASK_REACHING:  # residual_list[0].target[k] for the position residuals, 0 after
+                targets.append(rest[k] if k < self.n else 0.0)
+            else:
+                targets.append(rest[p])  # residual_list[k].target[0]
             p += sz
         return start, np.array(targets)
 

@@ -94,6 +94,21 @@ def cpu_arm(args, tc, snaps, targets, U, steps, warmup, want_flops=True):
     om = oracle.Model(tc.model.blob())
     T = args.horizon
     n_rep = args.cpu_replans
+    if tc.kind == 2 and not np.any(U):
+        # reaching: gravity-compensation initial controls (Reaching.cpp:269-296), restated with the oracle, untimed
+        U = np.array(U, copy=True)
+        S, nu = tc.model.S, tc.model.nu
+        d = oracle.Data(om)
+        for j in range(len(snaps)):
+            d.load(snaps[j])
+            for t in range(T):
+                d.forward()
+                bias = d.get("qfrc_bias")
+                s = d.save()
+                s[S - nu + tc.ctrl_adr] = bias[tc.dof_adr]
+                d.load(s)
+                d.step()
+                U[j, t] = bias[tc.dof_adr]
     ilqr = None
     times, jac = [], []
     flops_per_jac = None
@@ -186,6 +201,11 @@ def main():
     tr = capi.Traj(tc, T, B)
     for b in range(B):
         tr.set_targets(b, targets[b])
+    if tc.kind == capi.TASK_REACHING:
+        # pandaReaching::CreateInitOptimisationControls (Reaching.cpp:269-296): gravity-compensation rollout, on the
+        # device, outside the timed region (the reference also generates it once per trial before Optimise)
+        U[...] = tr.init_controls_gravcomp(snaps)[0]
+        config["initial_controls"] = "gravity compensation (tokp_init_controls_gravcomp)"
     launches0 = capi.lib().tokp_launch_count()
 
     def barrier():

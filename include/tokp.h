@@ -111,6 +111,10 @@ int tokp_step_worlds(const tokp_model* m, const double* snapshots_in, double* sn
 
 /* iLQR::RolloutTrajectory (iLQR.cpp:202-254) for all B trajectories: snapshot0[B][S], U[B][T][m] -> cost[B] */
 int tokp_rollout(tokp_traj* tr, const double* snapshot0, const double* U, double* cost);
+/* pandaReaching::CreateInitOptimisationControls (src/ModelTranslator/Reaching.cpp:269-296): gravity-compensation
+ * rollout from snapshot0[B][S]; control t = qfrc_bias of the state joints at step t (mj_forward), then mj_step.
+ * U_out[B][T][m]; status[B] (optional) receives the per-world warning bits. */
+int tokp_init_controls_gravcomp(tokp_traj* tr, const double* snapshot0, double* U_out, int* status);
 /* KeypointGenerator::GenerateKeyPoints (KeyPointGenerator.cpp:76-135) on the nominal X_old; optional outputs:
  * counts[B][T], indices[B][T][2n] (row lists, in reference order, duplicates kept), pct[B][n] */
 int tokp_keypoints(tokp_traj* tr, int* counts, int* indices, double* pct);

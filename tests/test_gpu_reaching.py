@@ -89,3 +89,30 @@ def test_reaching_optimise_cost(built):
         assert abs(stats[b, 1] - sc["new_cost"]) <= 0.01 * abs(sc["new_cost"]), (stats[b], sc)  # final cost within 1 %
         assert int(stats[b, 2]) == int(sc["num_iterations"])
     assert stats[0, 1] < stats[0, 0]
+
+
+def test_reaching_gravcomp_init_controls(built):
+    """tokp_init_controls_gravcomp == pandaReaching::CreateInitOptimisationControls restated with the oracle:
+    mj_forward, ctrl := qfrc_bias of the arm joints, mj_step (Reaching.cpp:269-296)."""
+    tc = make("reaching")
+    m = tc.model
+    T, B = 25, 3
+    om = oracle_model(tc)
+    snaps = np.stack([perturbed_start(tc, 40 + b, dq=0.1, dv=0.05) for b in range(B)])
+    tr = capi.Traj(tc, T, B)
+    U_dev, st = tr.init_controls_gravcomp(snaps)
+    assert not st.any()
+    d = oracle.Data(om)
+    for b in range(B):
+        d.load(snaps[b])
+        for t in range(T):
+            d.forward()
+            bias = d.get("qfrc_bias")
+            s = d.save()
+            s[m.S - m.nu + tc.ctrl_adr] = bias[tc.dof_adr]
+            d.load(s)
+            d.step()
+            ref = bias[tc.dof_adr]
+            assert np.abs(U_dev[b, t] - ref).max() <= 1e-9 * max(1.0, np.abs(ref).max()), (b, t)
+    # holding the arm: joint velocities stay small under gravity compensation
+    assert np.abs(U_dev).max() > 1.0

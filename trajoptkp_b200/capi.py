@@ -76,6 +76,7 @@ def lib():
         L.tokp_traj_set_snapshot.argtypes = [vp, C.c_int, C.c_int, _dp]
         L.tokp_traj_get_snapshot.argtypes = [vp, C.c_int, C.c_int, _dp]
         L.tokp_rollout.argtypes = [vp, _dp, _dp, _dp]
+        L.tokp_init_controls_gravcomp.argtypes = [vp, _dp, _dp, _ip]
         L.tokp_keypoints.argtypes = [vp, _ip, _ip, _dp]
         L.tokp_traj_set_keypoints.argtypes = [vp, C.c_int, _ip, _ip]
         L.tokp_dynamics_derivs.argtypes = [vp, C.c_int, C.c_double]
@@ -216,6 +217,14 @@ class Traj:
         cost = np.zeros(self.B)
         check(lib().tokp_rollout(self.h, _d(s), _d(U), _d(cost)))
         return cost
+
+    def init_controls_gravcomp(self, snap0):
+        """pandaReaching::CreateInitOptimisationControls on the device: U[B][T][m]."""
+        s = np.ascontiguousarray(np.broadcast_to(np.asarray(snap0, dtype=np.float64), (self.B, self.model.S)))
+        U = np.zeros((self.B, self.T, self.m))
+        st = np.zeros(self.B, dtype=np.int32)
+        check(lib().tokp_init_controls_gravcomp(self.h, _d(s), _d(U), _i(st)))
+        return U, st
 
     def keypoints(self):
         counts = np.zeros((self.B, self.T), dtype=np.int32)

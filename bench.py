@@ -117,7 +117,7 @@ def cpu_arm(args, tc, snaps, targets, U, steps, warmup, want_flops=True):
     def one_replan(j):
         nonlocal ilqr
         ot = oracle.Task(tc.kind, tc.qpos_adr, tc.dof_adr, tc.ctrl_adr, targets[j], tc.weight, tc.weight_terminal,
-                         tc.kp_method, tc.min_N, tc.max_N, tc.jerk_thr, tc.vel_thr, tc.iter_thr)
+                         tc.kp_method, tc.min_N, tc.max_N, tc.jerk_thr, tc.vel_thr, tc.iter_thr, aux=tc.aux)
         ilqr = oracle.ILQR(om, ot, T, threads=max(1, cores - 1))
         ilqr.set_lambda(0.1)
         ilqr.optimise(snaps[j], U[j], 1, 1)
@@ -142,7 +142,7 @@ def cpu_arm(args, tc, snaps, targets, U, steps, warmup, want_flops=True):
         # ALGORITHMIC flops per Jacobian: instrumented oracle run of the reference schedule (stage skipping included)
         saved = ilqr.get("saved").reshape(T + 1, -1)
         ot = oracle.Task(tc.kind, tc.qpos_adr, tc.dof_adr, tc.ctrl_adr, targets[0], tc.weight, tc.weight_terminal,
-                         tc.kp_method, tc.min_N, tc.max_N, tc.jerk_thr, tc.vel_thr, tc.iter_thr)
+                         tc.kp_method, tc.min_N, tc.max_N, tc.jerk_thr, tc.vel_thr, tc.iter_thr, aux=tc.aux)
         fl = [oracle.flops_dynamics_derivs(om, ot, saved[t], list(range(tc.n))) for t in range(1, T, max(1, T // 8))]
         flops_per_jac = float(np.mean(fl))
     ms = 1e3 * float(np.mean(times))

@@ -35,7 +35,8 @@ enum { TOKP_OBJ_BODY = 1, TOKP_OBJ_JOINT = 3, TOKP_OBJ_GEOM = 5, TOKP_OBJ_SITE =
 
 /* task kinds: which MT::Residuals override runs on the device
  * (src/ModelTranslator/Acrobot.cpp:26-55, Walker.cpp:59-90) */
-enum { TOKP_TASK_ACROBOT = 0, TOKP_TASK_WALKER = 1, TOKP_TASK_REACHING = 2 /* pandaReaching, src/ModelTranslator/Reaching.cpp:28-60 */ };
+enum { TOKP_TASK_ACROBOT = 0, TOKP_TASK_WALKER = 1, TOKP_TASK_REACHING = 2 /* pandaReaching, src/ModelTranslator/Reaching.cpp:28-60 */,
+       TOKP_TASK_BOXSWEEP = 3 /* BoxSweep, src/ModelTranslator/BoxSweep.cpp:101-139 */ };
 
 /* key-point methods (include/KeyPointGenerator.h:34-43) */
 enum {
@@ -71,6 +72,13 @@ typedef struct tokp_task_desc {
   const double* jerk_thresholds;        /* [n]                                                        */
   const double* velchange_thresholds;   /* [n]                                                        */
   double iterative_error_threshold;
+  /* Residuals whose targets are vectors (BoxSweep: goal_pos (x, y), goal_vel (x, y), reach (d)) and residuals that
+   * read body poses.  num_target = 0 means num_resid; resid_target then holds num_target scalars, the residuals'
+   * target vectors concatenated (residual_list[i].target[j], include/StdInclude.h:82-88).  aux[num_aux] = model
+   * ids the residual needs: BoxSweep {goal body id, franka_gripper body id}. */
+  int num_target;
+  int num_aux;
+  const int* aux;
 } tokp_task_desc;
 
 const char* tokp_last_error(void);

@@ -33,7 +33,8 @@ class TaskDesc(C.Structure):
                 ("resid_weight_terminal", C.POINTER(C.c_double)),
                 ("kp_method", C.c_int), ("min_N", C.c_int), ("max_N", C.c_int),
                 ("jerk_thresholds", C.POINTER(C.c_double)), ("velchange_thresholds", C.POINTER(C.c_double)),
-                ("iterative_error_threshold", C.c_double)]
+                ("iterative_error_threshold", C.c_double),
+                ("num_target", C.c_int), ("num_aux", C.c_int), ("aux", C.POINTER(C.c_int))]
 
 
 _dp = C.POINTER(C.c_double)
@@ -112,7 +113,7 @@ class Task:
     """Owns the numpy buffers behind a TaskDesc."""
 
     def __init__(self, kind, qpos_adr, dof_adr, ctrl_adr, target, weight, weight_terminal, kp_method, min_N, max_N,
-                 jerk_thr, vel_thr, iter_thr):
+                 jerk_thr, vel_thr, iter_thr, aux=None):
         self.qpos_adr = np.ascontiguousarray(qpos_adr, dtype=np.int32)
         self.dof_adr = np.ascontiguousarray(dof_adr, dtype=np.int32)
         self.ctrl_adr = np.ascontiguousarray(ctrl_adr, dtype=np.int32)
@@ -122,7 +123,8 @@ class Task:
         self.jerk_thr = np.ascontiguousarray(jerk_thr, dtype=np.float64)
         self.vel_thr = np.ascontiguousarray(vel_thr, dtype=np.float64)
         self.kind, self.kp_method, self.min_N, self.max_N, self.iter_thr = kind, kp_method, min_N, max_N, iter_thr
-        self.n, self.m, self.nr = len(self.qpos_adr), len(self.ctrl_adr), len(self.target)
+        self.aux = np.ascontiguousarray([] if aux is None else aux, dtype=np.int32)
+        self.n, self.m, self.nr = len(self.qpos_adr), len(self.ctrl_adr), len(self.weight)
 
     def desc(self):
         d = TaskDesc()
@@ -133,6 +135,9 @@ class Task:
         d.kp_method, d.min_N, d.max_N = self.kp_method, self.min_N, self.max_N
         d.jerk_thresholds, d.velchange_thresholds = _d(self.jerk_thr), _d(self.vel_thr)
         d.iterative_error_threshold = self.iter_thr
+        d.num_target = len(self.target) if len(self.target) != self.nr else 0
+        d.num_aux = len(self.aux)
+        d.aux = _i(self.aux) if len(self.aux) else None
         return d
 
 

@@ -14,7 +14,7 @@ def oracle_task(tc, kp_method=None, min_N=None, max_N=None, target=None):
                        tc.target if target is None else target, tc.weight, tc.weight_terminal,
                        tc.kp_method if kp_method is None else kp_method,
                        tc.min_N if min_N is None else min_N, tc.max_N if max_N is None else max_N,
-                       tc.jerk_thr, tc.vel_thr, tc.iter_thr)
+                       tc.jerk_thr, tc.vel_thr, tc.iter_thr, aux=tc.aux)
 
 
 def random_controls(tc, T, seed, scale=0.3):

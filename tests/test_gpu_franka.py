@@ -116,3 +116,93 @@ def test_reaching_gravcomp_init_controls(built):
             assert np.abs(U_dev[b, t] - ref).max() <= 1e-9 * max(1.0, np.abs(ref).max()), (b, t)
     # holding the arm: joint velocities stay small under gravity compensation
     assert np.abs(U_dev).max() > 1.0
+
+
+# ---- box_sweep (BASELINE configs[2]): boxSweep.xml nq 23 / nv 21, state = 7 arm joints + goal box x, y, z; contacts:
+# box-plane (condim 1), mesh-box through the convex collider, finger pads, the display_goal sliver on the floor
+
+def test_box_sweep_step_worlds_match_oracle(built):
+    tc = make("box_sweep")
+    m = tc.model
+    om = oracle_model(tc)
+    rng = np.random.default_rng(8)
+    count, nsteps = 12, 12
+    snaps = []
+    for i in range(count):
+        start, _ = tc.load_trial(i)
+        r = np.random.default_rng(500 + i)
+        start[:7] += r.uniform(-0.05, 0.05, 7)
+        start[9] = 0.081 + 0.05 * (i % 3)   # box resting on / dropping onto the floor
+        snaps.append(tc.start_snapshot(start_pos=start, qvel=0.1 * r.standard_normal(tc.n)))
+    snaps = np.stack(snaps)
+    lim = m.real("actuator_ctrlrange").reshape(-1, 2)[:, 1]
+    snaps[:, m.S - m.nu:] = rng.uniform(-0.3, 0.3, (count, m.nu)) * lim
+    out = np.zeros_like(snaps)
+    st = np.zeros(count, dtype=np.int32)
+    capi.check(capi.lib().tokp_step_worlds(m.h, capi._d(snaps), capi._d(out), count, nsteps, -1, 0.0, capi._i(st)))
+    assert not st.any(), st
+    d = oracle.Data(om)
+    worst, ncon = 0.0, 0
+    for i in range(count):
+        d.load(snaps[i])
+        for _ in range(nsteps):
+            d.step()
+        assert d.get("warning")[0] == 0
+        ncon = max(ncon, int(d.get("ncon")[0]))
+        ref = d.save()
+        worst = max(worst, np.abs(ref - out[i]).max() / max(1.0, np.abs(ref).max()))
+    assert ncon >= 9   # box on the floor (4) + display_goal (4) + finger pads
+    # contact-rich: converged Newton on both sides; summation order differs
+    assert worst < 1e-8, worst
+
+
+def test_box_sweep_rollout_keypoints_jacobians(built):
+    tc = make("box_sweep", kp_method=capi.KP_SET_INTERVAL, min_N=4)
+    T = 24
+    om = oracle_model(tc)
+    start, target = tc.load_trial(1)
+    start[9] = 0.0805
+    ot = oracle_task(tc, target=target)
+    snap0 = tc.start_snapshot(start_pos=start)
+    U = random_controls(tc, T, 6, scale=0.1)
+    ref = oracle.ILQR(om, ot, T, threads=4)
+    c_ref = ref.rollout(snap0, U)
+    ref.generate_keypoints()
+    ref.dynamics_derivs()
+    tr = capi.Traj(tc, T, 1)
+    tr.set_targets(0, target)
+    c_dev = tr.rollout(snap0, U)[0]
+    assert abs(c_dev - c_ref) <= 1e-8 * max(1.0, abs(c_ref)), (c_dev, c_ref)
+    X_ref, X_dev = ref.get("X_old"), tr.get(0, "X_old")
+    assert np.abs(X_ref - X_dev).max() / max(1.0, np.abs(X_ref).max()) < 1e-8
+    assert np.allclose(ref.get("resid"), tr.get(0, "resid"), rtol=0, atol=1e-8)   # incl. the gripper-to-box distance
+    rows, pct = tr.keypoints()
+    assert rows[0] == ref.keypoints()
+    tr.dynamics_derivs()
+    nx = tr.nx
+    A_ref, B_ref = ref.get("A").reshape(T, nx, nx), ref.get("B").reshape(T, tr.m, nx)
+    A_dev, B_dev = tr.get(0, "A").reshape(T, nx, nx), tr.get(0, "B").reshape(T, tr.m, nx)
+    kp_rows = [t for t in range(T) if rows[0][t]]
+    errs = [max(rel_fro(A_dev[t], A_ref[t]), rel_fro(B_dev[t], B_ref[t])) for t in kp_rows]
+    assert max(errs) < AB_RTOL, errs
+
+
+def test_box_sweep_optimise_cost(built):
+    tc = make("box_sweep", kp_method=capi.KP_SET_INTERVAL, min_N=5)
+    T = 40
+    om = oracle_model(tc)
+    start, target = tc.load_trial(2)
+    ot = oracle_task(tc, target=target)
+    snap0 = tc.start_snapshot(start_pos=start)
+    U = np.zeros((T, tc.m))
+    ref = oracle.ILQR(om, ot, T, threads=4)
+    ref.set_lambda(0.1)
+    ref.optimise(snap0, U, 2, 1)
+    sc = ref.scalars()
+    tr = capi.Traj(tc, T, 2)
+    for b in range(2):
+        tr.set_targets(b, target)
+    U_dev, stats = tr.optimise(snap0, U, 2, 1, lam=0.1)
+    for b in range(2):
+        assert abs(stats[b, 0] - sc["initial_cost"]) <= 1e-8 * abs(sc["initial_cost"])
+        assert abs(stats[b, 1] - sc["new_cost"]) <= 0.01 * abs(sc["new_cost"]), (stats[b], sc)  # final cost within 1 %

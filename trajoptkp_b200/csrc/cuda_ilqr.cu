@@ -26,9 +26,9 @@ __global__ void k_resid_derivs(DM dm, TaskDev tk_, const double* __restrict__ sn
   for (int i = 0; i < nq; i++) q[i] = s[1 + i];
   for (int i = 0; i < nv; i++) v[i] = s[1 + nq + i];
   for (int i = 0; i < nu; i++) u[i] = s[1 + nq + 3 * nv + i];
-  const double* tgt = target + (size_t)b * nr;
+  const double* tgt = target + (size_t)b * tk_.ntg;
   double r0[kMaxResid], ri[kMaxResid], rd[kMaxResid];
-  task_residuals(tk_, q, v, u, tgt, r0);
+  task_residuals(dm, tk_, q, v, u, tgt, r0);
   double* rxo = rx + (size_t)gid * nr * nx;
   double* ruo = ru + (size_t)gid * nr * m;
   for (int i = 0; i < m; i++) {
@@ -36,8 +36,8 @@ __global__ void k_resid_derivs(DM dm, TaskDev tk_, const double* __restrict__ sn
     double u0 = u[ua];
     bool fwd = !(u0 + eps > tk_.ctrl_limits[2 * i + 1]);
     bool back = (central || !fwd) && !(u0 - eps < tk_.ctrl_limits[2 * i]);
-    if (fwd) { u[ua] = u0 + eps; task_residuals(tk_, q, v, u, tgt, ri); }
-    if (back) { u[ua] = u0 - eps; task_residuals(tk_, q, v, u, tgt, rd); }
+    if (fwd) { u[ua] = u0 + eps; task_residuals(dm, tk_, q, v, u, tgt, ri); }
+    if (back) { u[ua] = u0 - eps; task_residuals(dm, tk_, q, v, u, tgt, rd); }
     u[ua] = u0;
     for (int j = 0; j < nr; j++) {
       if (fwd && back) ruo[i * nr + j] = (ri[j] - rd[j]) / (2 * eps);
@@ -49,8 +49,8 @@ __global__ void k_resid_derivs(DM dm, TaskDev tk_, const double* __restrict__ sn
     int va = tk_.dof_adr[i];
     double v0 = v[va];
     v[va] = v0 + eps;
-    task_residuals(tk_, q, v, u, tgt, ri);
-    if (central) { v[va] = v0 - eps; task_residuals(tk_, q, v, u, tgt, rd); }
+    task_residuals(dm, tk_, q, v, u, tgt, ri);
+    if (central) { v[va] = v0 - eps; task_residuals(dm, tk_, q, v, u, tgt, rd); }
     v[va] = v0;
     for (int j = 0; j < nr; j++) rxo[(i + n) * nr + j] = central ? (ri[j] - rd[j]) / (2 * eps) : (ri[j] - r0[j]) / eps;
   }
@@ -59,8 +59,8 @@ __global__ void k_resid_derivs(DM dm, TaskDev tk_, const double* __restrict__ sn
     int qa = tk_.qpos_adr[i];
     double q0 = q[qa];
     q[qa] = q0 + eps * 1.0;
-    task_residuals(tk_, q, v, u, tgt, ri);
-    if (central) { q[qa] = q0 + (-eps) * 1.0; task_residuals(tk_, q, v, u, tgt, rd); }
+    task_residuals(dm, tk_, q, v, u, tgt, ri);
+    if (central) { q[qa] = q0 + (-eps) * 1.0; task_residuals(dm, tk_, q, v, u, tgt, rd); }
     q[qa] = q0;
     for (int j = 0; j < nr; j++) rxo[i * nr + j] = central ? (ri[j] - rd[j]) / (2 * eps) : (ri[j] - r0[j]) / eps;
   }
@@ -419,7 +419,7 @@ __global__ void k_accept(DM dm, TaskDev tk_, double* __restrict__ snap, const do
     // saved[t] <- rollout_data[t] (time, qpos, qvel, qacc, warmstart); its ctrl is still the old one here
     for (int i = 0; i < so; i++) s[i] = c[i];
     double r[kMaxResid];
-    task_residuals(tk_, s + 1, s + 1 + nq, s + so, target + (size_t)b * nr, r);
+    task_residuals(dm, tk_, s + 1, s + 1 + nq, s + so, target + (size_t)b * tk_.ntg, r);
     for (int i = 0; i < nr; i++) resid[((size_t)b * (T + 1) + t) * nr + i] = r[i];
     double* Xo = X + ((size_t)b * (T + 1) + t) * nx;
     for (int i = 0; i < n; i++) { Xo[i] = s[1 + tk_.qpos_adr[i]]; Xo[n + i] = s[1 + nq + tk_.dof_adr[i]]; }

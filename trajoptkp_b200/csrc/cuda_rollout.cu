@@ -67,7 +67,7 @@ __global__ void __launch_bounds__(G == 16 ? 384 : 128, G == 16 ? 1 : 2) k_rollou
   g.sync();
   double* Xb = a.X + (size_t)b * (T + 1) * nx;
   double* Ub = a.U + (size_t)b * T * m;
-  const double* tgt = a.target + (size_t)b * nr;
+  const double* tgt = a.target + (size_t)b * tk_.ntg;
   double cost = 0.0;
   int st = 0;
   double alpha = a.mode ? a.alphas[ai] : 0.0;
@@ -101,7 +101,7 @@ __global__ void __launch_bounds__(G == 16 ? 384 : 128, G == 16 ? 1 : 2) k_rollou
       // cost of (x_t, u_t) before the step (iLQR.cpp:896-912)
       if (g.gl == 0) {
         double r[kMaxResid];
-        task_residuals(tk_, w.qpos, w.qvel, w.ctrl, tgt, r);
+        task_residuals(dm, tk_, w.qpos, w.qvel, w.ctrl, tgt, r);
         cost = __dadd_rn(cost, task_cost(tk_, r, t == T - 1));
       }
     }
@@ -110,7 +110,7 @@ __global__ void __launch_bounds__(G == 16 ? 384 : 128, G == 16 ? 1 : 2) k_rollou
       // residuals / cost after the step, X_old, U_old, saved[t+1] (iLQR.cpp:222-246)
       if (g.gl == 0) {
         double r[kMaxResid];
-        task_residuals(tk_, w.qpos, w.qvel, w.ctrl, tgt, r);
+        task_residuals(dm, tk_, w.qpos, w.qvel, w.ctrl, tgt, r);
         double* rb = a.resid + ((size_t)b * (T + 1) + t) * nr;
         for (int i = 0; i < nr; i++) rb[i] = r[i];
         cost = __dadd_rn(cost, task_cost(tk_, r, t == T - 1));

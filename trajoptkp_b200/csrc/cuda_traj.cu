@@ -59,7 +59,8 @@ extern "C" int tokp_traj_create(const tokp_model* m, const tokp_task_desc* td, i
   size_t o_luu = p.take((size_t)B * (T + 1) * mm * mm, 8);
   size_t o_K = p.take((size_t)B * T * mm * nx, 8);
   size_t o_k = p.take((size_t)B * T * mm, 8);
-  size_t o_target = p.take((size_t)B * nr, 8);
+  const int ntg = td->num_target > 0 ? td->num_target : nr;
+  size_t o_target = p.take((size_t)B * ntg, 8);
   size_t o_cand = p.take((size_t)B * NA * (T + 1) * tr->SD, 8);
   size_t o_candcost = p.take((size_t)B * NA, 8);
   size_t o_fd = p.take((size_t)B * T * tr->W * (dm.nq + dm.nv), 8);
@@ -115,14 +116,15 @@ extern "C" int tokp_traj_create(const tokp_model* m, const tokp_task_desc* td, i
   cudaMemcpy(tr->task_ints, ti.data(), ti.size() * 4, cudaMemcpyHostToDevice);
   cudaMemcpy(tr->task_reals, trl.data(), trl.size() * 8, cudaMemcpyHostToDevice);
   TaskDev& t = tr->task;
-  t.kind = td->kind; t.n = n; t.m = mm; t.nr = nr;
+  t.kind = td->kind; t.n = n; t.m = mm; t.nr = nr; t.ntg = ntg;
+  for (int i = 0; i < 4; i++) t.aux[i] = (td->aux && i < td->num_aux) ? td->aux[i] : -1;
   t.kp_method = td->kp_method; t.min_N = td->min_N; t.max_N = td->max_N; t.iter_thr = td->iterative_error_threshold;
   t.qpos_adr = tr->task_ints; t.dof_adr = tr->task_ints + n; t.ctrl_adr = tr->task_ints + 2 * n;
   t.weight = tr->task_reals; t.weight_terminal = tr->task_reals + nr; t.jerk_thr = tr->task_reals + 2 * nr;
   t.vel_thr = tr->task_reals + 2 * nr + n; t.ctrl_limits = tr->task_reals + 2 * nr + 2 * n;
   // every trajectory starts with the YAML targets
-  std::vector<double> tg((size_t)B * nr);
-  for (int b = 0; b < B; b++) std::memcpy(&tg[(size_t)b * nr], td->resid_target, nr * 8);
+  std::vector<double> tg((size_t)B * ntg);
+  for (int b = 0; b < B; b++) std::memcpy(&tg[(size_t)b * ntg], td->resid_target, ntg * 8);
   cudaMemcpy(tr->target, tg.data(), tg.size() * 8, cudaMemcpyHostToDevice);
   cudaStreamCreate(&tr->stream);
   cudaEventCreate(&tr->ev0);
@@ -148,7 +150,7 @@ extern "C" void tokp_traj_destroy(tokp_traj* tr) {
 
 extern "C" int tokp_traj_set_targets(tokp_traj* tr, int b, const double* resid_target) {
   if (!tr || !resid_target || b < 0 || b >= tr->B) { set_error("tokp_traj_set_targets: bad argument"); return TOKP_ERR_ARG; }
-  TOKP_CUDA(cudaMemcpyAsync(tr->target + (size_t)b * tr->nr, resid_target, tr->nr * 8, cudaMemcpyHostToDevice, tr->stream));
+  TOKP_CUDA(cudaMemcpyAsync(tr->target + (size_t)b * tr->task.ntg, resid_target, tr->task.ntg * 8, cudaMemcpyHostToDevice, tr->stream));
   TOKP_CUDA(cudaStreamSynchronize(tr->stream));
   return TOKP_OK;
 }
@@ -217,7 +219,7 @@ bool named_array(tokp_traj* tr, const std::string& nm, double** p, size_t* cnt) 
   F("A", A, (size_t)T * nx * nx) F("B", Bm, (size_t)T * nx * m)
   F("r_x", rx, (size_t)(T + 1) * nr * nx) F("r_u", ru, (size_t)(T + 1) * nr * m)
   F("l_x", lx, (T + 1) * nx) F("l_xx", lxx, (size_t)(T + 1) * nx * nx) F("l_u", lu, (T + 1) * m) F("l_uu", luu, (T + 1) * m * m)
-  F("K", K, (size_t)T * m * nx) F("k", k, T * m) F("target", target, nr)
+  F("K", K, (size_t)T * m * nx) F("k", k, T * m) F("target", target, tr->task.ntg)
   F("snap", snap, (size_t)(T + 1) * tr->SD) F("cand", cand, (size_t)tokp_traj::NA * (T + 1) * tr->SD)
   F("fd_out", fd_out, (size_t)T * tr->W * (tr->dm.nq + tr->dm.nv))
 #undef F

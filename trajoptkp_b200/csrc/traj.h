@@ -60,6 +60,8 @@ inline int dsnap_size(const DM& dm) { return 1 + dm.nq + 3 * dm.nv + dm.nu; }
 
 struct TaskDev {
   int kind, n, m, nr;
+  int ntg;      // target scalars per trajectory (nr unless the task has vector targets)
+  int aux[4];   // model ids the residual reads (BoxSweep: goal body, gripper body)
   int kp_method, min_N, max_N;
   double iter_thr;
   const int *qpos_adr, *dof_adr, *ctrl_adr;           // device

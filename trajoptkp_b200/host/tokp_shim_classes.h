@@ -46,6 +46,7 @@ class ModelTranslator {
     d.jerk_thresholds = current_kp.jerk_thresholds.data();
     d.velchange_thresholds = current_kp.velocity_change_thresholds.data();
     d.iterative_error_threshold = current_kp.iterative_error_threshold;
+    d.num_target = 0; d.num_aux = 0; d.aux = nullptr;
     return d;
   }
   // ReturnStateVector (ModelTranslator.cpp:882-897): [pos(n); vel(n)]

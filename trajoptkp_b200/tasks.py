@@ -16,6 +16,7 @@ TASKS = {
     "acrobot": ("tasks/acrobot.yaml", "models/acrobot.xml", capi.TASK_ACROBOT),
     "walker_run": ("tasks/walker_run.yaml", "models/walker_plane.xml", capi.TASK_WALKER),
     "reaching": ("tasks/reaching.yaml", "models/franka/reaching_scene.xml", capi.TASK_REACHING),
+    "box_sweep": ("tasks/box_sweep.yaml", "models/franka/boxSweep.xml", capi.TASK_BOXSWEEP),
 }
 
 
@@ -50,12 +51,46 @@ class TaskConfig:
                 if aid < 0:
                     raise KeyError("actuator %s not in model" % an)
                 ctrl_adr.append(aid)
-        if cfg.get("bodies"):
-            raise NotImplementedError("rigid-body state elements are outside round-1 scope")
+        # rigid bodies (stateVectorList::Update, include/StdInclude.h:119-188; ComputeStateDofAdrIndices,
+        # ModelTranslator.cpp:1548-1610): per body the active linear x, y, z then the active angular DoFs of its free
+        # joint.  Linear elements read qpos directly; angular ones would need the axis-angle read-out (quat2Axis) and
+        # are rejected until a shipped task in scope activates them.
+        self.num_robot_dofs = len(qpos_adr)
+        self.body_names, self.body_start = [], []
+        body_jntadr = m.int("body_jntadr")
+        for bname, body in (cfg.get("bodies") or {}).items():
+            bid = m.name2id(capi.OBJ_BODY, bname)
+            if bid < 0:
+                raise KeyError("body %s not in model" % bname)
+            if any(body["activeAngularDOF"]):
+                raise NotImplementedError("angular rigid-body state elements are not supported yet")
+            jid = int(body_jntadr[bid])
+            self.body_names.append(bname)
+            self.body_start.append((int(jnt_qposadr[jid]), list(map(float, body["startLinearPos"])),
+                                    list(map(float, body["startAngularPos"]))))
+            for k in range(3):
+                if body["activeLinearDOF"][k]:
+                    qpos_adr.append(int(jnt_qposadr[jid]) + k)
+                    dof_adr.append(int(jnt_dofadr[jid]) + k)
+                    jerk.append(float(body["linearJerkThreshold"][k]))
+                    vel.append(float(body["linearMagVelThreshold"][k]))
+                    start.append(float(body["startLinearPos"][k]))
+        self.aux = np.zeros(0, dtype=np.int32)
+        if kind == capi.TASK_BOXSWEEP:
+            self.aux = np.array([m.name2id(capi.OBJ_BODY, "goal"), m.name2id(capi.OBJ_BODY, "franka_gripper")],
+                                dtype=np.int32)
+            if (self.aux < 0).any():
+                raise KeyError("box_sweep needs the bodies 'goal' and 'franka_gripper'")
         target, weight, weight_t = [], [], []
         self.resid_target_sizes = []
         for rn, r in cfg["residuals"].items():
             dim = int(r.get("resid_dimension", 1))
+            if kind == capi.TASK_BOXSWEEP:  # vector targets, concatenated (tokp_task_desc.num_target)
+                target += [float(x) for x in r["target"]]
+                weight.append(float(r["weight"]))
+                weight_t.append(float(r["weight_terminal"]))
+                self.resid_target_sizes.append(len(r["target"]))
+                continue
             for k in range(dim):  # FileHandler.cpp:276-287 replicates the entry resid_dimension times
                 # pandaReaching::Residuals reads residual_list[0].target[i] for its i-th residual (Reaching.cpp:46)
                 first_group = kind == capi.TASK_REACHING and len(target) < dim
@@ -72,7 +107,7 @@ class TaskConfig:
         self.jerk_thr = np.array(jerk)
         self.vel_thr = np.array(vel)
         self.start_pos = np.array(start)
-        self.n, self.m, self.nr = len(qpos_adr), len(ctrl_adr), len(target)
+        self.n, self.m, self.nr = len(qpos_adr), len(ctrl_adr), len(weight)
         self.kp_method = capi.KP_NAMES[cfg.get("keypointMethod", "set_interval")] if kp_method is None else kp_method
         self.min_N = int(cfg.get("minN", 1)) if min_N is None else min_N
         self.max_N = int(cfg.get("maxN", 10)) if max_N is None else max_N
@@ -88,6 +123,9 @@ class TaskConfig:
         d.kp_method, d.min_N, d.max_N = self.kp_method, self.min_N, self.max_N
         d.jerk_thresholds, d.velchange_thresholds = capi._d(self.jerk_thr), capi._d(self.vel_thr)
         d.iterative_error_threshold = self.iter_thr
+        d.num_target = len(self.target) if len(self.target) != self.nr else 0
+        d.num_aux = len(self.aux)
+        d.aux = capi._i(self.aux) if len(self.aux) else None
         return d
 
     # ---- TestTasks fixtures --------------------------------------------------------------------
@@ -100,8 +138,17 @@ class TaskConfig:
         path = os.path.join(ASSETS, "test_tasks", self.name + ".csv")
         rows = [l.strip() for l in open(path) if l.strip() and not l.startswith("#")]
         vals = [float(v) for v in rows[i].split(",")]
-        start = np.array(vals[:self.n])
-        rest = vals[self.n:]
+        # the file lists every robot joint, then x, y, z, roll, pitch, yaw of every body (FileHandler.cpp:536-553)
+        nfile = self.num_robot_dofs + 6 * len(self.body_names)
+        start = np.array(vals[:self.num_robot_dofs])
+        for k in range(len(self.body_names)):
+            o = self.num_robot_dofs + 6 * k
+            if any(abs(a) > 0 for a in vals[o + 3:o + 6]):
+                raise NotImplementedError("rotated rigid-body start poses are not supported yet")
+            start = np.concatenate([start, vals[o:o + 3]])
+        rest = vals[nfile:]
+        if self.kind == capi.TASK_BOXSWEEP:
+            return start, np.array(rest[:len(self.target)])
         targets, p = [], 0
         for k, sz in enumerate(self.resid_target_sizes):
             if self.kind == capi.TASK_REACHING:  # residual_list[0].target[k] for the position residuals, 0 after

@@ -45,13 +45,20 @@ def workload(args, rank, world):
     tc = tasks.TaskConfig(args.task, kp_method=KP_METHOD[args.kp])
     B, T = args.batch, args.horizon
     snaps = np.zeros((B, tc.model.S))
-    targets = np.zeros((B, tc.nr))
+    targets = np.zeros((B, len(tc.target)))
     for j in range(B):
         gj = rank * B + j                      # global replan index: weak scaling, fixed work per GPU
         scene, p = gj % 100, gj // 100
         start, tg = tc.load_trial(scene)
         rng = np.random.default_rng(1000 * 7 + 10 * scene + p)
-        q = start + rng.uniform(-0.02, 0.02, tc.n)
+        # joints +-0.02 rad, body x, y +-0.005 m (z untouched), velocities N(0, 0.01)
+        nj = getattr(tc, "num_robot_dofs", tc.n)
+        dq = rng.uniform(-0.02, 0.02, tc.n)
+        if tc.n > nj:
+            dq[nj:] = 0.0
+            for k in range(nj, tc.n, 3):
+                dq[k:k + 2] = rng.uniform(-0.005, 0.005, 2)
+        q = start + dq
         v = 0.01 * rng.standard_normal(tc.n)
         snaps[j] = tc.start_snapshot(start_pos=q, qvel=v)
         targets[j] = tg
@@ -94,7 +101,7 @@ def cpu_arm(args, tc, snaps, targets, U, steps, warmup, want_flops=True):
     om = oracle.Model(tc.model.blob())
     T = args.horizon
     n_rep = args.cpu_replans
-    if tc.kind == 2 and not np.any(U):
+    if tc.kind in (2, 3) and not np.any(U):
         # reaching: gravity-compensation initial controls (Reaching.cpp:269-296), restated with the oracle, untimed
         U = np.array(U, copy=True)
         S, nu = tc.model.S, tc.model.nu
@@ -201,11 +208,13 @@ def main():
     tr = capi.Traj(tc, T, B)
     for b in range(B):
         tr.set_targets(b, targets[b])
-    if tc.kind == capi.TASK_REACHING:
+    if tc.kind in (capi.TASK_REACHING, capi.TASK_BOXSWEEP):
         # pandaReaching::CreateInitOptimisationControls (Reaching.cpp:269-296): gravity-compensation rollout, on the
         # device, outside the timed region (the reference also generates it once per trial before Optimise)
         U[...] = tr.init_controls_gravcomp(snaps)[0]
-        config["initial_controls"] = "gravity compensation (tokp_init_controls_gravcomp)"
+        config["initial_controls"] = "gravity compensation (tokp_init_controls_gravcomp)" + (
+            "; the reference's Jacobian end-effector path follower (PushBaseClass.cpp:8-248, SURVEY N2) is not built yet"
+            if tc.kind == capi.TASK_BOXSWEEP else "")
     launches0 = capi.lib().tokp_launch_count()
 
     def barrier():

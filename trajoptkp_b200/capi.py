@@ -195,7 +195,7 @@ class Traj:
 
     def set_targets(self, b, targets):
         t = np.ascontiguousarray(targets, dtype=np.float64)
-        assert t.size == self.nr
+        assert t.size == (self._desc.num_target or self.nr)
         check(lib().tokp_traj_set_targets(self.h, b, _d(t)))
 
     def set_keypoint_method(self, method, min_N, max_N, jerk_thr=None, vel_thr=None, iter_thr=0.0):

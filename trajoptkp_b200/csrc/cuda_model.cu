@@ -130,6 +130,14 @@ int ensure_device_model(const tokp_model* mc, const DM** out) {
   for (auto& p : patches) *p.dst = (const uint8_t*)d->arena + p.off;
   dm.nq = h.nq(); dm.nv = h.nv(); dm.nu = h.nu(); dm.nbody = h.nbody(); dm.njnt = h.njnt(); dm.ngeom = h.ngeom();
   dm.npair = h.npair(); dm.maxcontact = h.maxcontact() > 0 ? h.maxcontact() : 1; dm.maxefc = h.maxefc() > 0 ? h.maxefc() : 1;
+  // The compiler's bound assumes every filtered pair in contact at once (Franka scenes: 345-949 rows); the redo pass
+  // sizes its shared-memory workspace by this number, so it is capped like MuJoCo's njmax (TOKP_EFC_MAX, default
+  // 192 rows).  A world that still overflows keeps ST_OVERFLOW in its status / gets a NaN rollout cost.
+  {
+    int cap = 192;
+    if (const char* e = getenv("TOKP_EFC_MAX")) { int v = atoi(e); if (v > 0) cap = v; }
+    if (dm.maxefc > cap) dm.maxefc = cap;
+  }
   dm.treedepth = h.dims[10];
   dm.iterations = h.opt_int[0]; dm.ls_iterations = h.opt_int[1];
   dm.timestep = h.opt_real[0];

@@ -25,7 +25,7 @@ struct RollArgs {
   double tolerance;
   TaskDev task;
   int* flags;          // [nworlds] overflow flags written by pass 0, consumed by pass 1
-  int ecap, pass;
+  int ecap, pass, last;  // last: no further pass re-runs overflowed worlds
   int spread;          // 1: one world per warp (first group only) - latency layout for small batches
   int bsync;           // Grp::bsync level: the block walks the stages of every step together
 };
@@ -132,8 +132,9 @@ __global__ void __launch_bounds__(G == 16 ? 384 : 128, G == 16 ? 1 : 2) k_rollou
     }
     g.sync();
   }
-  if (g.gl == 0) a.cost[a.mode == 0 ? b : b * a.NA + ai] = cost;
   int ovf = g.any(st & tk::ST_OVERFLOW);
+  if (a.last && ovf) cost = __longlong_as_double(0x7ff8000000000000ll);  // constraint rows beyond the capacity: loud
+  if (g.gl == 0) a.cost[a.mode == 0 ? b : b * a.NA + ai] = cost;
   if (g.gl == 0) a.flags[widx] = (a.pass == 0 && ovf) ? 1 : 0;
 }
 
@@ -157,7 +158,7 @@ int launch_rollout(tokp_traj* tr, int mode, const double* d_Uin, const double* d
     LaunchPlan lp;
     int rc = plan_launch(dm, G, pass, &lp);
     if (rc) return rc;
-    a.ecap = lp.ecap; a.pass = pass;
+    a.ecap = lp.ecap; a.pass = pass; a.last = (pass == 1 || !needs_redo_pass(dm)) ? 1 : 0;
     int warps = lp.warps;
     int blocks = (nworlds + lp.worlds_per_block - 1) / lp.worlds_per_block;
     if (a.spread) {
@@ -166,6 +167,7 @@ int launch_rollout(tokp_traj* tr, int mode, const double* d_Uin, const double* d
       warps = (nworlds + 147) / 148;
       if (warps > 4) warps = 4;
       if (const char* e = getenv("TOKP_SPREAD_WARPS")) { int v = atoi(e); if (v >= 1 && v <= 4) warps = v; }
+      while (warps > 1 && (size_t)lp.wsd * 8 * warps > 226 * 1024) warps--;  // large models: fewer worlds per block
       blocks = (nworlds + warps - 1) / warps;
       lp.smem = (size_t)lp.wsd * 8 * warps;
     }

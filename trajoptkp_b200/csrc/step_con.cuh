@@ -137,7 +137,9 @@ TK_DEV void collision(const DM& m, WS& w, const Grp<G, NV>& g, int& status) {
       // instantiation carries this code: the specialised walker / acrobot kernels have no mesh geoms
       double d[3] = {pos2[0] - pos1[0], pos2[1] - pos1[1], pos2[2] - pos1[2]};
       double bound = m.geom_rbound[g1] + m.geom_rbound[g2] + margin;
-      if (dot3(d, d) <= bound * bound)
+      bool boxed = (t1 == GEOM_MESH || t1 == GEOM_BOX) && (t2 == GEOM_MESH || t2 == GEOM_BOX);
+      if (dot3(d, d) <= bound * bound &&
+          !(boxed && obb_disjoint(pos1, mat1, &m.geom_size[3 * g1], pos2, mat2, &m.geom_size[3 * g2], margin)))
         n = convex_convex(m, margin, g1, pos1, mat1, g2, pos2, mat2, &w.con_dist[slot], &w.con_pos[3 * slot], &w.con_frame[6 * slot]);
     } else {
       status |= ST_UNSUPPORTED;

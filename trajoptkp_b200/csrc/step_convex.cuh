@@ -231,6 +231,40 @@ TK_DEV int mpr_penetration(const DM& m, const CvxObj& a, const CvxObj& b, double
   }
 }
 
+// Separating-axis test of the two geoms' oriented bounding boxes (half-extents h1 / h2 in the geom frames, inflated
+// by margin / 2 each; mesh geoms carry the box of their vertices in geom_size).  true = the boxes are disjoint, so
+// the convex shapes inside them are too and the narrow phase would return no contact: a cull that cannot change a
+// result (MuJoCo's mj_collideGeoms applies the same kind of box filter before the narrow phase).
+TK_DEV bool obb_disjoint(const double* pos1, const double* mat1, const double* h1, const double* pos2, const double* mat2,
+                         const double* h2, double margin) {
+  double a[3] = {h1[0] + 0.5 * margin, h1[1] + 0.5 * margin, h1[2] + 0.5 * margin};
+  double b[3] = {h2[0] + 0.5 * margin, h2[1] + 0.5 * margin, h2[2] + 0.5 * margin};
+  double R[9], AR[9], t[3];
+  double d[3] = {pos2[0] - pos1[0], pos2[1] - pos1[1], pos2[2] - pos1[2]};
+  for (int i = 0; i < 3; i++) {
+    t[i] = mat1[i] * d[0] + mat1[3 + i] * d[1] + mat1[6 + i] * d[2];
+    for (int j = 0; j < 3; j++) {
+      double r = mat1[i] * mat2[j] + mat1[3 + i] * mat2[3 + j] + mat1[6 + i] * mat2[6 + j];
+      R[3 * i + j] = r;
+      AR[3 * i + j] = fabs(r) + 1e-9;  // slack: near-parallel edges make the cross-product axes degenerate
+    }
+  }
+  for (int i = 0; i < 3; i++)
+    if (fabs(t[i]) > a[i] + b[0] * AR[3 * i] + b[1] * AR[3 * i + 1] + b[2] * AR[3 * i + 2]) return true;
+  for (int j = 0; j < 3; j++)
+    if (fabs(t[0] * R[j] + t[1] * R[3 + j] + t[2] * R[6 + j]) > a[0] * AR[j] + a[1] * AR[3 + j] + a[2] * AR[6 + j] + b[j]) return true;
+  for (int i = 0; i < 3; i++) {
+    int i1 = (i + 1) % 3, i2 = (i + 2) % 3;
+    for (int j = 0; j < 3; j++) {
+      int j1 = (j + 1) % 3, j2 = (j + 2) % 3;
+      double ra = a[i1] * AR[3 * i2 + j] + a[i2] * AR[3 * i1 + j];
+      double rb = b[j1] * AR[3 * i + j2] + b[j2] * AR[3 * i + j1];
+      if (fabs(t[i2] * R[3 * i1 + j] - t[i1] * R[3 * i2 + j]) > ra + rb) return true;
+    }
+  }
+  return false;
+}
+
 // mjc_Convex: writes dist, pos[3], frame[0:6] (tangent hint zero); returns the number of contacts (0 or 1)
 TK_DEV int convex_convex(const DM& m, double margin, int g1, const double* pos1, const double* mat1, int g2, const double* pos2,
                          const double* mat2, double* dist, double* pos, double* frame) {

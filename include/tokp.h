@@ -36,7 +36,10 @@ enum { TOKP_OBJ_BODY = 1, TOKP_OBJ_JOINT = 3, TOKP_OBJ_GEOM = 5, TOKP_OBJ_SITE =
 /* task kinds: which MT::Residuals override runs on the device
  * (src/ModelTranslator/Acrobot.cpp:26-55, Walker.cpp:59-90) */
 enum { TOKP_TASK_ACROBOT = 0, TOKP_TASK_WALKER = 1, TOKP_TASK_REACHING = 2 /* pandaReaching, src/ModelTranslator/Reaching.cpp:28-60 */,
-       TOKP_TASK_BOXSWEEP = 3 /* BoxSweep, src/ModelTranslator/BoxSweep.cpp:101-139 */ };
+       TOKP_TASK_BOXSWEEP = 3 /* BoxSweep, src/ModelTranslator/BoxSweep.cpp:101-139 */,
+       TOKP_TASK_PUSH = 4 /* TwoDPushing (no / light / heavy clutter), src/ModelTranslator/TwoDPushing.cpp:291-356;
+                             aux = {goal body, franka_gripper body}; targets = goal_pos (x, y), goal_vel (x, y), then
+                             per obstacle its start (x, y), then joint_5_velocity (1), reach (1) */ };
 
 /* key-point methods (include/KeyPointGenerator.h:34-43) */
 enum {

@@ -107,6 +107,8 @@ int plane_convex(const Model* m, Contact<R>* con, R margin, const R* pos1, const
 template <class R>
 int convex_convex(const Model* m, Contact<R>* con, R margin, int g1, const R* pos1, const R* mat1, int g2, const R* pos2,
                   const R* mat2);
+template <class R>
+int plane_cylinder(Contact<R>* con, R margin, const R* pos1, const R* mat1, const R* pos2, const R* mat2, const double* size2);
 inline bool is_convex_type(int t) {
   return t == GEOM_SPHERE || t == GEOM_CAPSULE || t == GEOM_CYLINDER || t == GEOM_BOX || t == GEOM_MESH;
 }
@@ -134,9 +136,12 @@ void collision(const Model* m, Data<R>* d) {
       if (t2 == GEOM_SPHERE) n = plane_sphere(tmp, margin, pos1, mat1, pos2, R(m->geom_size[3 * g2]));
       else if (t2 == GEOM_CAPSULE) n = plane_capsule(tmp, margin, pos1, mat1, pos2, mat2, &m->geom_size[3 * g2]);
       else if (t2 == GEOM_BOX) n = plane_box(tmp, margin, pos1, mat1, pos2, mat2, &m->geom_size[3 * g2]);
+      else if (t2 == GEOM_CYLINDER) n = plane_cylinder(tmp, margin, pos1, mat1, pos2, mat2, &m->geom_size[3 * g2]);
       else if (t2 == GEOM_MESH) n = plane_convex(m, tmp, margin, pos1, mat1, g2, pos2, mat2);
       else { d->warning |= 32; continue; }
-    } else if ((t1 == GEOM_MESH || t2 == GEOM_MESH) && is_convex_type(t1) && is_convex_type(t2)) {
+    } else if (is_convex_type(t1) && is_convex_type(t2) &&
+               (t1 == GEOM_MESH || t2 == GEOM_MESH || (t1 == GEOM_CYLINDER && t2 == GEOM_CYLINDER) ||
+                (t1 == GEOM_CYLINDER && t2 == GEOM_BOX) || (t1 == GEOM_BOX && t2 == GEOM_CYLINDER))) {
       // mj_collideGeoms: bounding-sphere filter, then the general convex collider (mjc_Convex)
       R dif[3] = {pos2[0] - pos1[0], pos2[1] - pos1[1], pos2[2] - pos1[2]};
       R bound = R(m->geom_rbound[g1]) + R(m->geom_rbound[g2]) + margin;

@@ -276,6 +276,56 @@ int convex_convex(const Model* m, Contact<R>* con, R margin, int g1, const R* po
   return 1;
 }
 
+// mjc_PlaneCylinder (engine_collision_primitive.c): nearest rim point of each cap, then two more points of the nearer
+// cap that make a triangle with the first; at most 4 contacts
+template <class R>
+int plane_cylinder(Contact<R>* con, R margin, const R* pos1, const R* mat1, const R* pos2, const R* mat2, const double* size2) {
+  using std::sqrt;
+  R normal[3] = {mat1[2], mat1[5], mat1[8]};
+  R axis[3] = {mat2[2], mat2[5], mat2[8]};
+  R prjaxis = dot3(normal, axis);
+  if (prjaxis > R(0.0)) { for (int k = 0; k < 3; k++) axis[k] = -axis[k]; prjaxis = -prjaxis; }
+  R vec[3] = {pos2[0] - pos1[0], pos2[1] - pos1[1], pos2[2] - pos1[2]};
+  R dist0 = dot3(vec, normal);
+  for (int k = 0; k < 3; k++) vec[k] = axis[k] * prjaxis - normal[k];
+  R len_sqr = dot3(vec, vec);
+  if (len_sqr >= R(kMinVal) * R(kMinVal)) {
+    R scl = R(size2[0]) / sqrt(len_sqr);
+    for (int k = 0; k < 3; k++) vec[k] *= scl;
+  } else {
+    vec[0] = mat2[0] * R(size2[0]); vec[1] = mat2[3] * R(size2[0]); vec[2] = mat2[6] * R(size2[0]);
+  }
+  R prjvec = dot3(vec, normal);
+  for (int k = 0; k < 3; k++) axis[k] *= R(size2[1]);
+  prjaxis *= R(size2[1]);
+  int cnt = 0;
+  auto put = [&](R d, double sa, double sv, const R* side, double ss) {
+    con[cnt].dist = d;
+    for (int k = 0; k < 3; k++) {
+      R p = pos2[k] + R(sv) * vec[k] + R(sa) * axis[k];
+      if (side) p = p + R(ss) * side[k];
+      con[cnt].pos[k] = p - normal[k] * d * R(0.5);
+      con[cnt].frame[k] = normal[k];
+    }
+    for (int k = 3; k < 9; k++) con[cnt].frame[k] = R(0.0);
+    cnt++;
+  };
+  if (dist0 + prjaxis + prjvec <= margin) put(dist0 + prjaxis + prjvec, 1.0, 1.0, nullptr, 0.0);
+  else return 0;
+  if (dist0 - prjaxis + prjvec <= margin) put(dist0 - prjaxis + prjvec, -1.0, 1.0, nullptr, 0.0);
+  R prjvec1 = -prjvec * R(0.5);
+  if (dist0 + prjaxis + prjvec1 <= margin) {
+    R vec1[3];
+    cross(vec1, vec, axis);
+    normalize3(vec1);
+    R s = R(size2[0]) * sqrt(R(3.0)) * R(0.5);
+    for (int k = 0; k < 3; k++) vec1[k] *= s;
+    put(dist0 + prjaxis + prjvec1, 1.0, -0.5, vec1, 1.0);
+    put(dist0 + prjaxis + prjvec1, 1.0, -0.5, vec1, -1.0);
+  }
+  return cnt;
+}
+
 // mjc_PlaneConvex, deepest point only (see the header note)
 template <class R>
 int plane_convex(const Model* m, Contact<R>* con, R margin, const R* pos1, const R* mat1, int g2, const R* pos2, const R* mat2) {

@@ -10,7 +10,7 @@
 
 namespace ok {
 
-enum { TASK_ACROBOT = 0, TASK_WALKER = 1, TASK_REACHING = 2, TASK_BOXSWEEP = 3 };
+enum { TASK_ACROBOT = 0, TASK_WALKER = 1, TASK_REACHING = 2, TASK_BOXSWEEP = 3, TASK_PUSH = 4 };
 enum { KP_SET_INTERVAL = 0, KP_ADAPTIVE_JERK = 1, KP_ADAPTIVE_ACCEL = 2, KP_ITERATIVE_ERROR = 3, KP_VELOCITY_CHANGE = 4 };
 
 // Mirrors tokp_task_desc (include/tokp.h) field for field.
@@ -181,6 +181,26 @@ void residuals(const Task& t, const Data<R>* d, R* r) {
       dx = ee[0] - d->qpos[gq]; dy = ee[1] - d->qpos[gq + 1];
       R dz = ee[2] - d->qpos[gq + 2];
       r[2] = sqrt(dx * dx + dy * dy + dz * dz) - R(t.target[4]);
+      break;
+    }
+    case TASK_PUSH: {  // TwoDPushing.cpp:291-356
+      using std::sqrt;
+      int nobs = t.num_resid - 4, k = 0;
+      int gq = t.qpos_adr[7], gv = t.dof_adr[7];
+      R dx = d->qpos[gq] - R(t.target[0]), dy = d->qpos[gq + 1] - R(t.target[1]);
+      r[k++] = sqrt(dx * dx + dy * dy);
+      r[k++] = sqrt(d->qvel[gv] * d->qvel[gv] + d->qvel[gv + 1] * d->qvel[gv + 1]);
+      for (int i = 0; i < nobs; i++) {
+        int oq = t.qpos_adr[10 + 3 * i];
+        dx = d->qpos[oq] - R(t.target[4 + 2 * i]); dy = d->qpos[oq + 1] - R(t.target[5 + 2 * i]);
+        r[k++] = sqrt(dx * dx + dy * dy);
+      }
+      r[k++] = v(5);
+      R ee[3];
+      body_world_pos(d->m, d->qpos.data(), t.aux[1], ee);
+      dx = ee[0] - d->qpos[gq]; dy = ee[1] - d->qpos[gq + 1];
+      R dz = ee[2] - d->qpos[gq + 2];
+      r[k++] = sqrt(dx * dx + dy * dy + dz * dz);
       break;
     }
     case TASK_REACHING:  // Reaching.cpp:28-60: joint positions against the goal configuration, then joint velocities

@@ -206,3 +206,76 @@ def test_box_sweep_optimise_cost(built):
     for b in range(2):
         assert abs(stats[b, 0] - sc["initial_cost"]) <= 1e-8 * abs(sc["initial_cost"])
         assert abs(stats[b, 1] - sc["new_cost"]) <= 0.01 * abs(sc["new_cost"]), (stats[b], sc)  # final cost within 1 %
+
+
+# ---- push_ncl / push_lcl / push_mcl (BASELINE configs[3]): cylinder_pushing*.xml, nv 21 / 39 / 63; plane-cylinder,
+# cylinder-cylinder / box-cylinder / mesh-cylinder through the convex collider, condim 1 and 3
+
+def _push_snaps(tc, count, seed):
+    snaps = []
+    for i in range(count):
+        start, _ = tc.load_trial(i)
+        r = np.random.default_rng(seed + i)
+        start[:7] += r.uniform(-0.05, 0.05, 7)
+        snaps.append(tc.start_snapshot(start_pos=start, qvel=0.05 * r.standard_normal(tc.n)))
+    return np.stack(snaps)
+
+
+@pytest.mark.parametrize("name,count,nsteps", [("push_ncl", 12, 12), ("push_lcl", 8, 10), ("push_mcl", 4, 8)])
+def test_push_step_worlds_match_oracle(built, name, count, nsteps):
+    tc = make(name)
+    m = tc.model
+    om = oracle_model(tc)
+    rng = np.random.default_rng(3)
+    snaps = _push_snaps(tc, count, 700)
+    lim = m.real("actuator_ctrlrange").reshape(-1, 2)[:, 1]
+    snaps[:, m.S - m.nu:] = rng.uniform(-0.3, 0.3, (count, m.nu)) * lim
+    out = np.zeros_like(snaps)
+    st = np.zeros(count, dtype=np.int32)
+    capi.check(capi.lib().tokp_step_worlds(m.h, capi._d(snaps), capi._d(out), count, nsteps, -1, 0.0, capi._i(st)))
+    assert not st.any(), st
+    d = oracle.Data(om)
+    worst = 0.0
+    for i in range(count):
+        d.load(snaps[i])
+        for _ in range(nsteps):
+            d.step()
+        assert d.get("warning")[0] == 0
+        ref = d.save()
+        worst = max(worst, np.abs(ref - out[i]).max() / max(1.0, np.abs(ref).max()))
+    assert worst < 1e-8, worst
+
+
+@pytest.mark.parametrize("name", ["push_ncl", "push_lcl"])
+def test_push_rollout_keypoints_jacobians_cost(built, name):
+    tc = make(name, kp_method=capi.KP_SET_INTERVAL, min_N=5)
+    T = 20
+    om = oracle_model(tc)
+    start, target = tc.load_trial(1)
+    ot = oracle_task(tc, target=target)
+    snap0 = tc.start_snapshot(start_pos=start)
+    U = random_controls(tc, T, 8, scale=0.1)
+    ref = oracle.ILQR(om, ot, T, threads=4)
+    c_ref = ref.rollout(snap0, U)
+    ref.generate_keypoints()
+    ref.dynamics_derivs()
+    tr = capi.Traj(tc, T, 1)
+    tr.set_targets(0, target)
+    c_dev = tr.rollout(snap0, U)[0]
+    assert abs(c_dev - c_ref) <= 1e-8 * max(1.0, abs(c_ref)), (c_dev, c_ref)
+    assert np.allclose(ref.get("resid"), tr.get(0, "resid"), rtol=0, atol=1e-8)
+    rows, pct = tr.keypoints()
+    assert rows[0] == ref.keypoints()
+    tr.dynamics_derivs()
+    nx = tr.nx
+    A_ref, B_ref = ref.get("A").reshape(T, nx, nx), ref.get("B").reshape(T, tr.m, nx)
+    A_dev, B_dev = tr.get(0, "A").reshape(T, nx, nx), tr.get(0, "B").reshape(T, tr.m, nx)
+    kp_rows = [t for t in range(T) if rows[0][t]]
+    errs = [max(rel_fro(A_dev[t], A_ref[t]), rel_fro(B_dev[t], B_ref[t])) for t in kp_rows]
+    assert max(errs) < AB_RTOL, errs
+    # one Optimise call: final cost within 1 %
+    ref.set_lambda(0.1)
+    ref.optimise(snap0, np.zeros((T, tc.m)), 2, 1)
+    sc = ref.scalars()
+    U_dev, stats = tr.optimise(snap0, np.zeros((T, tc.m)), 2, 1, lam=0.1)
+    assert abs(stats[0, 1] - sc["new_cost"]) <= 0.01 * abs(sc["new_cost"]), (stats[0], sc)

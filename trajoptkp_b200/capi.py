@@ -12,7 +12,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("TOKP_LIB", os.path.join(_HERE, "_build", "libtokp.so"))
 
 OBJ_BODY, OBJ_JOINT, OBJ_GEOM, OBJ_SITE, OBJ_ACTUATOR = 1, 3, 5, 6, 19
-TASK_ACROBOT, TASK_WALKER, TASK_REACHING, TASK_BOXSWEEP = 0, 1, 2, 3
+TASK_ACROBOT, TASK_WALKER, TASK_REACHING, TASK_BOXSWEEP, TASK_PUSH = 0, 1, 2, 3, 4
 KP_SET_INTERVAL, KP_ADAPTIVE_JERK, KP_ADAPTIVE_ACCEL, KP_ITERATIVE_ERROR, KP_VELOCITY_CHANGE = range(5)
 KP_NAMES = {"set_interval": 0, "setInterval": 0, "adaptive_jerk": 1, "adaptive_accel": 2, "iterative_error": 3,
             "velocity_change": 4}

@@ -126,13 +126,16 @@ TK_DEV void collision(const DM& m, WS& w, const Grp<G, NV>& g, int& status) {
             for (int k = 3; k < 6; k++) w.con_frame[6 * s + k] = 0.0;
             n++;
           }
+        } else if (NV == 0 && t2 == GEOM_CYLINDER) {
+          n = plane_cylinder(margin, pos1, mat1, pos2, mat2, &m.geom_size[3 * g2], &w.con_dist[slot], &w.con_pos[3 * slot],
+                             &w.con_frame[6 * slot]);
         } else if (NV == 0 && t2 == GEOM_MESH) {
           n = plane_convex(m, margin, pos1, mat1, g2, pos2, mat2, &w.con_dist[slot], &w.con_pos[3 * slot], &w.con_frame[6 * slot]);
         } else {
           status |= ST_UNSUPPORTED;
         }
       }
-    } else if (NV == 0 && (t1 == GEOM_MESH || t2 == GEOM_MESH) && is_convex_type(t1) && is_convex_type(t2)) {
+    } else if (NV == 0 && uses_convex_collider(t1, t2)) {
       // mj_collideGeoms: bounding-sphere filter, then the general convex collider.  Only the generic (NV = 0)
       // instantiation carries this code: the specialised walker / acrobot kernels have no mesh geoms
       double d[3] = {pos2[0] - pos1[0], pos2[1] - pos1[1], pos2[2] - pos1[2]};

@@ -265,6 +265,62 @@ TK_DEV bool obb_disjoint(const double* pos1, const double* mat1, const double* h
   return false;
 }
 
+// pairs MuJoCo's collision table sends to mjc_Convex among the geom types in scope: everything with a mesh, and the
+// cylinder pairs without a native collider (cylinder-cylinder, box-cylinder)
+TK_DEV bool uses_convex_collider(int t1, int t2) {
+  if (!is_convex_type(t1) || !is_convex_type(t2)) return false;
+  if (t1 == GEOM_MESH || t2 == GEOM_MESH) return true;
+  return (t1 == GEOM_CYLINDER && t2 == GEOM_CYLINDER) || (t1 == GEOM_CYLINDER && t2 == GEOM_BOX) ||
+         (t1 == GEOM_BOX && t2 == GEOM_CYLINDER);
+}
+
+// mjc_PlaneCylinder (engine_collision_primitive.c): the rim point nearest the plane on each cap, plus two points of the
+// nearer cap that complete a triangle; at most 4 contacts.  dist[], pos[3*], frame[6*] are slot arrays.
+TK_DEV int plane_cylinder(double margin, const double* pos1, const double* mat1, const double* pos2, const double* mat2,
+                          const double* size2, double* dist, double* pos, double* frame) {
+  double normal[3] = {mat1[2], mat1[5], mat1[8]};
+  double axis[3] = {mat2[2], mat2[5], mat2[8]};
+  double prjaxis = dot3(normal, axis);
+  if (prjaxis > 0.0) { for (int k = 0; k < 3; k++) axis[k] = -axis[k]; prjaxis = -prjaxis; }
+  double vec[3] = {pos2[0] - pos1[0], pos2[1] - pos1[1], pos2[2] - pos1[2]};
+  double dist0 = dot3(vec, normal);
+  for (int k = 0; k < 3; k++) vec[k] = axis[k] * prjaxis - normal[k];
+  double len_sqr = dot3(vec, vec);
+  if (len_sqr >= kMinVal * kMinVal) {
+    double scl = size2[0] / sqrt(len_sqr);
+    for (int k = 0; k < 3; k++) vec[k] *= scl;
+  } else {  // disc parallel to the plane: any radial direction, MuJoCo takes the cylinder's x axis
+    vec[0] = mat2[0] * size2[0]; vec[1] = mat2[3] * size2[0]; vec[2] = mat2[6] * size2[0];
+  }
+  double prjvec = dot3(vec, normal);
+  for (int k = 0; k < 3; k++) axis[k] *= size2[1];
+  prjaxis *= size2[1];
+  int cnt = 0;
+  auto put = [&](double d, double sa, double sv, const double* side, double ss) {
+    dist[cnt] = d;
+    for (int k = 0; k < 3; k++) {
+      pos[3 * cnt + k] = pos2[k] + sv * vec[k] + sa * axis[k] + (side ? ss * side[k] : 0.0) - normal[k] * d * 0.5;
+      frame[6 * cnt + k] = normal[k];
+      frame[6 * cnt + 3 + k] = 0.0;
+    }
+    cnt++;
+  };
+  if (dist0 + prjaxis + prjvec <= margin) put(dist0 + prjaxis + prjvec, 1.0, 1.0, nullptr, 0.0);
+  else return 0;
+  if (dist0 - prjaxis + prjvec <= margin) put(dist0 - prjaxis + prjvec, -1.0, 1.0, nullptr, 0.0);
+  double prjvec1 = -prjvec * 0.5;
+  if (dist0 + prjaxis + prjvec1 <= margin) {
+    double vec1[3];
+    cross3(vec1, vec, axis);
+    normalize3(vec1);
+    double s = size2[0] * sqrt(3.0) * 0.5;
+    for (int k = 0; k < 3; k++) vec1[k] *= s;
+    put(dist0 + prjaxis + prjvec1, 1.0, -0.5, vec1, 1.0);
+    put(dist0 + prjaxis + prjvec1, 1.0, -0.5, vec1, -1.0);
+  }
+  return cnt;
+}
+
 // mjc_Convex: writes dist, pos[3], frame[0:6] (tangent hint zero); returns the number of contacts (0 or 1)
 TK_DEV int convex_convex(const DM& m, double margin, int g1, const double* pos1, const double* mat1, int g2, const double* pos2,
                          const double* mat2, double* dist, double* pos, double* frame) {

@@ -1,5 +1,5 @@
 // Device restatement of the task residuals / cost (MT::Residuals overrides:
-// src/ModelTranslator/Acrobot.cpp:26-55, src/ModelTranslator/Walker.cpp:59-90, src/ModelTranslator/Reaching.cpp:28-60, src/ModelTranslator/BoxSweep.cpp:101-139;
+// src/ModelTranslator/Acrobot.cpp:26-55, src/ModelTranslator/Walker.cpp:59-90, src/ModelTranslator/Reaching.cpp:28-60, src/ModelTranslator/BoxSweep.cpp:101-139, src/ModelTranslator/TwoDPushing.cpp:291-356;
 // MT::CostFunction src/ModelTranslator/ModelTranslator.cpp:314-327).
 #pragma once
 #include "step.cuh"
@@ -85,6 +85,27 @@ __device__ inline void task_residuals(const DM& dm, const TaskDev& t, const doub
       dx = ee[0] - q[gq]; dy = ee[1] - q[gq + 1];
       double dz = ee[2] - q[gq + 2];
       r[2] = sqrt(dx * dx + dy * dy + dz * dz) - target[4];
+      break;
+    }
+    case TOKP_TASK_PUSH: {
+      // TwoDPushing.cpp:291-356: state = 7 arm joints, then x, y, z of the goal and of every obstacle (free joints)
+      int nobs = t.nr - 4;
+      int gq = t.qpos_adr[7], gv = t.dof_adr[7];
+      double dx = q[gq] - target[0], dy = q[gq + 1] - target[1];
+      int k = 0;
+      r[k++] = sqrt(dx * dx + dy * dy);
+      r[k++] = sqrt(v[gv] * v[gv] + v[gv + 1] * v[gv + 1]);
+      for (int i = 0; i < nobs; i++) {  // obstacle displacement from its start position
+        int oq = t.qpos_adr[10 + 3 * i];
+        dx = q[oq] - target[4 + 2 * i]; dy = q[oq + 1] - target[5 + 2 * i];
+        r[k++] = sqrt(dx * dx + dy * dy);
+      }
+      r[k++] = v[t.dof_adr[5]];
+      double ee[3];
+      body_world_pos(dm, q, t.aux[1], ee);
+      dx = ee[0] - q[gq]; dy = ee[1] - q[gq + 1];
+      double dz = ee[2] - q[gq + 2];
+      r[k++] = sqrt(dx * dx + dy * dy + dz * dz);
       break;
     }
     default:

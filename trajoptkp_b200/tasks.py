@@ -17,6 +17,9 @@ TASKS = {
     "walker_run": ("tasks/walker_run.yaml", "models/walker_plane.xml", capi.TASK_WALKER),
     "reaching": ("tasks/reaching.yaml", "models/franka/reaching_scene.xml", capi.TASK_REACHING),
     "box_sweep": ("tasks/box_sweep.yaml", "models/franka/boxSweep.xml", capi.TASK_BOXSWEEP),
+    "push_ncl": ("tasks/push_ncl.yaml", "models/franka/cylinder_pushing.xml", capi.TASK_PUSH),
+    "push_lcl": ("tasks/push_lcl.yaml", "models/franka/cylinder_pushing_lowClutter.xml", capi.TASK_PUSH),
+    "push_mcl": ("tasks/push_mcl.yaml", "models/franka/cylinder_pushing_heavyClutter.xml", capi.TASK_PUSH),
 }
 
 
@@ -76,16 +79,16 @@ class TaskConfig:
                     vel.append(float(body["linearMagVelThreshold"][k]))
                     start.append(float(body["startLinearPos"][k]))
         self.aux = np.zeros(0, dtype=np.int32)
-        if kind == capi.TASK_BOXSWEEP:
+        if kind in (capi.TASK_BOXSWEEP, capi.TASK_PUSH):
             self.aux = np.array([m.name2id(capi.OBJ_BODY, "goal"), m.name2id(capi.OBJ_BODY, "franka_gripper")],
                                 dtype=np.int32)
             if (self.aux < 0).any():
-                raise KeyError("box_sweep needs the bodies 'goal' and 'franka_gripper'")
+                raise KeyError("box_sweep / push need the bodies 'goal' and 'franka_gripper'")
         target, weight, weight_t = [], [], []
         self.resid_target_sizes = []
         for rn, r in cfg["residuals"].items():
             dim = int(r.get("resid_dimension", 1))
-            if kind == capi.TASK_BOXSWEEP:  # vector targets, concatenated (tokp_task_desc.num_target)
+            if kind in (capi.TASK_BOXSWEEP, capi.TASK_PUSH):  # vector targets, concatenated (tokp_task_desc.num_target)
                 target += [float(x) for x in r["target"]]
                 weight.append(float(r["weight"]))
                 weight_t.append(float(r["weight_terminal"]))
@@ -149,6 +152,13 @@ class TaskConfig:
         rest = vals[nfile:]
         if self.kind == capi.TASK_BOXSWEEP:
             return start, np.array(rest[:len(self.target)])
+        if self.kind == capi.TASK_PUSH:
+            tg = np.array(rest[:len(self.target)])
+            # obstacle residuals measure the displacement from the obstacle's START position
+            # (full_state_vector.rigid_bodies[i + 1].start_linear_pos, TwoDPushing.cpp:332-333), not a file target
+            for i in range(self.nr - 4):
+                tg[4 + 2 * i:6 + 2 * i] = start[10 + 3 * i:12 + 3 * i]
+            return start, tg
         targets, p = [], 0
         for k, sz in enumerate(self.resid_target_sizes):
             if self.kind == capi.TASK_REACHING:  # residual_list[0].target[k] for the position residuals, 0 after

@@ -130,7 +130,7 @@ TK_DEV void collision(const DM& m, WS& w, const Grp<G, NV>& g, int& status) {
           n = plane_cylinder(margin, pos1, mat1, pos2, mat2, &m.geom_size[3 * g2], &w.con_dist[slot], &w.con_pos[3 * slot],
                              &w.con_frame[6 * slot]);
         } else if (NV == 0 && t2 == GEOM_MESH) {
-          n = plane_convex(m, margin, pos1, mat1, g2, pos2, mat2, &w.con_dist[slot], &w.con_pos[3 * slot], &w.con_frame[6 * slot]);
+          n = -1;  // narrow phase by the whole group, below
         } else {
           status |= ST_UNSUPPORTED;
         }
@@ -143,7 +143,7 @@ TK_DEV void collision(const DM& m, WS& w, const Grp<G, NV>& g, int& status) {
       bool boxed = (t1 == GEOM_MESH || t1 == GEOM_BOX) && (t2 == GEOM_MESH || t2 == GEOM_BOX);
       if (dot3(d, d) <= bound * bound &&
           !(boxed && obb_disjoint(pos1, mat1, &m.geom_size[3 * g1], pos2, mat2, &m.geom_size[3 * g2], margin)))
-        n = convex_convex(m, margin, g1, pos1, mat1, g2, pos2, mat2, &w.con_dist[slot], &w.con_pos[3 * slot], &w.con_frame[6 * slot]);
+        n = -1;  // narrow phase by the whole group, below
     } else {
       status |= ST_UNSUPPORTED;
     }
@@ -151,6 +151,34 @@ TK_DEV void collision(const DM& m, WS& w, const Grp<G, NV>& g, int& status) {
     w.cnt[p] = n;
   }
   g.sync();
+  if (NV == 0) {
+    // convex narrow phase: the pairs that passed the filters, one after the other, all lanes of the group on each
+    int slot = 0;
+    for (int p = 0; p < m.npair; p++) {
+      int g1 = m.pair_geom1[p], g2 = m.pair_geom2[p];
+      int t1 = m.geom_type[g1], t2 = m.geom_type[g2];
+      if (w.cnt[p] < 0) {  // group-uniform: every lane reads the same flag
+        double margin = fmax(m.geom_margin[g1], m.geom_margin[g2]);
+        double pos1[3], mat1[9], pos2[3], mat2[9], dist, cpos[3], frame[6];
+        geom_pose(m, w, g1, pos1, mat1);
+        geom_pose(m, w, g2, pos2, mat2);
+        int n = t1 == GEOM_PLANE ? plane_convex(m, g, margin, pos1, mat1, g2, pos2, mat2, &dist, cpos, frame)
+                                 : convex_convex(m, g, margin, g1, pos1, mat1, g2, pos2, mat2, &dist, cpos, frame);
+        g.sync();
+        if (g.gl == 0) {
+          if (n) {
+            make_frame(frame);
+            w.con_dist[slot] = dist;
+            for (int k = 0; k < 3; k++) w.con_pos[3 * slot + k] = cpos[k];
+            for (int k = 0; k < 6; k++) w.con_frame[6 * slot + k] = frame[k];
+          }
+          w.cnt[p] = n;
+        }
+        g.sync();
+      }
+      slot += pair_slots(t1, t2);
+    }
+  }
   // ordered compaction (pair order, then contact order), done by one lane: contact counts are tiny
   if (g.gl == 0) {
     int dst = 0, slot = 0;

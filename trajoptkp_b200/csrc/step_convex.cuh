@@ -7,9 +7,13 @@
 // geom2), pos = midpoint of the witnesses}; one contact per pair (mjENBL_MULTICCD is off by default).  Call sites on
 // the reference path: every mj_step / mj_stepSkip (src/Differentiator/Differentiator.cpp:69,118; iLQR.cpp:222,914).
 //
-// One lane runs one pair (the lanes of a group take the pairs of the world in turn, as the primitive colliders do);
-// the support function of a mesh scans its merged vertices, whose maximiser is the hull's.  plane-mesh yields the
-// deepest vertex only (MuJoCo adds up to three hull neighbours; no hull graph is built).
+// The lanes of a group first filter the pairs of their world one pair per lane (bounding spheres, oriented boxes);
+// the pairs that survive go through the narrow phase one after the other with the WHOLE group on each: the MPR state
+// is replicated in every lane (group-uniform control flow, like the rest of the step) and the support function of a
+// mesh - a scan of its merged vertices, whose maximiser is the hull's - is split over the lanes and reduced by
+// shuffles (first maximal index wins, so the result equals the serial scan's).  A lane-per-pair narrow phase spent 64 %
+// of the FD kernel's instructions in these scans at 1.8 active lanes (profiles/r1t_*).  plane-mesh yields the deepest
+// vertex only (MuJoCo adds up to three hull neighbours; no hull graph is built).
 #pragma once
 #include "step.cuh"
 
@@ -32,19 +36,34 @@ struct CvxObj {
   double margin;
 };
 
-// mjccd_support: farthest point of the inflated geom along the unit world direction dir
-TK_DEV void convex_support(const DM& m, const CvxObj& o, const double* dir, double* res) {
+// index of the first vertex maximising v . ld, the n vertices split over the lanes of the group
+template <int G, int NV>
+TK_DEV int mesh_argmax(const Grp<G, NV>& g, const double* v, int n, const double* ld) {
+  double bd = -1e300;
+  int best = 0x7fffffff;
+  for (int i = g.gl; i < n; i += G) {
+    double dd = v[3 * i] * ld[0] + v[3 * i + 1] * ld[1] + v[3 * i + 2] * ld[2];
+    if (dd > bd) { bd = dd; best = i; }
+  }
+#pragma unroll
+  for (int off = G / 2; off > 0; off >>= 1) {
+    double od = __shfl_xor_sync(g.mask, bd, off, G);
+    int ob = __shfl_xor_sync(g.mask, best, off, G);
+    if (od > bd || (od == bd && ob < best)) { bd = od; best = ob; }
+  }
+  return best;
+}
+
+// mjccd_support: farthest point of the inflated geom along the unit world direction dir (group-cooperative: every
+// lane of the group calls it with the same arguments and receives the same point)
+template <int G, int NV>
+TK_DEV void convex_support(const DM& m, const Grp<G, NV>& g, const CvxObj& o, const double* dir, double* res) {
   const double* size = &m.geom_size[3 * o.geom];
   double ld[3], lp[3] = {0.0, 0.0, 0.0};
   for (int k = 0; k < 3; k++) ld[k] = o.mat[k] * dir[0] + o.mat[3 + k] * dir[1] + o.mat[6 + k] * dir[2];
   if (o.type == GEOM_MESH) {
     const double* v = &m.mesh_vert[3 * m.geom_meshadr[o.geom]];
-    int n = m.geom_meshnum[o.geom], best = 0;
-    double bd = v[0] * ld[0] + v[1] * ld[1] + v[2] * ld[2];
-    for (int i = 1; i < n; i++) {
-      double dd = v[3 * i] * ld[0] + v[3 * i + 1] * ld[1] + v[3 * i + 2] * ld[2];
-      if (dd > bd) { bd = dd; best = i; }
-    }
+    int best = mesh_argmax(g, v, m.geom_meshnum[o.geom], ld);
     for (int k = 0; k < 3; k++) lp[k] = v[3 * best + k];
   } else if (o.type == GEOM_BOX) {
     for (int k = 0; k < 3; k++) lp[k] = ld[k] >= 0.0 ? size[k] : -size[k];
@@ -67,10 +86,11 @@ TK_DEV void convex_support(const DM& m, const CvxObj& o, const double* dir, doub
 
 struct MprPt { double v[3], v1[3], v2[3]; };
 
-TK_DEV void mpr_support(const DM& m, const CvxObj& a, const CvxObj& b, const double* dir, MprPt& p) {
+template <int G, int NV>
+TK_DEV void mpr_support(const DM& m, const Grp<G, NV>& g, const CvxObj& a, const CvxObj& b, const double* dir, MprPt& p) {
   double nd[3] = {-dir[0], -dir[1], -dir[2]};
-  convex_support(m, a, dir, p.v1);
-  convex_support(m, b, nd, p.v2);
+  convex_support(m, g, a, dir, p.v1);
+  convex_support(m, g, b, nd, p.v2);
   for (int k = 0; k < 3; k++) p.v[k] = p.v1[k] - p.v2[k];
 }
 
@@ -133,14 +153,16 @@ TK_DEV void mpr_expand(MprPt* p, const MprPt& v4) {
 }
 
 // ccdMPRPenetration: 1 and depth / dir / pos when the inflated geoms intersect, else 0
-TK_DEV int mpr_penetration(const DM& m, const CvxObj& a, const CvxObj& b, double* depth, double* dir_out, double* pos_out) {
+template <int G, int NV>
+TK_DEV int mpr_penetration(const DM& m, const Grp<G, NV>& g, const CvxObj& a, const CvxObj& b, double* depth, double* dir_out,
+                           double* pos_out) {
   MprPt p[4];  // p[0] = interior point, p[1..3] = portal
   double dir[3], va[3], vb[3];
   for (int k = 0; k < 3; k++) { p[0].v1[k] = a.pos[k]; p[0].v2[k] = b.pos[k]; p[0].v[k] = a.pos[k] - b.pos[k]; }
   if (ccd_zero3(p[0].v)) p[0].v[0] = p[0].v[0] + 10.0 * kCcdEps;
   for (int k = 0; k < 3; k++) dir[k] = -p[0].v[k];
   normalize3(dir);
-  mpr_support(m, a, b, dir, p[1]);
+  mpr_support(m, g, a, b, dir, p[1]);
   double d = dot3(p[1].v, dir);
   if (ccd_zero(d) || d < 0.0) return 0;
   cross3(dir, p[0].v, p[1].v);
@@ -157,7 +179,7 @@ TK_DEV int mpr_penetration(const DM& m, const CvxObj& a, const CvxObj& b, double
     return 1;
   }
   normalize3(dir);
-  mpr_support(m, a, b, dir, p[2]);
+  mpr_support(m, g, a, b, dir, p[2]);
   d = dot3(p[2].v, dir);
   if (ccd_zero(d) || d < 0.0) return 0;
   for (int k = 0; k < 3; k++) { va[k] = p[1].v[k] - p[0].v[k]; vb[k] = p[2].v[k] - p[0].v[k]; }
@@ -169,7 +191,7 @@ TK_DEV int mpr_penetration(const DM& m, const CvxObj& a, const CvxObj& b, double
   }
   for (int guard = 0;; guard++) {
     if (guard > 100) return 0;
-    mpr_support(m, a, b, dir, p[3]);
+    mpr_support(m, g, a, b, dir, p[3]);
     d = dot3(p[3].v, dir);
     if (ccd_zero(d) || d < 0.0) return 0;
     bool cont = false;
@@ -191,14 +213,14 @@ TK_DEV int mpr_penetration(const DM& m, const CvxObj& a, const CvxObj& b, double
     mpr_portal_dir(p, dir);
     d = dot3(dir, p[1].v);
     if (ccd_zero(d) || d > 0.0) break;
-    mpr_support(m, a, b, dir, v4);
+    mpr_support(m, g, a, b, dir, v4);
     d = dot3(v4.v, dir);
     if (!(ccd_zero(d) || d > 0.0) || mpr_reach_tolerance(p, v4, dir) || guard > 1000) return 0;
     mpr_expand(p, v4);
   }
   for (int it = 0;; it++) {
     mpr_portal_dir(p, dir);
-    mpr_support(m, a, b, dir, v4);
+    mpr_support(m, g, a, b, dir, v4);
     if (mpr_reach_tolerance(p, v4, dir) || it > kMprIter) {
       double w[3];
       closest_on_triangle_to_origin(p[1].v, p[2].v, p[3].v, w);
@@ -322,12 +344,13 @@ TK_DEV int plane_cylinder(double margin, const double* pos1, const double* mat1,
 }
 
 // mjc_Convex: writes dist, pos[3], frame[0:6] (tangent hint zero); returns the number of contacts (0 or 1)
-TK_DEV int convex_convex(const DM& m, double margin, int g1, const double* pos1, const double* mat1, int g2, const double* pos2,
+template <int G, int NV>
+TK_DEV int convex_convex(const DM& m, const Grp<G, NV>& g, double margin, int g1, const double* pos1, const double* mat1, int g2, const double* pos2,
                          const double* mat2, double* dist, double* pos, double* frame) {
   CvxObj a{g1, m.geom_type[g1], pos1, mat1, 0.5 * margin};
   CvxObj b{g2, m.geom_type[g2], pos2, mat2, 0.5 * margin};
   double depth, dir[3], cp[3];
-  if (!mpr_penetration(m, a, b, &depth, dir, cp)) return 0;
+  if (!mpr_penetration(m, g, a, b, &depth, dir, cp)) return 0;
   if (dir[0] == 0.0 && dir[1] == 0.0 && dir[2] == 0.0) return 0;
   *dist = margin - depth;
   for (int k = 0; k < 3; k++) { frame[k] = dir[k]; pos[k] = cp[k]; frame[3 + k] = 0.0; }
@@ -335,11 +358,12 @@ TK_DEV int convex_convex(const DM& m, double margin, int g1, const double* pos1,
 }
 
 // mjc_PlaneConvex, deepest point only
-TK_DEV int plane_convex(const DM& m, double margin, const double* pos1, const double* mat1, int g2, const double* pos2,
+template <int G, int NV>
+TK_DEV int plane_convex(const DM& m, const Grp<G, NV>& g, double margin, const double* pos1, const double* mat1, int g2, const double* pos2,
                         const double* mat2, double* dist, double* pos, double* frame) {
   double nrm[3] = {mat1[2], mat1[5], mat1[8]}, nd[3] = {-mat1[2], -mat1[5], -mat1[8]}, vec[3], dif[3];
   CvxObj o{g2, m.geom_type[g2], pos2, mat2, 0.0};
-  convex_support(m, o, nd, vec);
+  convex_support(m, g, o, nd, vec);
   for (int k = 0; k < 3; k++) dif[k] = vec[k] - pos1[k];
   double dd = dot3(dif, nrm);
   if (dd > margin) return 0;

@@ -300,6 +300,15 @@ int launch_fd(tokp_traj* tr, const unsigned long long* mask, const int* rows, in
   return TOKP_OK;
 }
 
+// contact-rich batches (push scenes: 30-120 rows) would send most worlds through the low-occupancy redo pass: when
+// more than 5 % of a launch overflowed, the next launches of this batch start from twice the capacity
+void adapt_fast_capacity(tokp_traj* tr, long long worlds, long long overflowed) {
+  if (worlds > 0 && overflowed * 20 > worlds) {
+    int cap = fast_ecap(tr->dm);
+    if (cap < tr->dm.maxefc) tr->dm.fast_ecap = cap * 2 < tr->dm.maxefc ? cap * 2 : tr->dm.maxefc;
+  }
+}
+
 // counters: worlds actually simulated and Jacobians (|C|/n per row) for the current key-point masks
 int update_fd_counters(tokp_traj* tr) {
   std::vector<unsigned long long> hm((size_t)tr->B * tr->T);
@@ -317,6 +326,7 @@ int update_fd_counters(tokp_traj* tr) {
   }
   tr->counters[0] = worlds;
   tr->counters[3] = hc[1];  // worlds that overflowed the fast constraint-row capacity and were re-run
+  adapt_fast_capacity(tr, worlds, hc[1]);
   tr->counters[1] = (int64_t)((double)cols / tr->n * 1e6);
   return TOKP_OK;
 }

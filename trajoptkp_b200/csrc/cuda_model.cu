@@ -33,7 +33,7 @@ int lanes_for_model(const DM& dm) {
 }
 
 int fast_ecap(const DM& dm) {
-  int cap = 32;
+  int cap = dm.fast_ecap > 0 ? dm.fast_ecap : 32;
   if (const char* e = getenv("TOKP_EFC_CAP")) { int v = atoi(e); if (v > 0) cap = v; }
   return cap < dm.maxefc ? cap : dm.maxefc;
 }
@@ -139,6 +139,7 @@ int ensure_device_model(const tokp_model* mc, const DM** out) {
     if (dm.maxefc > cap) dm.maxefc = cap;
   }
   dm.treedepth = h.dims[10];
+  dm.fast_ecap = 0;
   dm.iterations = h.opt_int[0]; dm.ls_iterations = h.opt_int[1];
   dm.timestep = h.opt_real[0];
   dm.gravity[0] = h.opt_real[1]; dm.gravity[1] = h.opt_real[2]; dm.gravity[2] = h.opt_real[3];

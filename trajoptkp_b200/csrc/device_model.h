@@ -7,6 +7,8 @@ struct DM {
   int nq, nv, nu, nbody, njnt, ngeom, npair, maxcontact, maxefc, treedepth;
   int iterations, ls_iterations;
   int any_damping, any_gravcomp;
+  int fast_ecap;  // constraint-row capacity of the fast pass (0 = default 32); a trajectory batch raises its own copy
+                  // when many of its FD worlds overflow (update_fd_counters)
   double timestep, gravity[3], tolerance, ls_tolerance, meaninertia;
   // int arrays
   const int *body_parentid, *body_rootid, *body_weldid, *body_jntadr, *body_jntnum, *body_dofadr, *body_dofnum, *body_depth;

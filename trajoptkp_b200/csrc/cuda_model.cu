@@ -108,7 +108,7 @@ int ensure_device_model(const tokp_model* mc, const DM** out) {
   AI(body_depth) AI(body_subtreemask_lo) AI(body_subtreemask_hi)
   AI(jnt_type) AI(jnt_qposadr) AI(jnt_dofadr) AI(jnt_bodyid) AI(jnt_limited)
   AI(dof_bodyid) AI(dof_jntid) AI(dof_parentid) AI(dof_ancmask_lo) AI(dof_ancmask_hi)
-  AI(geom_type) AI(geom_bodyid) AI(geom_condim) AI(geom_priority) AI(pair_geom1) AI(pair_geom2) AI(geom_meshadr) AI(geom_meshnum)
+  AI(geom_type) AI(geom_bodyid) AI(geom_condim) AI(geom_priority) AI(pair_geom1) AI(pair_geom2) AI(pair_slotadr) AI(geom_meshadr) AI(geom_meshnum)
   AI(actuator_trnid) AI(actuator_dofadr) AI(actuator_ctrllimited) AI(actuator_forcelimited) AI(actuator_biastype)
   AR(qpos0) AR(body_pos) AR(body_quat) AR(body_ipos) AR(body_iquat) AR(body_mass) AR(body_inertia) AR(body_invweight0)
   AR(body_gravcomp)

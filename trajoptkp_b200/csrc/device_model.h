@@ -16,7 +16,7 @@ struct DM {
   const int *jnt_type, *jnt_qposadr, *jnt_dofadr, *jnt_bodyid, *jnt_limited;
   const int *dof_bodyid, *dof_jntid, *dof_parentid;
   const unsigned *dof_ancmask_lo, *dof_ancmask_hi;
-  const int *geom_type, *geom_bodyid, *geom_condim, *geom_priority, *pair_geom1, *pair_geom2, *geom_meshadr, *geom_meshnum;
+  const int *geom_type, *geom_bodyid, *geom_condim, *geom_priority, *pair_geom1, *pair_geom2, *pair_slotadr, *geom_meshadr, *geom_meshnum;
   const int *actuator_trnid, *actuator_dofadr, *actuator_ctrllimited, *actuator_forcelimited, *actuator_biastype;
   // real arrays
   const double *qpos0, *body_pos, *body_quat, *body_ipos, *body_iquat, *body_mass, *body_inertia, *body_invweight0,

@@ -827,6 +827,7 @@ struct Compiler {
             if (m.geom_type[a] == GEOM_PLANE && m.geom_type[b] == GEOM_PLANE) continue;
             m.pair_geom1.push_back(a);
             m.pair_geom2.push_back(b);
+            m.pair_slotadr.push_back(maxcon);
             int nc = pair_maxcontacts(m.geom_type[a], m.geom_type[b]);
             int condim = std::max(m.geom_condim[a], m.geom_condim[b]);
             if (m.geom_priority[a] != m.geom_priority[b])

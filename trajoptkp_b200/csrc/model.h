@@ -27,7 +27,7 @@ enum GeomType { GEOM_PLANE = 0, GEOM_HFIELD = 1, GEOM_SPHERE = 2, GEOM_CAPSULE =
   X(dof_ancmask_lo) X(dof_ancmask_hi) /* bit j set: dof j is dof i or one of its ancestors */      \
   X(geom_type) X(geom_bodyid) X(geom_contype) X(geom_conaffinity) X(geom_condim)                   \
   X(geom_priority) X(geom_meshadr) X(geom_meshnum)                                                 \
-  X(pair_geom1) X(pair_geom2)                                                                      \
+  X(pair_geom1) X(pair_geom2) X(pair_slotadr) /* first contact slot of the pair (prefix of its maximum contacts) */ \
   X(actuator_trnid) X(actuator_dofadr) X(actuator_ctrllimited) X(actuator_forcelimited)            \
   X(actuator_biastype)
 

@@ -85,8 +85,7 @@ TK_DEV void collision(const DM& m, WS& w, const Grp<G, NV>& g, int& status) {
   for (int p = g.gl; p < m.npair; p += G) {
     int g1 = m.pair_geom1[p], g2 = m.pair_geom2[p];
     int t1 = m.geom_type[g1], t2 = m.geom_type[g2];
-    int slot = 0;
-    for (int q = 0; q < p; q++) slot += pair_slots(m.geom_type[m.pair_geom1[q]], m.geom_type[m.pair_geom2[q]]);
+    int slot = m.pair_slotadr[p];  // prefix of pair_slots(), laid down by the model compiler
     double margin = fmax(m.geom_margin[g1], m.geom_margin[g2]);
     double pos1[3], mat1[9], pos2[3], mat2[9];
     geom_pose(m, w, g1, pos1, mat1);
@@ -153,11 +152,11 @@ TK_DEV void collision(const DM& m, WS& w, const Grp<G, NV>& g, int& status) {
   g.sync();
   if (NV == 0) {
     // convex narrow phase: the pairs that passed the filters, one after the other, all lanes of the group on each
-    int slot = 0;
     for (int p = 0; p < m.npair; p++) {
-      int g1 = m.pair_geom1[p], g2 = m.pair_geom2[p];
-      int t1 = m.geom_type[g1], t2 = m.geom_type[g2];
       if (w.cnt[p] < 0) {  // group-uniform: every lane reads the same flag
+        int g1 = m.pair_geom1[p], g2 = m.pair_geom2[p];
+        int t1 = m.geom_type[g1];
+        int slot = m.pair_slotadr[p];
         double margin = fmax(m.geom_margin[g1], m.geom_margin[g2]);
         double pos1[3], mat1[9], pos2[3], mat2[9], dist, cpos[3], frame[6];
         geom_pose(m, w, g1, pos1, mat1);
@@ -176,14 +175,13 @@ TK_DEV void collision(const DM& m, WS& w, const Grp<G, NV>& g, int& status) {
         }
         g.sync();
       }
-      slot += pair_slots(t1, t2);
     }
   }
   // ordered compaction (pair order, then contact order), done by one lane: contact counts are tiny
   if (g.gl == 0) {
-    int dst = 0, slot = 0;
+    int dst = 0;
     for (int p = 0; p < m.npair; p++) {
-      int n = w.cnt[p];
+      int n = w.cnt[p], slot = m.pair_slotadr[p];
       for (int i = 0; i < n; i++) {
         int s = slot + i;
         if (s != dst) {
@@ -194,7 +192,6 @@ TK_DEV void collision(const DM& m, WS& w, const Grp<G, NV>& g, int& status) {
         w.con_pair[dst] = p;
         dst++;
       }
-      slot += pair_slots(m.geom_type[m.pair_geom1[p]], m.geom_type[m.pair_geom2[p]]);
     }
     w.cnt[m.npair > m.njnt ? m.npair : m.njnt] = dst;
   }

@@ -102,6 +102,9 @@ int tokp_model_get_int(const tokp_model* m, const char* field, int32_t* out, int
 /* doubles per snapshot: [time | qpos nq | qvel nv | qacc nv | qacc_warmstart nv | qfrc_applied nv |
  * xfrc_applied 6*nbody | ctrl nu] - the 8 fields of MuJoCoHelper::CpMjData (MuJoCoHelper.cpp:732-741) */
 int tokp_snapshot_size(const tokp_model* m);
+/* mj_kinematics restricted to the chain world -> body (host): world position and orientation of a body at qpos[nq],
+ * what MuJoCoHelper::GetBodyPoseQuatViaXpos (MuJoCoHelper.cpp:400-410) reads after mj_kinematics */
+int tokp_model_body_pose(const tokp_model* m, const double* qpos, int body, double pos[3], double quat[4]);
 
 /* ---- trajectory batch (Optimiser storage include/Optimiser/Optimiser.h:194-211; iLQR::Resize iLQR.cpp:37-200;
  *      saved_systems_state_list / fd_data include/MuJoCoHelper.h:118-123) --------------------------------- */
@@ -120,12 +123,29 @@ int tokp_traj_get_snapshot(tokp_traj* tr, int b, int t, double* snapshot);
 int tokp_step_worlds(const tokp_model* m, const double* snapshots_in, double* snapshots_out, int count, int nsteps,
                      int solver_iterations, double solver_tolerance, int* status);
 
+/* the same followed by one mj_forward (ModelTranslator::CreateInitSetupControls, ModelTranslator.cpp:875-880, between the
+ * plant step and Optimise in GenTestingData.cpp:189-205): the state is the one after `nsteps` steps, qacc and
+ * qacc_warmstart are the constraint solver's solution at that state */
+int tokp_forward_worlds(const tokp_model* m, const double* snapshots_in, double* snapshots_out, int count, int nsteps,
+                        int solver_iterations, double solver_tolerance, int* status);
+
 /* iLQR::RolloutTrajectory (iLQR.cpp:202-254) for all B trajectories: snapshot0[B][S], U[B][T][m] -> cost[B] */
 int tokp_rollout(tokp_traj* tr, const double* snapshot0, const double* U, double* cost);
 /* pandaReaching::CreateInitOptimisationControls (src/ModelTranslator/Reaching.cpp:269-296): gravity-compensation
  * rollout from snapshot0[B][S]; control t = qfrc_bias of the state joints at step t (mj_forward), then mj_step.
  * U_out[B][T][m]; status[B] (optional) receives the per-world warning bits. */
 int tokp_init_controls_gravcomp(tokp_traj* tr, const double* snapshot0, double* U_out, int* status);
+/* PushBaseClass::JacobianEEControl (src/ModelTranslator/PushBaseClass.cpp:139-248) with its way-point builders
+ * (EEWayPointsSetup :8-44, EEWayPointsPush :46-115, CreateAllEETransitPoints :117-137), driven in the order of
+ * GenTestingData::GenDataOpenloopOptimisation (src/GenTestingData.cpp:177-220) for every trajectory of the batch:
+ * `pre_steps` x mj_step, mj_forward, CreateInitSetupControls(setup_horizon) (TwoDPushing.cpp:225-258; 0 = BoxSweep.cpp:63-70,
+ * no setup motion), snapshot0_out[B][S] <- state (what Optimise starts from), CreateInitOptimisationControls(T)
+ * (BoxSweep.cpp:72-99, TwoDPushing.cpp:260-289) -> U_out[B][T][m].  snapshot_start[B][S] = the state
+ * ModelTranslator::InitialiseSystemToStartState (ModelTranslator.cpp:1711-1781) leaves; goal_xy[B][2] =
+ * residual_list[0].target; task aux = {pushed body, end-effector body}.  Optional: U_setup_out[B][setup_horizon][m],
+ * status[B] (step warning bits; bit 6 = rank-deficient end-effector Jacobian). */
+int tokp_init_controls_ee(tokp_traj* tr, const double* snapshot_start, const double* goal_xy, int pre_steps,
+                          int setup_horizon, double* snapshot0_out, double* U_out, double* U_setup_out, int* status);
 /* KeypointGenerator::GenerateKeyPoints (KeyPointGenerator.cpp:76-135) on the nominal X_old; optional outputs:
  * counts[B][T], indices[B][T][2n] (row lists, in reference order, duplicates kept), pct[B][n] */
 int tokp_keypoints(tokp_traj* tr, int* counts, int* indices, double* pct);

@@ -5,6 +5,7 @@
 #include <string>
 
 #include "ok_ilqr.h"
+#include "ok_init.h"
 
 using namespace ok;
 
@@ -178,6 +179,19 @@ void ok_interpolate(const int* counts, const int* indices, int T, int n, int m, 
 void ok_percentages(const int* counts, const int* indices, int T, int n, double* pct) {
   auto p = keypoint_percentages(unpack_kp(counts, indices, T), n, T);
   for (int i = 0; i < n; i++) pct[i] = p[i];
+}
+
+// GenTestingData.cpp:177-220 for one BoxSweep / TwoDPushing trial (ok_init.h); returns warning bits or -1
+int ok_init_sequence_ee(const Model* m, const TaskDesc* td, const double* start, const double* goal_xy, int setup_horizon,
+                        int T, double* snapshot0, double* U, double* U_setup) {
+  int warn = -1;
+  if (guard([&] {
+        Task task;
+        task.init(m, td);
+        warn = init_sequence_ee(m, task, start, goal_xy, setup_horizon, T, snapshot0, U, U_setup);
+      }))
+    return -1;
+  return warn;
 }
 
 // ---- iLQR object ---------------------------------------------------------------------------

@@ -84,6 +84,7 @@ def lib():
         L.ok_keypoints.argtypes = [C.c_int, _dp, C.c_int, C.c_int, C.c_double, C.c_int, C.c_int, _dp, _dp, _ip, _ip, C.c_int]
         L.ok_interpolate.argtypes = [_ip, _ip, C.c_int, C.c_int, C.c_int, _dp, _dp]
         L.ok_percentages.argtypes = [_ip, _ip, C.c_int, C.c_int, _dp]
+        L.ok_init_sequence_ee.argtypes = [C.c_void_p, C.POINTER(TaskDesc), _dp, _dp, C.c_int, C.c_int, _dp, _dp, _dp]
         L.ok_ilqr_create.restype = C.c_void_p
         L.ok_ilqr_create.argtypes = [C.c_void_p, C.POINTER(TaskDesc), C.c_int, C.c_int]
         L.ok_ilqr_destroy.argtypes = [C.c_void_p]
@@ -219,6 +220,21 @@ def residual_derivs(model, task, snap, central=True, eps=1e-6):
     if rc:
         raise RuntimeError(lib().ok_last_error().decode())
     return rx, ru[:, :task.m]
+
+
+def init_sequence_ee(model, task, start, goal_xy, setup_horizon, T):
+    """GenTestingData.cpp:177-220 for one BoxSweep (setup_horizon 0) / TwoDPushing (1000) trial:
+    returns (snapshot0, U[T][m], U_setup[setup_horizon][m], warning bits)."""
+    start = np.ascontiguousarray(start, dtype=np.float64)
+    goal = np.ascontiguousarray(goal_xy, dtype=np.float64)
+    snap0 = np.zeros(model.S)
+    U = np.zeros((T, task.m))
+    Us = np.zeros((max(setup_horizon, 1), task.m))
+    d = task.desc()
+    rc = lib().ok_init_sequence_ee(model.h, C.byref(d), _d(start), _d(goal), setup_horizon, T, _d(snap0), _d(U), _d(Us))
+    if rc < 0:
+        raise RuntimeError(lib().ok_last_error().decode())
+    return snap0, U, Us[:setup_horizon], rc
 
 
 def keypoints(method, X, n, T, dt, min_N, max_N, jerk_thr, vel_thr):

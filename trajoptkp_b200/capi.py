@@ -67,7 +67,9 @@ def lib():
     L.tokp_model_get_real.argtypes = [vp, C.c_char_p, _dp, C.c_int]
     L.tokp_model_get_int.argtypes = [vp, C.c_char_p, C.POINTER(C.c_int32), C.c_int]
     L.tokp_snapshot_size.argtypes = [vp]
+    L.tokp_model_body_pose.argtypes = [vp, _dp, C.c_int, _dp, _dp]
     L.tokp_step_worlds.argtypes = [vp, _dp, _dp, C.c_int, C.c_int, C.c_int, C.c_double, _ip]
+    L.tokp_forward_worlds.argtypes = [vp, _dp, _dp, C.c_int, C.c_int, C.c_int, C.c_double, _ip]
     L.tokp_launch_count.restype = C.c_int64
     if hasattr(L, "tokp_traj_create"):
         L.tokp_traj_create.argtypes = [vp, C.POINTER(TaskDesc), C.c_int, C.c_int, C.POINTER(vp)]
@@ -78,6 +80,7 @@ def lib():
         L.tokp_traj_get_snapshot.argtypes = [vp, C.c_int, C.c_int, _dp]
         L.tokp_rollout.argtypes = [vp, _dp, _dp, _dp]
         L.tokp_init_controls_gravcomp.argtypes = [vp, _dp, _dp, _ip]
+        L.tokp_init_controls_ee.argtypes = [vp, _dp, _dp, C.c_int, C.c_int, _dp, _dp, _dp, _ip]
         L.tokp_keypoints.argtypes = [vp, _ip, _ip, _dp]
         L.tokp_traj_set_keypoints.argtypes = [vp, C.c_int, _ip, _ip]
         L.tokp_dynamics_derivs.argtypes = [vp, C.c_int, C.c_double]
@@ -154,6 +157,14 @@ class Model:
         return out
 
     # ---- snapshot helpers (layout of MuJoCoHelper::CpMjData) -------------------------------------
+    def body_pose(self, qpos, body):
+        """World pose (pos[3], quat[4]) of a body at qpos (host kinematics of the chain)."""
+        q = np.ascontiguousarray(qpos, dtype=np.float64)
+        assert q.size == self.nq
+        pos, quat = np.zeros(3), np.zeros(4)
+        check(lib().tokp_model_body_pose(self.h, _d(q), int(body), _d(pos), _d(quat)))
+        return pos, quat
+
     def snapshot(self, qpos=None, qvel=None, ctrl=None, qacc=None, warm=None, time=0.0):
         s = np.zeros(self.S)
         s[0] = time
@@ -226,6 +237,18 @@ class Traj:
         st = np.zeros(self.B, dtype=np.int32)
         check(lib().tokp_init_controls_gravcomp(self.h, _d(s), _d(U), _i(st)))
         return U, st
+
+    def init_controls_ee(self, snap_start, goal_xy, pre_steps=1, setup_horizon=0, want_setup=False):
+        """GenTestingData.cpp:177-220 for BoxSweep (setup_horizon 0) / TwoDPushing (1000) trials on the device:
+        returns (snapshot0[B][S], U[B][T][m], status[B]) (+ U_setup[B][setup_horizon][m] when want_setup)."""
+        s = np.ascontiguousarray(np.broadcast_to(np.asarray(snap_start, dtype=np.float64), (self.B, self.model.S)))
+        g = np.ascontiguousarray(np.broadcast_to(np.asarray(goal_xy, dtype=np.float64), (self.B, 2)))
+        snap0 = np.zeros((self.B, self.model.S))
+        U = np.zeros((self.B, self.T, self.m))
+        Us = np.zeros((self.B, setup_horizon, self.m)) if (want_setup and setup_horizon) else None
+        st = np.zeros(self.B, dtype=np.int32)
+        check(lib().tokp_init_controls_ee(self.h, _d(s), _d(g), pre_steps, setup_horizon, _d(snap0), _d(U), _d(Us), _i(st)))
+        return (snap0, U, st, Us) if want_setup else (snap0, U, st)
 
     def keypoints(self):
         counts = np.zeros((self.B, self.T), dtype=np.int32)

@@ -2,7 +2,9 @@
 // (src/PhysicsSimulators/MuJoCoHelper.cpp:877-923) and the mj_name2id lookups of MuJoCoHelper.cpp:36-438.
 #include <cstring>
 #include <exception>
+#include <vector>
 
+#include "host_math.h"
 #include "tokp_internal.h"
 
 namespace tokp {
@@ -109,6 +111,57 @@ int tokp_model_get_int(const tokp_model* m, const char* field, int32_t* out, int
   TOKP_MODEL_INT_FIELDS(X)
 #undef X
   return -1000000;
+}
+
+int tokp_model_body_pose(const tokp_model* m, const double* qpos, int body, double pos[3], double quat[4]) {
+  if (!m || !qpos || !pos || !quat || body < 0 || body >= m->host.nbody()) { set_error("tokp_model_body_pose: bad argument"); return TOKP_ERR_ARG; }
+  namespace hm = tokp::hm;
+  const auto& h = m->host;
+  std::vector<int> chain;
+  for (int b = body; b > 0; b = h.body_parentid[b]) chain.push_back(b);
+  double xpos[3] = {0, 0, 0}, xquat[4] = {1, 0, 0, 0};
+  for (int c = (int)chain.size() - 1; c >= 0; c--) {
+    int b = chain[c];
+    int jadr = h.body_jntadr[b], jnum = h.body_jntnum[b];
+    if (jnum == 1 && h.jnt_type[jadr] == tokp::JNT_FREE) {
+      int qa = h.jnt_qposadr[jadr];
+      for (int k = 0; k < 3; k++) xpos[k] = qpos[qa + k];
+      for (int k = 0; k < 4; k++) xquat[k] = qpos[qa + 3 + k];
+      hm::quat_normalize(xquat);
+      continue;
+    }
+    double p[3], q[4];
+    hm::rot_vec_quat(p, &h.body_pos[3 * b], xquat);
+    for (int k = 0; k < 3; k++) p[k] += xpos[k];
+    hm::quat_mul(q, xquat, &h.body_quat[4 * b]);
+    for (int j = jadr; j >= 0 && j < jadr + jnum; j++) {
+      int qa = h.jnt_qposadr[j];
+      double axis[3], anchor[3];
+      hm::rot_vec_quat(axis, &h.jnt_axis[3 * j], q);
+      hm::rot_vec_quat(anchor, &h.jnt_pos[3 * j], q);
+      for (int k = 0; k < 3; k++) anchor[k] += p[k];
+      if (h.jnt_type[j] == tokp::JNT_SLIDE) {
+        double dq = qpos[qa] - h.qpos0[qa];
+        for (int k = 0; k < 3; k++) p[k] += axis[k] * dq;
+      } else if (h.jnt_type[j] == tokp::JNT_HINGE) {
+        double ql[4], t[4], v[3];
+        hm::axis_angle2quat(ql, &h.jnt_axis[3 * j], qpos[qa] - h.qpos0[qa]);
+        hm::quat_mul(t, q, ql);
+        for (int k = 0; k < 4; k++) q[k] = t[k];
+        hm::rot_vec_quat(v, &h.jnt_pos[3 * j], q);
+        for (int k = 0; k < 3; k++) p[k] = anchor[k] - v[k];
+      } else {
+        set_error("tokp_model_body_pose: unsupported joint type on the chain");
+        return TOKP_ERR_UNSUPPORTED;
+      }
+    }
+    hm::quat_normalize(q);
+    for (int k = 0; k < 3; k++) xpos[k] = p[k];
+    for (int k = 0; k < 4; k++) xquat[k] = q[k];
+  }
+  for (int k = 0; k < 3; k++) pos[k] = xpos[k];
+  for (int k = 0; k < 4; k++) quat[k] = xquat[k];
+  return TOKP_OK;
 }
 
 int tokp_snapshot_size(const tokp_model* m) {

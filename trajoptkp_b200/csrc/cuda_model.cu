@@ -156,7 +156,8 @@ int ensure_device_model(const tokp_model* mc, const DM** out) {
 // in/out: host-layout snapshots [count][S] already on the device
 template <int G, int NV>
 __global__ void k_step_worlds(DM dm, const double* __restrict__ in, double* __restrict__ out, int* __restrict__ status,
-                              int count, int nsteps, int iterations, double tolerance, int S, int wsd, int ecap, int pass) {
+                              int count, int nsteps, int iterations, double tolerance, int S, int wsd, int ecap, int pass,
+                              int forward_after) {
   extern __shared__ double smem[];
   constexpr int GPW = 32 / G;  // groups per warp
   tk::Grp<G, NV> g;
@@ -183,6 +184,12 @@ __global__ void k_step_worlds(DM dm, const double* __restrict__ in, double* __re
   g.sync();
   int st = 0;
   for (int k = 0; k < nsteps; k++) tk::step(dm, w, g, iterations, tolerance, time, st);
+  if (forward_after) {  // mj_forward: the state stays, qacc and qacc_warmstart become the solution at this state
+    tk::step_smooth(dm, w, g, st);
+    g.sync();
+    tk::fwd_constraint(dm, w, g, iterations, tolerance);
+    g.sync();
+  }
   double* o = out + (size_t)gidx * S;
   for (int i = g.gl; i < S; i += G) o[i] = 0.0;
   g.sync();
@@ -204,8 +211,9 @@ __global__ void k_step_worlds(DM dm, const double* __restrict__ in, double* __re
 
 using namespace tokp;
 
-extern "C" int tokp_step_worlds(const tokp_model* m, const double* snapshots_in, double* snapshots_out, int count,
-                                int nsteps, int solver_iterations, double solver_tolerance, int* status) {
+namespace tokp {
+static int step_worlds_impl(const tokp_model* m, const double* snapshots_in, double* snapshots_out, int count, int nsteps,
+                            int solver_iterations, double solver_tolerance, int* status, int forward_after) {
   if (!m || !snapshots_in || !snapshots_out || count <= 0 || nsteps < 0) { set_error("tokp_step_worlds: bad argument"); return TOKP_ERR_ARG; }
   const DM* dmp;
   int rc = ensure_device_model(m, &dmp);
@@ -218,12 +226,13 @@ extern "C" int tokp_step_worlds(const tokp_model* m, const double* snapshots_in,
     for (int i = 0; i < dm.nv + 6 * dm.nbody; i++)
       if (s[i] != 0.0) { set_error("tokp_step_worlds: non-zero qfrc_applied/xfrc_applied unsupported"); return TOKP_ERR_UNSUPPORTED; }
   }
-  double *d_in = nullptr, *d_out = nullptr;
-  int* d_st = nullptr;
   size_t bytes = (size_t)count * S * sizeof(double);
-  TOKP_CUDA(cudaMalloc(&d_in, bytes));
-  TOKP_CUDA(cudaMalloc(&d_out, bytes));
-  TOKP_CUDA(cudaMalloc(&d_st, count * sizeof(int)));
+  // one scratch allocation (in | out | status), released on every return path
+  struct Scratch { void* p = nullptr; ~Scratch() { if (p) cudaFree(p); } } scratch;
+  TOKP_CUDA(cudaMalloc(&scratch.p, 2 * bytes + (size_t)count * sizeof(int)));
+  double* d_in = static_cast<double*>(scratch.p);
+  double* d_out = d_in + (size_t)count * S;
+  int* d_st = reinterpret_cast<int*>(d_out + (size_t)count * S);
   TOKP_CUDA(cudaMemcpy(d_in, snapshots_in, bytes, cudaMemcpyHostToDevice));
   int iters = solver_iterations < 0 ? dm.iterations : solver_iterations;
   double tol = solver_iterations < 0 ? dm.tolerance : solver_tolerance;
@@ -231,12 +240,12 @@ extern "C" int tokp_step_worlds(const tokp_model* m, const double* snapshots_in,
   for (int pass = 0; pass < (needs_redo_pass(dm) ? 2 : 1); pass++) {
     LaunchPlan lp;
     rc = plan_launch(dm, G, pass, &lp);
-    if (rc) { cudaFree(d_in); cudaFree(d_out); cudaFree(d_st); return rc; }
+    if (rc) return rc;
     int blocks = (count + lp.worlds_per_block - 1) / lp.worlds_per_block;
 #define LAUNCH(GG, NN)                                                                                                    \
   TOKP_CUDA(cudaFuncSetAttribute(k_step_worlds<GG, NN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lp.smem));      \
   k_step_worlds<GG, NN><<<blocks, lp.warps * 32, lp.smem>>>(dm, d_in, d_out, d_st, count, nsteps, iters, tol, S, lp.wsd, \
-                                                        lp.ecap, pass);
+                                                        lp.ecap, pass, forward_after);
     TOKP_DISPATCH(G, dm.nv, LAUNCH)
 #undef LAUNCH
     g_launches++;
@@ -245,8 +254,18 @@ extern "C" int tokp_step_worlds(const tokp_model* m, const double* snapshots_in,
   TOKP_CUDA(cudaDeviceSynchronize());
   TOKP_CUDA(cudaMemcpy(snapshots_out, d_out, bytes, cudaMemcpyDeviceToHost));
   if (status) TOKP_CUDA(cudaMemcpy(status, d_st, count * sizeof(int), cudaMemcpyDeviceToHost));
-  cudaFree(d_in); cudaFree(d_out); cudaFree(d_st);
   return TOKP_OK;
+}
+}  // namespace tokp
+
+extern "C" int tokp_step_worlds(const tokp_model* m, const double* snapshots_in, double* snapshots_out, int count,
+                                int nsteps, int solver_iterations, double solver_tolerance, int* status) {
+  return step_worlds_impl(m, snapshots_in, snapshots_out, count, nsteps, solver_iterations, solver_tolerance, status, 0);
+}
+
+extern "C" int tokp_forward_worlds(const tokp_model* m, const double* snapshots_in, double* snapshots_out, int count,
+                                   int nsteps, int solver_iterations, double solver_tolerance, int* status) {
+  return step_worlds_impl(m, snapshots_in, snapshots_out, count, nsteps, solver_iterations, solver_tolerance, status, 1);
 }
 
 extern "C" int64_t tokp_launch_count(void) { return g_launches.load(); }

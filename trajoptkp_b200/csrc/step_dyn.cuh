@@ -436,8 +436,9 @@ TK_DEV void euler(const DM& m, WS& w, const Grp<G, NV>& g, double& time) {
 // then run the same region of this large code at the same time and share the instruction cache):
 //   step_smooth      position + velocity stages, actuation, smooth acceleration
 //   step_constrained constraint solver, acceleration check, Euler
+// position stage (mj_fwdPosition): everything that depends on qpos only.  xpos / xquat stay valid until step_velocity.
 template <int G, int NV>
-TK_DEV void step_smooth(const DM& m, WS& w, const Grp<G, NV>& g, int& status) {
+TK_DEV void step_position(const DM& m, WS& w, const Grp<G, NV>& g, int& status) {
   for (int i = g.gl; i < m.nq; i += G) if (bad_value(w.qpos[i])) status |= ST_BAD_QPOS;
   for (int i = g.gl; i < m.nv; i += G) if (bad_value(w.qvel[i])) status |= ST_BAD_QVEL;
   kinematics(m, w, g);
@@ -450,11 +451,22 @@ TK_DEV void step_smooth(const DM& m, WS& w, const Grp<G, NV>& g, int& status) {
   g.phase();
   make_constraint(m, w, g, status);
   g.phase();
+}
+
+// velocity stage + actuation + smooth acceleration (mj_fwdVelocity, mj_fwdActuation, mj_fwdAcceleration)
+template <int G, int NV>
+TK_DEV void step_velocity(const DM& m, WS& w, const Grp<G, NV>& g) {
   com_vel(m, w, g);
   passive_and_bias(m, w, g);
   g.phase();
   reference_constraint(m, w, g);
   actuation_acceleration(m, w, g);
+}
+
+template <int G, int NV>
+TK_DEV void step_smooth(const DM& m, WS& w, const Grp<G, NV>& g, int& status) {
+  step_position(m, w, g, status);
+  step_velocity(m, w, g);
 }
 
 template <int G, int NV>

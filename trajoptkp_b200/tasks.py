@@ -168,6 +168,54 @@ class TaskConfig:
             p += sz
         return start, np.array(targets)
 
+    # ---- ModelTranslator::InitialiseSystemToStartState ------------------------------------------
+    SETUP_HORIZON = 1000  # GenTestingData.cpp:197: CreateInitSetupControls(1000)
+
+    def trial_row(self, i):
+        """Raw row i of TestTasks/<task>: (robot joint starts, per body [x, y, z, r, p, y], residual targets as filed)."""
+        path = os.path.join(ASSETS, "test_tasks", self.name + ".csv")
+        rows = [l.strip() for l in open(path) if l.strip() and not l.startswith("#")]
+        vals = [float(v) for v in rows[i].rstrip(",").split(",")]
+        nr = self.num_robot_dofs
+        bodies = [vals[nr + 6 * k:nr + 6 * k + 6] for k in range(len(self.body_names))]
+        return np.array(vals[:nr]), bodies, vals[nr + 6 * len(self.body_names):]
+
+    def init_snapshot(self, i):
+        """The mjData state ModelTranslator::InitialiseSystemToStartState (ModelTranslator.cpp:1711-1781) leaves for
+        trial i of TestTasks (FileHandler::LoadTaskFromFile, FileHandler.cpp:471-578): everything zero, then
+        SetGoalVisuals of the task, robot joints at their start positions, every rigid body of the state vector at its
+        start pose (axis2Quat of the filed angles, StdInclude.cpp:124-147).  Returns (snapshot, goal_xy)."""
+        m = self.model
+        joints, bodies, rest = self.trial_row(i)
+        qpos = np.zeros(m.nq)
+        jnt_qposadr, body_jntadr = m.int("jnt_qposadr"), m.int("body_jntadr")
+
+        def set_body(name, pos, ang):
+            bid = m.name2id(capi.OBJ_BODY, name)
+            if bid < 0:
+                raise KeyError("body %s not in model" % name)
+            qa = int(jnt_qposadr[int(body_jntadr[bid])])
+            angle = float(np.sqrt(ang[0] ** 2 + ang[1] ** 2 + ang[2] ** 2))
+            sh = np.sin(angle / 2.0)
+            qpos[qa:qa + 3] = pos
+            qpos[qa + 3:qa + 7] = [np.cos(angle / 2.0), ang[0] * sh, ang[1] * sh, ang[2] * sh]
+
+        goal_xy = np.array(rest[:2]) if self.kind in (capi.TASK_BOXSWEEP, capi.TASK_PUSH) else None
+        # SetGoalVisuals (BoxSweep.cpp:52-61: z = 0; TwoDPushing.cpp:213-223: z = 0.032; Reaching.cpp:62-85)
+        if self.kind == capi.TASK_BOXSWEEP:
+            set_body("display_goal", [goal_xy[0], goal_xy[1], 0.0], [0.0, 0.0, 0.0])
+        elif self.kind == capi.TASK_PUSH:
+            set_body("display_goal", [goal_xy[0], goal_xy[1], 0.032], [0.0, 0.0, 0.0])
+        elif self.kind == capi.TASK_REACHING:
+            q = qpos.copy()
+            q[self.qpos_adr[:7]] = rest[:7]
+            pos, _ = m.body_pose(q, m.name2id(capi.OBJ_BODY, "franka_gripper"))
+            set_body("target", pos, [0.0, 0.0, 0.0])
+        qpos[self.qpos_adr[:self.num_robot_dofs]] = joints
+        for name, b in zip(self.body_names, bodies):
+            set_body(name, b[:3], b[3:])
+        return m.snapshot(qpos=qpos), goal_xy
+
     def start_snapshot(self, start_pos=None, qvel=None, ctrl=None):
         """InitialiseSystemToStartState for joint-only state vectors: qpos <- start positions, everything else 0."""
         m = self.model

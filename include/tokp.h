@@ -191,6 +191,12 @@ int tokp_optimise(tokp_traj* tr, const double* snapshot0, const double* U_init, 
  * returns count, -count if cap too small, -1e6 unknown */
 int tokp_traj_get(tokp_traj* tr, int b, const char* name, double* out, int cap);
 int tokp_traj_set(tokp_traj* tr, int b, const char* name, const double* in, int count);
+/* Per-trajectory step warnings, the analogue of mjData.warning: out[B][2]; out[b][0] = OR over all FD worlds of
+ * trajectory b since the last clear, out[b][1] = the same over rollout worlds.  Bits: 1 bad qpos, 2 bad qvel, 4 bad qacc,
+ * 8 constraint rows beyond the capacity (contacts dropped), 32 unsupported collision pair / contact dimension.
+ * tokp_dynamics_derivs and tokp_optimise return TOKP_ERR_UNSUPPORTED / TOKP_ERR_STATE themselves when bit 32 (any
+ * world) or bit 8 (FD worlds) is set. */
+int tokp_traj_status(tokp_traj* tr, int* out, int clear);
 /* counters of the last tokp_dynamics_derivs: [worlds, jacobians_x1e6, kernel_launches, worlds re-run with full row capacity] */
 int tokp_traj_counters(tokp_traj* tr, int64_t out[4]);
 /* CUDA-event time of the last derivative / backward / forward phase, ms (time_get_derivs_ms etc., iLQR.cpp:418-505) */

@@ -19,6 +19,7 @@ def oracle_sweep(tag, trials=range(100), T=500):
         d = oracle.Data(om)
         d.load(tc.start_snapshot(start_pos=start))
         d.step()                                             # GenTestingData.cpp:189: one plant step first
+        d.forward()                                          # CreateInitSetupControls (ModelTranslator.cpp:875-880)
         il = oracle.ILQR(om, oracle_task(tc, target=tg), T, threads=4)
         il.set_lambda(0.01)                                  # GenTestingData.cpp:217
         il.optimise(d.save(), np.zeros((T, tc.m)), 10, 3)

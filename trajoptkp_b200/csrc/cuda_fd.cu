@@ -10,6 +10,7 @@
 #include "traj.h"
 
 extern "C" int tokp_fd_kernel_ms(tokp_traj* tr, double out[3]);
+namespace tokp { int check_world_status(tokp_traj* tr, int column, const char* what); }
 
 namespace tokp {
 
@@ -36,6 +37,8 @@ struct FdArgs {
   int *list0, *list1;               // compacted world lists (gidx = row index * W + slot): all running / overflowed
   int* counts;                      // [0] |list0|, [1] |list1|, [2] cursor of pass 0, [3] cursor of pass 1
   int blocksync;                    // Grp::bsync level of this launch (0 = warps run independently)
+  int* wstatus;                     // [B][2] sticky per-trajectory warning bits (column 0 = FD worlds)
+  int last;                         // no further pass re-runs the worlds that overflow in this one
 };
 
 // which perturbation a world slot carries: kind 0 nominal, 1 control, 2 velocity, 3 position
@@ -187,6 +190,8 @@ __global__ void __launch_bounds__(G == 16 ? 384 : 128, G == 16 ? 1 : 2) k_fd_wor
       if (g.gl == 0) {
         a.status[(size_t)wd.row * a.W + wd.slot] = bits | (1 << 30);
         if (a.pass == 0 && (bits & tk::ST_OVERFLOW)) a.list1[atomicAdd(&a.counts[1], 1)] = (int)gidx;
+        int keep = a.last ? bits : (bits & ~tk::ST_OVERFLOW);
+        if (keep) atomicOr(&a.wstatus[2 * wd.b], keep);
       }
       g.sync();
     }
@@ -263,7 +268,7 @@ int launch_fd(tokp_traj* tr, const unsigned long long* mask, const int* rows, in
     double tmp[3];
     tokp_fd_kernel_ms(tr, tmp);
   }
-  a.list0 = tr->fd_list0; a.list1 = tr->fd_list1; a.counts = tr->fd_counts;
+  a.list0 = tr->fd_list0; a.list1 = tr->fd_list1; a.counts = tr->fd_counts; a.wstatus = tr->wstatus;
   a.ecap = 0; a.pass = 0;
   TOKP_CUDA(cudaMemsetAsync(tr->fd_counts, 0, 4 * sizeof(int), tr->stream));
   k_fd_plan<<<(int)((worlds + 255) / 256), 256, 0, tr->stream>>>(dm, a);
@@ -274,7 +279,7 @@ int launch_fd(tokp_traj* tr, const unsigned long long* mask, const int* rows, in
     LaunchPlan lp;
     int rc = plan_launch(dm, G, pass, &lp);
     if (rc) return rc;
-    a.ecap = lp.ecap; a.pass = pass;
+    a.ecap = lp.ecap; a.pass = pass; a.last = (pass == 1 || !needs_redo_pass(dm)) ? 1 : 0;
     // persistent grid: as many blocks as stay resident, never more than the worlds need
     long long need = (worlds + lp.worlds_per_block - 1) / lp.worlds_per_block;
     int blocks = (int)(need < (long long)lp.resident_blocks ? need : (long long)lp.resident_blocks);
@@ -347,7 +352,7 @@ extern "C" int tokp_dynamics_derivs(tokp_traj* tr, int central_diff, double eps)
   tr->timers[0] = ms;
   int rc2 = update_fd_counters(tr);
   if (rc2) return rc2;
-  return TOKP_OK;
+  return check_world_status(tr, 0, "tokp_dynamics_derivs");
 }
 
 extern "C" int tokp_dynamics_derivs_cols(tokp_traj* tr, int b, int t, const int* cols, int ncols, int central_diff,

@@ -442,6 +442,7 @@ void pack_snapshot(const tokp_traj* tr, const double* s, double* d);
 int check_applied_zero(const tokp_traj* tr, const double* s);
 int read_keypoints(tokp_traj* tr, int* counts, int* indices, double* pct);
 int update_fd_counters(tokp_traj* tr);
+int check_world_status(tokp_traj* tr, int column, const char* what);
 
 static int cost_derivs(tokp_traj* tr, int central, double eps) {
   int B = tr->B, T = tr->T;
@@ -730,6 +731,8 @@ extern "C" int tokp_optimise(tokp_traj* tr, const double* snapshot0, const doubl
     if (need) {
       rc = tokp_generate_derivatives(tr);
       if (rc) return rc;
+      rc = check_world_status(tr, 0, "tokp_optimise");
+      if (rc) return rc;
       rc = read_keypoints(tr, nullptr, nullptr, pct.data());
       if (rc) return rc;
       for (int b = 0; b < B; b++)
@@ -791,6 +794,8 @@ extern "C" int tokp_optimise(tokp_traj* tr, const double* snapshot0, const doubl
       if (converged && it >= min_iterations) done[b] = 1;
     }
   }
+  rc = check_world_status(tr, 1, "tokp_optimise");  // unsupported features inside a rollout
+  if (rc) return rc;
   if (U_out) TOKP_CUDA(cudaMemcpy(U_out, tr->U, (size_t)B * T * m * 8, cudaMemcpyDeviceToHost));
   if (stats)
     for (int b = 0; b < B; b++) {

@@ -28,6 +28,7 @@ struct RollArgs {
   int ecap, pass, last;  // last: no further pass re-runs overflowed worlds
   int spread;          // 1: one world per warp (first group only) - latency layout for small batches
   int bsync;           // Grp::bsync level: the block walks the stages of every step together
+  int* wstatus;        // [B][2] sticky per-trajectory warning bits (column 1 = rollout worlds)
 };
 
 template <int G, int NV>
@@ -136,6 +137,10 @@ __global__ void __launch_bounds__(G == 16 ? 384 : 128, G == 16 ? 1 : 2) k_rollou
   if (a.last && ovf) cost = __longlong_as_double(0x7ff8000000000000ll);  // constraint rows beyond the capacity: loud
   if (g.gl == 0) a.cost[a.mode == 0 ? b : b * a.NA + ai] = cost;
   if (g.gl == 0) a.flags[widx] = (a.pass == 0 && ovf) ? 1 : 0;
+  int bits = 0;
+  for (int k = 0; k < 6; k++) if (g.any((st >> k) & 1)) bits |= (1 << k);
+  if (!a.last) bits &= ~tk::ST_OVERFLOW;
+  if (g.gl == 0 && bits) atomicOr(&a.wstatus[2 * b + 1], bits);
 }
 
 int launch_rollout(tokp_traj* tr, int mode, const double* d_Uin, const double* d_alphas, int nalpha) {
@@ -148,7 +153,7 @@ int launch_rollout(tokp_traj* tr, int mode, const double* d_Uin, const double* d
   a.task = tr->task;
   if (mode == 1) a.NA = tokp_traj::NA;  // buffer stride; unused alpha slots are skipped by the grid size
   int G = tr->G;
-  a.flags = tr->roll_flags;
+  a.flags = tr->roll_flags; a.wstatus = tr->wstatus;
   int nworlds = mode == 0 ? tr->B : tr->B * tokp_traj::NA;
   // few worlds: latency layout - one world per warp with all 32 lanes on it (fewer trips through every strided
   // loop), one warp per block so that the worlds spread over the SMs

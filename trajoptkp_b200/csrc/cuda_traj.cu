@@ -70,6 +70,7 @@ extern "C" int tokp_traj_create(const tokp_model* m, const tokp_task_desc* td, i
   size_t o_prev = p.take((size_t)B * T * n, 4);
   size_t o_next = p.take((size_t)B * T * n, 4);
   size_t o_status = p.take((size_t)B * T * tr->W, 4);
+  size_t o_wst = p.take((size_t)B * 2, 4);
   size_t o_cost = p.take((size_t)B, 8);
   size_t o_dJ = p.take((size_t)B, 8);
   size_t o_lam = p.take((size_t)B, 8);
@@ -95,6 +96,7 @@ extern "C" int tokp_traj_create(const tokp_model* m, const tokp_task_desc* td, i
   tr->cand = (double*)(base + o_cand); tr->cand_cost = (double*)(base + o_candcost); tr->fd_out = (double*)(base + o_fd);
   tr->kp_mask = (unsigned long long*)(base + o_mask); tr->kp_last = (unsigned long long*)(base + o_last); tr->kp_flags = (int*)(base + o_flags);
   tr->kp_prev = (int*)(base + o_prev); tr->kp_next = (int*)(base + o_next); tr->status = (int*)(base + o_status);
+  tr->wstatus = (int*)(base + o_wst);
   tr->cost = (double*)(base + o_cost); tr->deltaJ = (double*)(base + o_dJ); tr->lambda_d = (double*)(base + o_lam);
   tr->bp_ok = (int*)(base + o_ok);
   tr->roll_flags = (int*)(base + o_rflags);
@@ -164,7 +166,36 @@ extern "C" int tokp_traj_set_keypoint_method(tokp_traj* tr, int kp_method, int m
   return TOKP_OK;
 }
 
+// Per-trajectory step warnings (the mjWARN_* analogues): out[b][0] = OR over every FD world of trajectory b since the
+// last clear, out[b][1] = the same for rollout worlds (nominal + line search).  Bits: 1 bad qpos, 2 bad qvel, 4 bad
+// qacc, 8 constraint rows beyond TOKP_EFC_MAX (contacts dropped), 32 unsupported collision pair / condim.
+extern "C" int tokp_traj_status(tokp_traj* tr, int* out, int clear) {
+  if (!tr || !out) { set_error("tokp_traj_status: bad argument"); return TOKP_ERR_ARG; }
+  TOKP_CUDA(cudaMemcpyAsync(out, tr->wstatus, (size_t)tr->B * 2 * 4, cudaMemcpyDeviceToHost, tr->stream));
+  if (clear) TOKP_CUDA(cudaMemsetAsync(tr->wstatus, 0, (size_t)tr->B * 2 * 4, tr->stream));
+  TOKP_CUDA(cudaStreamSynchronize(tr->stream));
+  return TOKP_OK;
+}
+
 namespace tokp {
+// after a phase: unsupported features and dropped contacts make A / B or a rollout wrong - fail loudly instead of
+// handing the optimiser a wrong model (the reference's MuJoCo would have aborted in mj_loadXML / raised mjWARN_CNSTRFULL)
+int check_world_status(tokp_traj* tr, int column, const char* what) {
+  std::vector<int> h((size_t)tr->B * 2);
+  TOKP_CUDA(cudaMemcpyAsync(h.data(), tr->wstatus, h.size() * 4, cudaMemcpyDeviceToHost, tr->stream));
+  TOKP_CUDA(cudaStreamSynchronize(tr->stream));
+  for (int b = 0; b < tr->B; b++) {
+    int bits = h[2 * b + column];
+    if (bits & 32) { set_error(std::string(what) + ": a world hit an unsupported collision pair or contact dimension"); return TOKP_ERR_UNSUPPORTED; }
+    if (column == 0 && (bits & 8)) {
+      set_error(std::string(what) + ": constraint rows of an FD world exceed TOKP_EFC_MAX, contacts were dropped (trajectory " +
+                std::to_string(b) + ")");
+      return TOKP_ERR_STATE;
+    }
+  }
+  return TOKP_OK;
+}
+
 // host snapshot [S] <-> device snapshot [SD]
 void pack_snapshot(const tokp_traj* tr, const double* s, double* d) {
   const DM& dm = tr->dm;

@@ -832,6 +832,24 @@ struct Compiler {
             int condim = std::max(m.geom_condim[a], m.geom_condim[b]);
             if (m.geom_priority[a] != m.geom_priority[b])
               condim = m.geom_priority[a] > m.geom_priority[b] ? m.geom_condim[a] : m.geom_condim[b];
+            // fail at load time, not silently inside a step: the narrow phase covers plane-{sphere, capsule, box,
+            // cylinder, mesh} and the convex collider's pairs (mesh-anything convex, cylinder-cylinder, box-cylinder);
+            // the constraint rows cover condim 1 and 3 (pyramidal)
+            {
+              int ta = m.geom_type[a], tb = m.geom_type[b];
+              auto convex = [](int t) { return t == GEOM_SPHERE || t == GEOM_CAPSULE || t == GEOM_CYLINDER || t == GEOM_BOX || t == GEOM_MESH; };
+              bool have = (ta == GEOM_PLANE && convex(tb)) ||
+                          (convex(ta) && convex(tb) &&
+                           (ta == GEOM_MESH || tb == GEOM_MESH || (ta == GEOM_CYLINDER && tb == GEOM_CYLINDER) ||
+                            (ta == GEOM_CYLINDER && tb == GEOM_BOX) || (ta == GEOM_BOX && tb == GEOM_CYLINDER)));
+              if (!have)
+                throw std::runtime_error("unsupported collision pair: geoms '" + m.geom_names[a] + "' (type " + std::to_string(ta) +
+                                         ") and '" + m.geom_names[b] + "' (type " + std::to_string(tb) +
+                                         ") have no narrow-phase function in this build (disable the pair with contype/conaffinity)");
+              if (condim != 1 && condim != 3)
+                throw std::runtime_error("unsupported contact dimension " + std::to_string(condim) + " for geoms '" + m.geom_names[a] +
+                                         "' / '" + m.geom_names[b] + "' (condim 1 and 3 are implemented)");
+            }
             maxcon += nc;
             maxefc += nc * (condim == 1 ? 1 : 2 * (condim - 1));
           }

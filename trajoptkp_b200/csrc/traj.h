@@ -90,6 +90,7 @@ struct tokp_traj {
   int* kp_flags;      // [B]: bit0 = velocity_change duplicate last row
   int *kp_prev, *kp_next;  // [B][T][n]
   int* status;        // [B][T][W]
+  int* wstatus;       // [B][2] sticky OR of the step status bits of every FD world / rollout world of trajectory b
   double *cost, *deltaJ, *lambda_d;  // [B]
   double *snap0_in, *U0_in;          // resident copies of the last host inputs of tokp_optimise ([B][SD], [B][T][m])
   int* bp_ok;         // [B]

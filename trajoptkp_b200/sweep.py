@@ -147,6 +147,48 @@ def method_name_of(tc):
             capi.KP_VELOCITY_CHANGE: "velocity_change"}[tc.kp_method]
 
 
+def prepare_trials(tc, trial_indices, horizon, tr=None):
+    """Everything GenDataOpenloopOptimisation does for a trial before Optimise (GenTestingData.cpp:177-214), for this
+    rank's trials at once on the device: InitialiseSystemToStartState, one plant step, CreateInitSetupControls
+    (mj_forward; TwoDPushing: 1000 controller steps that park the gripper behind the object),
+    CreateInitOptimisationControls of the task (zeros: acrobot / walker, ModelTranslator.cpp:1783-1797; gravity
+    compensation: Reaching.cpp:269-296; Jacobian end-effector follower: BoxSweep.cpp:72-99, TwoDPushing.cpp:260-289).
+    Returns (snapshot0[B][S], U[B][T][m], targets[B][...])."""
+    from . import capi
+    B = len(trial_indices)
+    snaps = np.zeros((B, tc.model.S))
+    goals = np.zeros((B, 2))
+    targets = []
+    franka = tc.kind in (capi.TASK_REACHING, capi.TASK_BOXSWEEP, capi.TASK_PUSH)
+    for r, j in enumerate(trial_indices):
+        start, tg = tc.load_trial(j % tc.num_trials())
+        targets.append(tg)
+        if franka:
+            snaps[r], g = tc.init_snapshot(j % tc.num_trials())
+            if g is not None:
+                goals[r] = g
+        else:
+            snaps[r] = tc.start_snapshot(start_pos=start)
+    targets = np.stack(targets)
+    st = np.zeros(B, dtype=np.int32)
+    if tr is None:
+        tr = capi.Traj(tc, horizon, B)
+    if tc.kind in (capi.TASK_BOXSWEEP, capi.TASK_PUSH):
+        setup = tc.SETUP_HORIZON if tc.kind == capi.TASK_PUSH else 0
+        snap0, U, st = tr.init_controls_ee(snaps, goals, pre_steps=1, setup_horizon=setup)
+    else:
+        snap0 = np.zeros_like(snaps)
+        capi.check(capi.lib().tokp_forward_worlds(tc.model.h, capi._d(snaps), capi._d(snap0), B, 1, -1, 0.0, capi._i(st)))
+        if tc.kind == capi.TASK_REACHING:
+            U, st2 = tr.init_controls_gravcomp(snap0)
+            st = st | st2
+        else:
+            U = np.zeros((B, horizon, tc.m))
+    if st.any():
+        raise RuntimeError("prepare_trials: step warnings %s" % sorted(set(int(x) for x in st if x)))
+    return snap0, U, targets
+
+
 def run_openloop_sweep(tc, horizon, num_trials=100, rank=0, world=1, dist=None, device=None, max_iter=10, min_iter=3,
                        lam=0.01, init_controls=None, batch=None):
     """GenDataOpenloopOptimisation on the device: this rank's trials as ONE tokp_traj batch (all trials of the rank
@@ -158,19 +200,10 @@ def run_openloop_sweep(tc, horizon, num_trials=100, rank=0, world=1, dist=None, 
     B = len(mine)
     recs = []
     if B:
-        snaps = np.zeros((B, tc.model.S))
-        targets = np.zeros((B, tc.nr))
-        for r, j in enumerate(mine):
-            start, tg = tc.load_trial(j % tc.num_trials())
-            snaps[r] = tc.start_snapshot(start_pos=start)
-            targets[r] = tg
-        # GenTestingData.cpp:189: one plant step before the optimisation starts
-        out = np.zeros_like(snaps)
-        st = np.zeros(B, dtype=np.int32)
-        capi.check(capi.lib().tokp_step_worlds(tc.model.h, capi._d(snaps), capi._d(out), B, 1, -1, 0.0, capi._i(st)))
-        snaps = out
-        U = np.zeros((B, horizon, tc.m)) if init_controls is None else init_controls(tc, mine, horizon)
         tr = capi.Traj(tc, horizon, B)
+        snaps, U, targets = prepare_trials(tc, mine, horizon, tr)
+        if init_controls is not None:
+            U = init_controls(tc, mine, horizon)
         for r in range(B):
             tr.set_targets(r, targets[r])
         t0 = time.perf_counter()

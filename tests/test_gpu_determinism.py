@@ -75,3 +75,51 @@ def test_lane_count_changes_only_rounding(built, lanes):
     per_row = [rel_fro(a, b) for a, b in zip(A1.reshape(-1, 18 * 18), A0.reshape(-1, 18 * 18))]
     assert np.median(per_row) < 1e-6
     assert np.mean(np.array(per_row) < 1e-4) > 0.9
+
+
+def _ab(name, B, T, share, kp=capi.KP_SET_INTERVAL, min_N=3, lanes=0):
+    tc = make(name, kp_method=kp, min_N=min_N, max_N=10)
+    if tc.kind in (capi.TASK_BOXSWEEP, capi.TASK_PUSH):
+        snaps, goals = zip(*[tc.init_snapshot(b) for b in range(B)])
+        tr = capi.Traj(tc, T, B)
+        snap0, U, st = tr.init_controls_ee(np.stack(snaps), np.stack(goals), pre_steps=1, setup_horizon=0)
+    else:
+        snap0 = np.stack([perturbed_start(tc, 40 + b, dq=0.05, dv=0.05) for b in range(B)])
+        U = np.stack([random_controls(tc, T, 90 + b) for b in range(B)])
+        tr = capi.Traj(tc, T, B)
+    tr.set_option("fd_stage_sharing", share)
+    tr.set_option("fd_lanes", lanes)
+    tr.rollout(snap0, U)
+    tr.generate_derivatives()
+    return (np.stack([tr.get(b, "A") for b in range(B)]), np.stack([tr.get(b, "B") for b in range(B)]),
+            tr.counters()[0])
+
+
+@pytest.mark.parametrize("name,B,T,kp", [("walker_run", 12, 40, capi.KP_SET_INTERVAL), ("acrobot", 8, 50, capi.KP_SET_INTERVAL),
+                                         ("box_sweep", 3, 150, capi.KP_SET_INTERVAL), ("reaching", 4, 30, capi.KP_SET_INTERVAL),
+                                         ("walker_run", 6, 33, capi.KP_ITERATIVE_ERROR)])
+def test_stage_sharing_changes_no_bit(built, name, B, T, kp):
+    """the control / velocity worlds of a key-point take the nominal world's position (and velocity) stage
+    and its factor of M + h D, as mj_stepSkip does in the reference (Differentiator.cpp:118,155,253,276).  The shared
+    values are the ones each world would have computed itself, so A and B must not change in a single bit."""
+    A1, B1, w1 = _ab(name, B, T, 1, kp)
+    A0, B0, w0 = _ab(name, B, T, 0, kp)
+    assert w1 == w0 and w1 > 0
+    assert np.array_equal(A1, A0)
+    assert np.array_equal(B1, B0)
+    assert np.abs(A1).max() > 0
+
+
+@pytest.mark.parametrize("name,B,T", [("walker_run", 12, 40), ("acrobot", 8, 50)])
+def test_lane_per_world_kernel_changes_only_rounding(built, name, B, T):
+    """The control / velocity worlds of small hinge / slide models run one world per lane (k_fd_dep_lanes): sequential
+    sums instead of butterfly reductions, so A / B agree with the group kernels up to rounding amplified by 1 / eps."""
+    A1, B1, w1 = _ab(name, B, T, 1, lanes=1)
+    A0, B0, w0 = _ab(name, B, T, 1, lanes=0)
+    assert w1 == w0 and w1 > 0
+    nx = A1.shape[-1] if A1.ndim == 3 else None
+    per_row = [rel_fro(a, b) for a, b in zip(A1.reshape(B * T, -1), A0.reshape(B * T, -1)) if np.abs(b).max() > 0]
+    assert np.median(per_row) < 1e-6, np.median(per_row)
+    assert np.mean(np.array(per_row) < 1e-4) > 0.9
+    per_row_b = [rel_fro(a, b) for a, b in zip(B1.reshape(B * T, -1), B0.reshape(B * T, -1)) if np.abs(b).max() > 0]
+    assert np.median(per_row_b) < 1e-6, np.median(per_row_b)

@@ -99,6 +99,7 @@ def lib():
         L.tokp_traj_get.argtypes = [vp, C.c_int, C.c_char_p, _dp, C.c_int]
         L.tokp_traj_set.argtypes = [vp, C.c_int, C.c_char_p, _dp, C.c_int]
         L.tokp_traj_status.argtypes = [vp, _ip, C.c_int]
+        L.tokp_traj_set_option.argtypes = [vp, C.c_char_p, C.c_int]
         L.tokp_traj_counters.argtypes = [vp, C.POINTER(C.c_int64)]
         L.tokp_timers.argtypes = [vp, _dp]
         L.tokp_fd_kernel_ms.argtypes = [vp, _dp]
@@ -250,6 +251,9 @@ class Traj:
         st = np.zeros(self.B, dtype=np.int32)
         check(lib().tokp_init_controls_ee(self.h, _d(s), _d(g), pre_steps, setup_horizon, _d(snap0), _d(U), _d(Us), _i(st)))
         return (snap0, U, st, Us) if want_setup else (snap0, U, st)
+
+    def set_option(self, name, value):
+        check(lib().tokp_traj_set_option(self.h, name.encode(), int(value)))
 
     def status(self, clear=False):
         """[B][2] sticky step-warning bits of the FD worlds / rollout worlds of each trajectory (tokp_traj_status)."""

@@ -2,8 +2,18 @@
 // pair is one independent one-step world; one launch per iteration.
 // Replaces Optimiser::ComputeDynamicsDerivativesAtKeypoints + WorkerComputeDerivatives
 // (src/Optimiser/Optimiser.cpp:239-323) and the loop nest of Differentiator::DynamicsDerivatives
-// (src/Differentiator/Differentiator.cpp:8-462).  mj_stepSkip's stage reuse is an optimisation that does
-// not change results (a skipped stage would recompute identical values), so each world runs the full step.
+// (src/Differentiator/Differentiator.cpp:8-462).
+//
+// Stage reuse (the fork's mj_stepSkip, Differentiator.cpp:118,155 skip >= VEL for control columns, :253,276 skip >= POS
+// for velocity columns, :357,377 none for positions): the worlds of a key-point that do not perturb qpos share the
+// nominal world's position stage, the control worlds its velocity stage too, and both its factor of M + h D
+// (mj_EulerSkip's skipfactor).  A launch therefore runs in two phases over two compacted work lists:
+//   phase 0  nominal and position-perturbed worlds: full step; the nominal world stores what later stages read
+//            (xipos, rootcom, cinert, cdof, M, its L'DL factor, J, D, B, K-terms | qfrc_passive, qfrc_bias, aref |
+//            factor of M + h D) in the key-point's slot of the share buffer (HBM, L2-resident);
+//   phase 1  control and velocity worlds: load instead of recompute, then run only the stages mj_stepSkip would run.
+// The loaded values are the bits the world would have computed itself, so A / B are bit-identical to the
+// every-world-runs-everything form (tests/test_gpu_determinism.py).
 #include <cstdlib>
 
 #include "step_dyn.cuh"
@@ -34,8 +44,16 @@ struct FdArgs {
   int iterations;
   double tolerance;
   int ecap, pass;                   // constraint-row capacity of this pass; pass 1 redoes overflowed worlds only
-  int *list0, *list1;               // compacted world lists (gidx = row index * W + slot): all running / overflowed
-  int* counts;                      // [0] |list0|, [1] |list1|, [2] cursor of pass 0, [3] cursor of pass 1
+  int phase;                        // 0: nominal + position worlds (full step), 1: control + velocity worlds (stage reuse)
+  int *list0, *list1;               // compacted world lists of pass 0 / pass 1 (gidx = row index * W + slot): phase-0
+                                    // worlds fill a list from the front, phase-1 worlds from the back
+  long long list_cap;               // entries per list
+  int* counts;                      // [2 * pass + phase] list sizes, [4 + 2 * pass + phase] cursors
+  int row_lo, row_hi;               // row-index range of this chunk (the share buffer holds row_hi - row_lo slots)
+  double* share;                    // [row_hi - row_lo][share_stride]
+  int share_stride;
+  int share_on;                     // 0: every world runs the full step (phase 0), for A/B bit-identity checks
+  int lane_mode;                    // 1: the control / velocity worlds run in k_fd_dep_lanes (one world per lane)
   int blocksync;                    // Grp::bsync level of this launch (0 = warps run independently)
   int* wstatus;                     // [B][2] sticky per-trajectory warning bits (column 0 = FD worlds)
   int last;                         // no further pass re-runs the worlds that overflow in this one
@@ -81,20 +99,44 @@ __device__ inline bool fd_decode(const DM& dm, const FdArgs& a, long long gidx, 
 // list0, all others get status 0.  Sparse key-point rows leave most of the B*T*W candidates empty; compaction fills
 // every warp of k_fd_worlds with running worlds.
 __global__ void k_fd_plan(DM dm, FdArgs a) {
-  long long gidx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  long long total = (long long)a.nrows * a.W;
+  long long gidx = (long long)a.row_lo * a.W + (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  long long total = (long long)a.row_hi * a.W;
   bool run = false;
   FdWorld wd;
+  wd.kind = 0;
   if (gidx < total) {
     run = fd_decode(dm, a, gidx, wd);
     if (!run) a.status[(size_t)wd.row * a.W + wd.slot] = 0;
   }
-  unsigned bal = __ballot_sync(0xffffffffu, run);
+  const bool dep = run && a.share_on && (wd.kind == 1 || wd.kind == 2);
+  unsigned bal0 = __ballot_sync(0xffffffffu, run && !dep), bal1 = __ballot_sync(0xffffffffu, dep);
   int lane = threadIdx.x & 31;
-  int base = 0;
-  if (lane == 0 && bal) base = atomicAdd(&a.counts[0], __popc(bal));
-  base = __shfl_sync(0xffffffffu, base, 0);
-  if (run) a.list0[base + __popc(bal & ((1u << lane) - 1u))] = (int)gidx;
+  int base0 = 0, base1 = 0;
+  if (lane == 0 && bal0) base0 = atomicAdd(&a.counts[0], __popc(bal0));
+  if (lane == 0 && bal1) base1 = atomicAdd(&a.counts[1], __popc(bal1));
+  base0 = __shfl_sync(0xffffffffu, base0, 0);
+  base1 = __shfl_sync(0xffffffffu, base1, 0);
+  unsigned below = (1u << lane) - 1u;
+  if (run && !dep) a.list0[base0 + __popc(bal0 & below)] = (int)gidx;
+  if (dep) a.list0[a.list_cap - 1 - (base1 + __popc(bal1 & below))] = (int)gidx;
+}
+
+// share-buffer slot of one key-point (doubles): what the nominal world hands to the worlds that reuse its stages
+struct ShareLayout {
+  int hdr, M, LD, LDinv, J, D, aref, fpas, fbias, Bc, kterm, xipos, rootcom, cinert, cdof, LDe, Hinv, total;
+  __host__ __device__ ShareLayout(const DM& m) {
+    int nv = m.nv, nb = m.nbody, ne = m.maxefc, p = 0;
+    auto take = [&](int n) { int r = p; p += n; return r; };
+    hdr = take(4); M = take(nv * nv); LD = take(nv * nv); LDinv = take(nv); J = take(ne * nv); D = take(ne); aref = take(ne);
+    fpas = take(nv); fbias = take(nv); Bc = take(ne); kterm = take(ne); xipos = take(3 * nb); rootcom = take(3 * nb);
+    cinert = take(10 * nb); cdof = take(6 * nv); LDe = take(nv * nv); Hinv = take(nv);
+    total = (p + 1) & ~1;
+  }
+};
+
+template <int G>
+__device__ __forceinline__ void cp_lanes(double* __restrict__ dst, const double* __restrict__ src, int n, int gl) {
+  for (int i = gl; i < n; i += G) dst[i] = src[i];
 }
 
 // Persistent kernel: every warp fetches GPW worlds at a time from the compacted list (dynamic cursor), one group of
@@ -108,16 +150,17 @@ __global__ void __launch_bounds__(G == 16 ? 384 : 128, G == 16 ? 1 : 2) k_fd_wor
   int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   int slot_s = warp * GPW + lane / G;
   const int* list = a.pass == 0 ? a.list0 : a.list1;
-  const int count = a.counts[a.pass];
-  int* cursor = &a.counts[2 + a.pass];
+  const int count = a.counts[2 * a.pass + a.phase];
+  int* cursor = &a.counts[4 + 2 * a.pass + a.phase];
   int nq = dm.nq, nv = dm.nv;
+  const ShareLayout L(dm);
   tk::WS w;
   tk::ws_init(w, smem + (size_t)slot_s * wsd, dm, a.ecap, G);
   __shared__ int s_base;
   for (;;) {
     int base = 0;
     if (a.blocksync) {
-      // the whole block fetches one chunk of worlds and walks the two halves of the step together
+      // the whole block fetches one chunk of worlds and walks the stages of the step together
       __syncthreads();
       if (threadIdx.x == 0) s_base = atomicAdd(cursor, GPW * (int)(blockDim.x >> 5));
       __syncthreads();
@@ -142,7 +185,7 @@ __global__ void __launch_bounds__(G == 16 ? 384 : 128, G == 16 ? 1 : 2) k_fd_wor
     double time = 0.0;
     int st = 0;
     if (run) {
-      gidx = list[li];
+      gidx = list[a.phase == 0 ? li : a.list_cap - 1 - li];
       fd_decode(dm, a, gidx, wd);
       const double* s = a.snap + ((size_t)wd.b * (a.T + 1) + wd.t) * a.SD;
       time = s[0];
@@ -179,7 +222,78 @@ __global__ void __launch_bounds__(G == 16 ? 384 : 128, G == 16 ? 1 : 2) k_fd_wor
         }
       }
       g.sync();
-      tk::step(dm, w, g, a.iterations, a.tolerance, time, st);
+      double* sh = a.share + (size_t)((int)(gidx / a.W) - a.row_lo) * a.share_stride;
+      w.work = 0;
+      if (a.phase == 0) {
+        // full step (mj_step / mj_stepSkip(mjSTAGE_NONE)); the nominal world publishes its stages
+        tk::step_position(dm, w, g, st);
+        tk::step_velocity(dm, w, g);
+        const bool pub = wd.kind == 0 && real;
+        if (pub) {
+          const int ne = w.nefc;
+          if (g.gl == 0) { sh[L.hdr] = (double)ne; sh[L.hdr + 1] = 0.0; }
+          cp_lanes<G>(sh + L.M, w.M, nv * nv, g.gl); cp_lanes<G>(sh + L.LD, w.LD, nv * nv, g.gl);
+          cp_lanes<G>(sh + L.LDinv, w.LDinv, nv, g.gl); cp_lanes<G>(sh + L.J, w.J, ne * nv, g.gl);
+          cp_lanes<G>(sh + L.D, w.efc_D, ne, g.gl); cp_lanes<G>(sh + L.aref, w.efc_aref, ne, g.gl);
+          cp_lanes<G>(sh + L.fpas, w.frc_passive, nv, g.gl); cp_lanes<G>(sh + L.fbias, w.frc_bias, nv, g.gl);
+          cp_lanes<G>(sh + L.Bc, w.efc_B, ne, g.gl); cp_lanes<G>(sh + L.kterm, w.efc_kterm, ne, g.gl);
+          cp_lanes<G>(sh + L.xipos, w.xipos, 3 * dm.nbody, g.gl); cp_lanes<G>(sh + L.rootcom, w.rootcom, 3 * dm.nbody, g.gl);
+          cp_lanes<G>(sh + L.cinert, w.cinert, 10 * dm.nbody, g.gl); cp_lanes<G>(sh + L.cdof, w.cdof, 6 * nv, g.gl);
+        }
+        g.phase();
+        tk::fwd_constraint(dm, w, g, a.iterations, a.tolerance);
+        g.phase();
+        tk::check_qacc(dm, w, g, st);
+        tk::euler_factor(dm, w, g);
+        if (pub) {
+          g.sync();
+          cp_lanes<G>(sh + L.LDe, w.LD, nv * nv, g.gl); cp_lanes<G>(sh + L.Hinv, w.Hinv, nv, g.gl);
+          // status bits of the position / velocity stage travel with the slot (overflow: the dependants are redone too)
+          int bits = 0;
+          for (int k = 0; k < 6; k++) if (g.any((st >> k) & 1)) bits |= (1 << k);
+          if (g.gl == 0) {
+            sh[L.hdr + 1] = (double)(bits & (tk::ST_OVERFLOW | tk::ST_UNSUPPORTED | tk::ST_BAD_QPOS));
+            sh[L.hdr + 2] = (double)w.work;  // line-search evaluations of the nominal world: its neighbours will need as many
+          }
+        }
+        tk::euler_advance(dm, w, g, time);
+      } else {
+        // mj_stepSkip(mjSTAGE_POS) for velocity worlds, mj_stepSkip(mjSTAGE_VEL) for control worlds
+        const int ne = (int)sh[L.hdr];
+        st |= (int)sh[L.hdr + 1];
+        w.nefc = ne;
+        for (int i = g.gl; i < nq; i += G) if (tk::bad_value(w.qpos[i])) st |= tk::ST_BAD_QPOS;
+        for (int i = g.gl; i < nv; i += G) if (tk::bad_value(w.qvel[i])) st |= tk::ST_BAD_QVEL;
+        cp_lanes<G>(w.M, sh + L.M, nv * nv, g.gl); cp_lanes<G>(w.LD, sh + L.LD, nv * nv, g.gl);
+        cp_lanes<G>(w.LDinv, sh + L.LDinv, nv, g.gl); cp_lanes<G>(w.J, sh + L.J, ne * nv, g.gl);
+        cp_lanes<G>(w.efc_D, sh + L.D, ne, g.gl);
+        if (wd.kind == 1) {
+          cp_lanes<G>(w.efc_aref, sh + L.aref, ne, g.gl);
+          cp_lanes<G>(w.frc_passive, sh + L.fpas, nv, g.gl); cp_lanes<G>(w.frc_bias, sh + L.fbias, nv, g.gl);
+        } else {
+          cp_lanes<G>(w.efc_B, sh + L.Bc, ne, g.gl); cp_lanes<G>(w.efc_kterm, sh + L.kterm, ne, g.gl);
+          cp_lanes<G>(w.xipos, sh + L.xipos, 3 * dm.nbody, g.gl); cp_lanes<G>(w.rootcom, sh + L.rootcom, 3 * dm.nbody, g.gl);
+          cp_lanes<G>(w.cinert, sh + L.cinert, 10 * dm.nbody, g.gl); cp_lanes<G>(w.cdof, sh + L.cdof, 6 * nv, g.gl);
+        }
+        g.sync();
+        g.phase();
+        if (wd.kind == 2) {
+          tk::com_vel(dm, w, g);
+          tk::passive_and_bias(dm, w, g);
+        }
+        g.phase();
+        if (wd.kind == 2) tk::reference_constraint(dm, w, g);
+        tk::actuation_acceleration(dm, w, g);
+        g.phase();
+        tk::fwd_constraint(dm, w, g, a.iterations, a.tolerance);
+        g.phase();
+        tk::check_qacc(dm, w, g, st);
+        if (dm.any_damping) {  // mj_EulerSkip(skipfactor = 1): the nominal world's factor of M + h D
+          cp_lanes<G>(w.LD, sh + L.LDe, nv * nv, g.gl); cp_lanes<G>(w.Hinv, sh + L.Hinv, nv, g.gl);
+          g.sync();
+        }
+        tk::euler_advance(dm, w, g, time);
+      }
     }
     if (run && real) {
       double* o = a.fd_out + ((size_t)wd.row * a.W + wd.slot) * (nq + nv);
@@ -189,7 +303,10 @@ __global__ void __launch_bounds__(G == 16 ? 384 : 128, G == 16 ? 1 : 2) k_fd_wor
       for (int k = 0; k < 6; k++) if (g.any((st >> k) & 1)) bits |= (1 << k);
       if (g.gl == 0) {
         a.status[(size_t)wd.row * a.W + wd.slot] = bits | (1 << 30);
-        if (a.pass == 0 && (bits & tk::ST_OVERFLOW)) a.list1[atomicAdd(&a.counts[1], 1)] = (int)gidx;
+        if (a.pass == 0 && (bits & tk::ST_OVERFLOW)) {
+          int k = atomicAdd(&a.counts[2 + a.phase], 1);
+          a.list1[a.phase == 0 ? k : a.list_cap - 1 - k] = (int)gidx;
+        }
         int keep = a.last ? bits : (bits & ~tk::ST_OVERFLOW);
         if (keep) atomicOr(&a.wstatus[2 * wd.b], keep);
       }
@@ -198,6 +315,10 @@ __global__ void __launch_bounds__(G == 16 ? 384 : 128, G == 16 ? 1 : 2) k_fd_wor
     __syncwarp();
   }
 }
+
+}  // namespace tokp
+#include "fd_lanes.cuh"
+namespace tokp {
 
 // (q2 - q1)/h on the configuration manifold for one dof (mj_differentiatePos restricted to a dof)
 __device__ inline double diff_pos_dof(const DM& dm, const double* q1, const double* q2, double h, int d) {
@@ -218,10 +339,10 @@ __global__ void k_fd_assemble(DM dm, FdArgs a, double* __restrict__ A, double* _
   int nx = 2 * a.n;
   long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   long long per_row = (long long)(a.m + 2 * a.n) * nx;
-  long long total = (long long)a.nrows * per_row;
+  long long total = (long long)(a.row_hi - a.row_lo) * per_row;
   if (gid >= total) return;
-  int rowi = (int)(gid / per_row);
-  int rem = (int)(gid - (long long)rowi * per_row);
+  int rowi = a.row_lo + (int)(gid / per_row);
+  int rem = (int)(gid - (long long)(rowi - a.row_lo) * per_row);
   int c = rem / nx, j = rem - c * nx;
   int row = a.rows ? a.rows[rowi] : rowi;
   int kind, col;
@@ -268,40 +389,93 @@ int launch_fd(tokp_traj* tr, const unsigned long long* mask, const int* rows, in
     double tmp[3];
     tokp_fd_kernel_ms(tr, tmp);
   }
+  // share buffer: one slot per key-point row of a chunk, at most ~1 GiB (larger launches run in row chunks)
+  const ShareLayout L(dm);
+  if (!tr->fd_share) {
+    long long want = (long long)tr->B * tr->T;
+    long long cap = (1ll << 30) / ((long long)L.total * 8);
+    if (cap < 1) cap = 1;
+    tr->fd_share_rows = (int)(want < cap ? want : cap);
+    TOKP_CUDA(cudaMalloc(&tr->fd_share, (size_t)tr->fd_share_rows * L.total * 8));
+  }
   a.list0 = tr->fd_list0; a.list1 = tr->fd_list1; a.counts = tr->fd_counts; a.wstatus = tr->wstatus;
-  a.ecap = 0; a.pass = 0;
-  TOKP_CUDA(cudaMemsetAsync(tr->fd_counts, 0, 4 * sizeof(int), tr->stream));
-  k_fd_plan<<<(int)((worlds + 255) / 256), 256, 0, tr->stream>>>(dm, a);
-  g_launches++;
-  tr->counters[2] += 1;
+  a.list_cap = (long long)tr->B * tr->T * tr->W;
+  a.share = tr->fd_share; a.share_stride = L.total; a.share_on = tr->fd_stage_sharing;
+  // lane-per-world kernel for the stage-reusing worlds: small hinge / slide models with an nv-specialised instantiation
+  a.lane_mode = (a.share_on && tr->fd_lanes && dm.lane_ok && 2 * (tr->m + tr->n) <= 64) ? 1 : 0;
+  // block-synchronous walk of the step (see Grp::bsync): the warps of a block stay in the same region of the step
+  // code, which is several times the instruction cache.  TOKP_FD_BLOCKSYNC=0 lets the warps run independently.
+  a.blocksync = tr->fd_blocksync;
   cudaEventRecord(tr->ev2, tr->stream);
-  for (int pass = 0; pass < (needs_redo_pass(dm) ? 2 : 1); pass++) {
-    LaunchPlan lp;
-    int rc = plan_launch(dm, G, pass, &lp);
-    if (rc) return rc;
-    a.ecap = lp.ecap; a.pass = pass; a.last = (pass == 1 || !needs_redo_pass(dm)) ? 1 : 0;
-    // persistent grid: as many blocks as stay resident, never more than the worlds need
-    long long need = (worlds + lp.worlds_per_block - 1) / lp.worlds_per_block;
-    int blocks = (int)(need < (long long)lp.resident_blocks ? need : (long long)lp.resident_blocks);
-    // block-synchronous walk of the step (see Grp::bsync): the warps of a block stay in the same region of the step
-    // code, which is several times the instruction cache.  TOKP_FD_BLOCKSYNC=0 lets the warps run independently.
-    a.blocksync = 2;
-    if (const char* e = getenv("TOKP_FD_BLOCKSYNC")) a.blocksync = atoi(e) < 0 ? 0 : (atoi(e) > 3 ? 3 : atoi(e));
+  for (int row_lo = 0; row_lo < nrows; row_lo += tr->fd_share_rows) {
+    a.row_lo = row_lo;
+    a.row_hi = row_lo + tr->fd_share_rows < nrows ? row_lo + tr->fd_share_rows : nrows;
+    long long cw = (long long)(a.row_hi - a.row_lo) * tr->W;
+    a.ecap = 0; a.pass = 0; a.phase = 0; a.last = 0;
+    TOKP_CUDA(cudaMemsetAsync(tr->fd_counts, 0, 8 * sizeof(int), tr->stream));
+    k_fd_plan<<<(int)((cw + 255) / 256), 256, 0, tr->stream>>>(dm, a);
+    g_launches++;
+    tr->counters[2] += 1;
+
+    for (int pass = 0; pass < (needs_redo_pass(dm) ? 2 : 1); pass++) {
+      LaunchPlan lp;
+      int rc = plan_launch(dm, G, pass, &lp);
+      if (rc) return rc;
+      a.ecap = lp.ecap; a.pass = pass; a.last = (pass == 1 || !needs_redo_pass(dm)) ? 1 : 0;
+      // persistent grid: as many blocks as stay resident, never more than the worlds need
+      long long need = (cw + lp.worlds_per_block - 1) / lp.worlds_per_block;
+      int blocks = (int)(need < (long long)lp.resident_blocks ? need : (long long)lp.resident_blocks);
+      for (int phase = 0; phase < (a.lane_mode ? 1 : 2); phase++) {
+        a.phase = phase;
 #define LAUNCH(GG, NN)                                                                                               \
   TOKP_CUDA(cudaFuncSetAttribute(k_fd_worlds<GG, NN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lp.smem));   \
   k_fd_worlds<GG, NN><<<blocks, lp.warps * 32, lp.smem, tr->stream>>>(dm, a, lp.wsd);
-    TOKP_DISPATCH(G, dm.nv, LAUNCH)
+        TOKP_DISPATCH(G, dm.spec_nv, LAUNCH)
 #undef LAUNCH
+        g_launches++;
+        tr->counters[2] += 1;
+      }
+    }
+    if (a.lane_mode) {
+      // after every pass of the full-step worlds: the nominal worlds' slots are final.  Bin the stage-reusing worlds
+      // by constraint-row count, then run the light bins (small workspace, more warps per SM) and the heavy ones.
+      LaneArgs la;
+      la.counts = tr->fd_counts + 8;  // [0, kLaneBins) sizes | [kLaneBins, 2 kLaneBins) fill counters | 2 cursors
+      la.list = tr->fd_list1 + (a.list_cap - cw);  // the redo list only grows from the front: its back is free
+      la.necap = 0; la.heavy = 0;
+      TOKP_CUDA(cudaMemsetAsync(la.counts, 0, (2 * kLaneBins + 2) * sizeof(int), tr->stream));
+      k_fd_bin<<<(int)((cw + 255) / 256), 256, 0, tr->stream>>>(dm, a, la, nullptr, 0);
+      k_fd_bin<<<(int)((cw + 255) / 256), 256, 0, tr->stream>>>(dm, a, la, tr->fd_list1 + (a.list_cap - cw), 1);
+      g_launches += 2;
+      tr->counters[2] += 2;
+      a.pass = 0; a.phase = 1; a.last = 1;
+      for (int heavy = 0; heavy < 2; heavy++) {
+        la.heavy = heavy;
+        la.necap = heavy ? dm.maxefc : (dm.maxefc < kLaneLightRows ? dm.maxefc : kLaneLightRows);
+        if (heavy && dm.maxefc <= kLaneLightRows) break;
+        const LanePlan lpn(dm, la.necap);
+        size_t lsmem = (size_t)lpn.total * 8;
+        int per_sm = (int)((227 * 1024) / (lsmem + 1024));
+        if (per_sm < 1) { set_error("lane workspace does not fit shared memory"); return TOKP_ERR_UNSUPPORTED; }
+        long long lneed = (cw + 31) / 32;
+        int lblocks = (int)(lneed < (long long)per_sm * tr->sm_count ? lneed : (long long)per_sm * tr->sm_count);
+#define LAUNCH_LANES(NN)                                                                                              \
+  TOKP_CUDA(cudaFuncSetAttribute(k_fd_dep_lanes<NN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lsmem));       \
+  k_fd_dep_lanes<NN><<<lblocks, 32, lsmem, tr->stream>>>(dm, a, la);
+        if (dm.spec_nv == 9) { LAUNCH_LANES(9) } else { LAUNCH_LANES(2) }
+#undef LAUNCH_LANES
+        g_launches++;
+        tr->counters[2] += 1;
+      }
+    }
+    long long tot = (long long)(a.row_hi - a.row_lo) * (tr->m + 2 * tr->n) * tr->nx;
+    k_fd_assemble<<<(int)((tot + 255) / 256), 256, 0, tr->stream>>>(dm, a, tr->A, tr->Bm);
     g_launches++;
     tr->counters[2] += 1;
   }
   cudaEventRecord(tr->ev3, tr->stream);
   tr->fd_timed = true;
-  long long tot = (long long)nrows * (tr->m + 2 * tr->n) * tr->nx;
-  k_fd_assemble<<<(int)((tot + 255) / 256), 256, 0, tr->stream>>>(dm, a, tr->A, tr->Bm);
-  g_launches++;
   TOKP_CUDA(cudaGetLastError());
-  tr->counters[2] += 1;
   return TOKP_OK;
 }
 
@@ -318,7 +492,7 @@ void adapt_fast_capacity(tokp_traj* tr, long long worlds, long long overflowed) 
 int update_fd_counters(tokp_traj* tr) {
   std::vector<unsigned long long> hm((size_t)tr->B * tr->T);
   TOKP_CUDA(cudaMemcpyAsync(hm.data(), tr->kp_mask, hm.size() * 8, cudaMemcpyDeviceToHost, tr->stream));
-  int hc[4] = {0, 0, 0, 0};
+  int hc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   TOKP_CUDA(cudaMemcpyAsync(hc, tr->fd_counts, sizeof(hc), cudaMemcpyDeviceToHost, tr->stream));
   TOKP_CUDA(cudaStreamSynchronize(tr->stream));
   long long worlds = 0, cols = 0;
@@ -330,8 +504,9 @@ int update_fd_counters(tokp_traj* tr) {
     cols += c;
   }
   tr->counters[0] = worlds;
-  tr->counters[3] = hc[1];  // worlds that overflowed the fast constraint-row capacity and were re-run
-  adapt_fast_capacity(tr, worlds, hc[1]);
+  // worlds that overflowed the fast constraint-row capacity and were re-run (of the last row chunk)
+  tr->counters[3] = hc[2] + hc[3];
+  adapt_fast_capacity(tr, hc[0] + hc[1], hc[2] + hc[3]);
   tr->counters[1] = (int64_t)((double)cols / tr->n * 1e6);
   return TOKP_OK;
 }

@@ -214,10 +214,10 @@ static int keypoints_iterative(tokp_traj* tr) {
     k_iter_error<<<((int)check.size() + 127) / 128, 128, 0, tr->stream>>>(tr->A, d_seg, (int)check.size(), T, n, tr->task.iter_thr, d_good);
     g_launches++;
     cudaMemcpyAsync(hgood.data(), d_good, hgood.size() * 4, cudaMemcpyDeviceToHost, tr->stream);
-    int hc[4] = {0, 0, 0, 0};
+    int hc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     if (!rows.empty()) cudaMemcpyAsync(hc, tr->fd_counts, sizeof(hc), cudaMemcpyDeviceToHost, tr->stream);
     if (cudaStreamSynchronize(tr->stream) != cudaSuccess) { set_error("iterative_error: CUDA failure"); rc = TOKP_ERR_CUDA; break; }
-    if (!rows.empty()) { adapt_fast_capacity(tr, hc[0], hc[1]); tr->counters[3] += hc[1]; }
+    if (!rows.empty()) { adapt_fast_capacity(tr, hc[0] + hc[1], hc[2] + hc[3]); tr->counters[3] += hc[2] + hc[3]; }
     std::vector<Seg> next;
     for (size_t i = 0; i < check.size(); i++)
       if (!hgood[i]) {

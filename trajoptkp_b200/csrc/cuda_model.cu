@@ -144,9 +144,18 @@ int ensure_device_model(const tokp_model* mc, const DM** out) {
   dm.timestep = h.opt_real[0];
   dm.gravity[0] = h.opt_real[1]; dm.gravity[1] = h.opt_real[2]; dm.gravity[2] = h.opt_real[3];
   dm.tolerance = h.opt_real[4]; dm.ls_tolerance = h.opt_real[5]; dm.meaninertia = h.opt_real[7];
+  // the nv-specialised instantiations (TOKP_DISPATCH) compile the cylinder / mesh / convex colliders out: only models
+  // whose every pair is plane-{sphere, capsule, box} may use them, whatever their nv
+  dm.spec_nv = dm.nv;
+  for (size_t p = 0; p < h.pair_geom1.size(); p++) {
+    int t1 = h.geom_type[h.pair_geom1[p]], t2 = h.geom_type[h.pair_geom2[p]];
+    if (!(t1 == GEOM_PLANE && (t2 == GEOM_SPHERE || t2 == GEOM_CAPSULE || t2 == GEOM_BOX))) dm.spec_nv = 0;
+  }
   dm.any_damping = 0; dm.any_gravcomp = 0;
   for (double v : h.dof_damping) if (v > 0) dm.any_damping = 1;
   for (double v : h.body_gravcomp) if (v != 0) dm.any_gravcomp = 1;
+  dm.lane_ok = (dm.spec_nv == 2 || dm.spec_nv == 9) && !dm.any_gravcomp && dm.maxefc <= 64;
+  for (int jt : h.jnt_type) if (jt != JNT_HINGE && jt != JNT_SLIDE) dm.lane_ok = 0;
   m->dev = d;
   *out = &m->dev->dm;
   return TOKP_OK;
@@ -246,7 +255,7 @@ static int step_worlds_impl(const tokp_model* m, const double* snapshots_in, dou
   TOKP_CUDA(cudaFuncSetAttribute(k_step_worlds<GG, NN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lp.smem));      \
   k_step_worlds<GG, NN><<<blocks, lp.warps * 32, lp.smem>>>(dm, d_in, d_out, d_st, count, nsteps, iters, tol, S, lp.wsd, \
                                                         lp.ecap, pass, forward_after);
-    TOKP_DISPATCH(G, dm.nv, LAUNCH)
+    TOKP_DISPATCH(G, dm.spec_nv, LAUNCH)
 #undef LAUNCH
     g_launches++;
   }

@@ -182,7 +182,7 @@ int launch_rollout(tokp_traj* tr, int mode, const double* d_Uin, const double* d
 #define LAUNCH(GG, NN)                                                                                              \
   TOKP_CUDA(cudaFuncSetAttribute(k_rollout<GG, NN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lp.smem));    \
   k_rollout<GG, NN><<<blocks, warps * 32, lp.smem, tr->stream>>>(dm, a, lp.wsd);
-    TOKP_DISPATCH(G, dm.nv, LAUNCH)
+    TOKP_DISPATCH(G, dm.spec_nv, LAUNCH)
 #undef LAUNCH
     g_launches++;
   }

@@ -2,6 +2,7 @@
 // Mirrors the storage the reference keeps in Optimiser (include/Optimiser/Optimiser.h:194-211),
 // iLQR::Resize (src/Optimiser/iLQR.cpp:37-200) and MuJoCoHelper::saved_systems_state_list
 // (include/MuJoCoHelper.h:118-123), as flat [B][T(+1)][...] device arrays.
+#include <cstdlib>
 #include <cstring>
 
 #include "traj.h"
@@ -78,7 +79,7 @@ extern "C" int tokp_traj_create(const tokp_model* m, const tokp_task_desc* td, i
   size_t o_rflags = p.take((size_t)B * NA, 4);
   size_t o_l0 = p.take((size_t)B * T * tr->W, 4);
   size_t o_l1 = p.take((size_t)B * T * tr->W, 4);
-  size_t o_cnt = p.take(4, 4);
+  size_t o_cnt = p.take(256, 4);
   size_t o_s0 = p.take((size_t)B * tr->SD, 8);
   size_t o_u0 = p.take((size_t)B * T * mm, 8);
   size_t o_tints = p.take((size_t)(2 * n + mm), 4);
@@ -128,6 +129,12 @@ extern "C" int tokp_traj_create(const tokp_model* m, const tokp_task_desc* td, i
   std::vector<double> tg((size_t)B * ntg);
   for (int b = 0; b < B; b++) std::memcpy(&tg[(size_t)b * ntg], td->resid_target, ntg * 8);
   cudaMemcpy(tr->target, tg.data(), tg.size() * 8, cudaMemcpyHostToDevice);
+  if (const char* e = getenv("TOKP_FD_BLOCKSYNC")) tr->fd_blocksync = atoi(e) < 0 ? 0 : (atoi(e) > 3 ? 3 : atoi(e));
+  {
+    int dev = 0, smc = 0;
+    cudaGetDevice(&dev);
+    if (cudaDeviceGetAttribute(&smc, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && smc > 0) tr->sm_count = smc;
+  }
   cudaStreamCreate(&tr->stream);
   cudaEventCreate(&tr->ev0);
   cudaEventCreate(&tr->ev1);
@@ -147,6 +154,7 @@ extern "C" void tokp_traj_destroy(tokp_traj* tr) {
   if (tr->ev2) cudaEventDestroy(tr->ev2);
   if (tr->ev3) cudaEventDestroy(tr->ev3);
   if (tr->arena) cudaFree(tr->arena);
+  if (tr->fd_share) cudaFree(tr->fd_share);
   delete tr;
 }
 
@@ -164,6 +172,17 @@ extern "C" int tokp_traj_set_keypoint_method(tokp_traj* tr, int kp_method, int m
   if (jerk_thr) TOKP_CUDA(cudaMemcpy((void*)tr->task.jerk_thr, jerk_thr, tr->n * 8, cudaMemcpyHostToDevice));
   if (vel_thr) TOKP_CUDA(cudaMemcpy((void*)tr->task.vel_thr, vel_thr, tr->n * 8, cudaMemcpyHostToDevice));
   return TOKP_OK;
+}
+
+// tuning / test switches of a trajectory batch
+extern "C" int tokp_traj_set_option(tokp_traj* tr, const char* name, int value) {
+  if (!tr || !name) { set_error("tokp_traj_set_option: bad argument"); return TOKP_ERR_ARG; }
+  std::string nm(name);
+  if (nm == "fd_stage_sharing") { tr->fd_stage_sharing = value ? 1 : 0; return TOKP_OK; }
+  if (nm == "fd_lanes") { tr->fd_lanes = value ? 1 : 0; return TOKP_OK; }
+  if (nm == "fd_blocksync") { tr->fd_blocksync = value < 0 ? 0 : (value > 3 ? 3 : value); return TOKP_OK; }
+  set_error("tokp_traj_set_option: unknown option " + nm);
+  return TOKP_ERR_ARG;
 }
 
 // Per-trajectory step warnings (the mjWARN_* analogues): out[b][0] = OR over every FD world of trajectory b since the

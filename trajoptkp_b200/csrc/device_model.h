@@ -7,6 +7,10 @@ struct DM {
   int nq, nv, nu, nbody, njnt, ngeom, npair, maxcontact, maxefc, treedepth;
   int iterations, ls_iterations;
   int any_damping, any_gravcomp;
+  int spec_nv;    // nv when the model may run a kernel instantiation specialised on nv (those carry no cylinder / mesh /
+                  // convex-collider code: every collision pair must be plane-{sphere, capsule, box}); 0 = generic kernels
+  int lane_ok;    // the lane-per-world FD kernel applies: spec_nv in {2, 9}, hinge / slide joints only, no gravity
+                  // compensation, at most 64 constraint rows
   int fast_ecap;  // constraint-row capacity of the fast pass (0 = default 32); a trajectory batch raises its own copy
                   // when many of its FD worlds overflow (update_fd_counters)
   double timestep, gravity[3], tolerance, ls_tolerance, meaninertia;

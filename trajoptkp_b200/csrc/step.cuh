@@ -186,6 +186,7 @@ struct WS {
   double *cvel, *cacc, *cfrc;
   double *frc_passive, *frc_bias, *frc_act, *frc_smooth, *acc_smooth, *frc_con, *Ma, *Mv, *grad, *Mgrad, *search, *tmpv;
   int ncon, nefc, ecap;
+  int work;  // cost evaluations of the line searches of this world so far (a measure of its solver work)
 };
 
 __host__ __device__ inline int ws_imax(int a, int b) { return a > b ? a : b; }
@@ -238,7 +239,7 @@ TK_DEV void ws_init(WS& w, double* base, const DM& m, int ecap, int lanes) {
   p = u;
   w.H = take(nv * nv);
   w.jar = take(ne); w.jv = take(ne); w.efc_force = take(ne); w.quad = take(ws_quad_doubles(ne, lanes));
-  w.ncon = 0; w.nefc = 0; w.ecap = ecap;
+  w.ncon = 0; w.nefc = 0; w.ecap = ecap; w.work = 0;
 }
 
 }  // namespace tk

@@ -398,9 +398,10 @@ TK_DEV void fwd_constraint(const DM& m, WS& w, const Grp<G, NV>& g, int iteratio
   }
 }
 
-// mj_EulerSkip + mj_advance
+// mj_EulerSkip + mj_advance, in two parts so that a world which shares its position stage with another one can take
+// the factor of M + h D from it (mj_EulerSkip's skipfactor): euler_factor leaves the factor in w.LD / w.Hinv
 template <int G, int NV>
-TK_DEV void euler(const DM& m, WS& w, const Grp<G, NV>& g, double& time) {
+TK_DEV void euler_factor(const DM& m, WS& w, const Grp<G, NV>& g) {
   const int nv = NV ? NV : m.nv;
   double h = m.timestep;
   if (m.any_damping) {
@@ -410,6 +411,14 @@ TK_DEV void euler(const DM& m, WS& w, const Grp<G, NV>& g, double& time) {
     }
     g.sync();
     factor_ldl(m, w.H, w.LD, w.Hinv, g);
+  }
+}
+
+template <int G, int NV>
+TK_DEV void euler_advance(const DM& m, WS& w, const Grp<G, NV>& g, double& time) {
+  const int nv = NV ? NV : m.nv;
+  double h = m.timestep;
+  if (m.any_damping) {
     for (int i = g.gl; i < nv; i += G) w.tmpv[i] = w.frc_smooth[i] + w.frc_con[i];
     g.sync();
     solve_ldl(m, w.LD, w.Hinv, w.tmpv, g);
@@ -430,6 +439,12 @@ TK_DEV void euler(const DM& m, WS& w, const Grp<G, NV>& g, double& time) {
   }
   time += h;
   g.sync();
+}
+
+template <int G, int NV>
+TK_DEV void euler(const DM& m, WS& w, const Grp<G, NV>& g, double& time) {
+  euler_factor(m, w, g);
+  euler_advance(m, w, g, time);
 }
 
 // one full step (mj_step) in two halves, so that a kernel can put a block barrier between them (all warps of an SM
@@ -461,6 +476,13 @@ TK_DEV void step_velocity(const DM& m, WS& w, const Grp<G, NV>& g) {
   g.phase();
   reference_constraint(m, w, g);
   actuation_acceleration(m, w, g);
+}
+
+// the part of a step after the smooth acceleration, with the Euler factor either computed here (share = nullptr) or
+// handed in by the caller through `load_factor` (mj_EulerSkip(skipfactor = 1))
+template <int G, int NV>
+TK_DEV void check_qacc(const DM& m, const WS& w, const Grp<G, NV>& g, int& status) {
+  for (int i = g.gl; i < m.nv; i += G) if (bad_value(w.qacc[i])) status |= ST_BAD_QACC;
 }
 
 template <int G, int NV>

@@ -204,6 +204,7 @@ TK_DEV double primal_search(const DM& m, WS& w, const Grp<G, NV>& g, double gaus
       if (fixed_point_check && a_eval == p1.alpha) { result = p1.alpha; state = LS_DONE; }
     }
   }
+  w.work += lsiter;
   return result;
 }
 

@@ -95,7 +95,13 @@ struct tokp_traj {
   double *snap0_in, *U0_in;          // resident copies of the last host inputs of tokp_optimise ([B][SD], [B][T][m])
   int* bp_ok;         // [B]
   int *fd_list0, *fd_list1;  // [B*T*W] compacted FD world lists
-  int* fd_counts;     // [4]
+  int* fd_counts;     // [256] list sizes and cursors of the FD launch, bin sizes of the lane kernel (cuda_fd.cu, fd_lanes.cuh)
+  double* fd_share = nullptr;  // [fd_share_rows][ShareLayout.total] stage-sharing slots (own allocation, made on first use)
+  int fd_share_rows = 0;
+  int fd_stage_sharing = 1;    // mj_stepSkip-style stage reuse between the worlds of a key-point (tokp_traj_set_option)
+  int fd_lanes = 1;            // lane-per-world kernel for the stage-reusing FD worlds where the model allows it
+  int sm_count = 148;
+  int fd_blocksync = 2;        // Grp::bsync level of the FD kernels (TOKP_FD_BLOCKSYNC, read once at creation)
   int* roll_flags;    // [B][NA] rollout worlds that overflowed the fast constraint-row capacity
   int* task_ints;     // qpos_adr | dof_adr | ctrl_adr
   double* task_reals;

@@ -129,6 +129,16 @@ int tokp_step_worlds(const tokp_model* m, const double* snapshots_in, double* sn
 int tokp_forward_worlds(const tokp_model* m, const double* snapshots_in, double* snapshots_out, int count, int nsteps,
                         int solver_iterations, double solver_tolerance, int* status);
 
+/* tokp_step_worlds without any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  The kernel's scratch (input snapshots | output snapshots | status words) is a static device array of 4 MiB
+ * (TOKP_STATIC_SCRATCH_BYTES) that every GPU loading the library holds until exit; a call needs
+ * count * (2 * 8 * tokp_snapshot_size(m) + 4) bytes of it and returns TOKP_ERR_ARG beyond that (walker: 2614 worlds).
+ * The model must already be on the device (any earlier tokp_traj_create / tokp_step_worlds on it; TOKP_ERR_STATE
+ * otherwise).  Calls no cudaMalloc / cudaFree.  All calls share the array: calls that overlap on the GPU race. */
+int tokp_step_worlds_static(const tokp_model* m, const double* snapshots_in, double* snapshots_out, int count, int nsteps,
+                            int solver_iterations, double solver_tolerance, int* status);
+
 /* iLQR::RolloutTrajectory (iLQR.cpp:202-254) for all B trajectories: snapshot0[B][S], U[B][T][m] -> cost[B] */
 int tokp_rollout(tokp_traj* tr, const double* snapshot0, const double* U, double* cost);
 /* pandaReaching::CreateInitOptimisationControls (src/ModelTranslator/Reaching.cpp:269-296): gravity-compensation

@@ -70,6 +70,7 @@ def lib():
     L.tokp_model_body_pose.argtypes = [vp, _dp, C.c_int, _dp, _dp]
     L.tokp_step_worlds.argtypes = [vp, _dp, _dp, C.c_int, C.c_int, C.c_int, C.c_double, _ip]
     L.tokp_forward_worlds.argtypes = [vp, _dp, _dp, C.c_int, C.c_int, C.c_int, C.c_double, _ip]
+    L.tokp_step_worlds_static.argtypes = [vp, _dp, _dp, C.c_int, C.c_int, C.c_int, C.c_double, _ip]
     L.tokp_launch_count.restype = C.c_int64
     if hasattr(L, "tokp_traj_create"):
         L.tokp_traj_create.argtypes = [vp, C.POINTER(TaskDesc), C.c_int, C.c_int, C.POINTER(vp)]

@@ -4,6 +4,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
+#include <string>
 
 #include "step_dyn.cuh"
 #include "traj.h"
@@ -275,6 +276,97 @@ extern "C" int tokp_step_worlds(const tokp_model* m, const double* snapshots_in,
 extern "C" int tokp_forward_worlds(const tokp_model* m, const double* snapshots_in, double* snapshots_out, int count,
                                    int nsteps, int solver_iterations, double solver_tolerance, int* status) {
   return step_worlds_impl(m, snapshots_in, snapshots_out, count, nsteps, solver_iterations, solver_tolerance, status, 1);
+}
+
+// ---- tokp_step_worlds_static: the same batched stepping without any allocation -------------------------------------
+// No counterpart in the reference: added for callers that cannot call cudaMalloc
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The scratch tokp_step_worlds takes
+// from cudaMalloc (input snapshots | output snapshots | status words) lives here in a file-scope device array of
+// TOKP_STATIC_SCRATCH_BYTES = 4 MiB, which every GPU that loads the library holds until the process exits.  All calls
+// share the array and it keeps the last call's contents: calls that overlap on the GPU race (serialise them).
+#define TOKP_STATIC_SCRATCH_BYTES (4u << 20)
+static __device__ __align__(256) unsigned char g_static_scratch[TOKP_STATIC_SCRATCH_BYTES];
+
+namespace tokp {
+// In host code `g_static_scratch` is a host-side stand-in, not a device address: the address a kernel may use comes
+// from cudaGetSymbolAddress, looked up once per device with that device current.
+static int static_scratch_ptr(unsigned char** out) {
+  constexpr int kMaxDev = 64;
+  static unsigned char* ptrs[kMaxDev] = {nullptr};
+  static std::mutex mu;
+  int dev = -1;
+  TOKP_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDev) { set_error("tokp_step_worlds_static: device index out of range"); return TOKP_ERR_CUDA; }
+  std::lock_guard<std::mutex> lock(mu);
+  if (!ptrs[dev]) {
+    void* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+    if (e != cudaSuccess || !p) {
+      set_error(std::string("tokp_step_worlds_static: cudaGetSymbolAddress failed: ") + cudaGetErrorString(e));
+      return TOKP_ERR_CUDA;
+    }
+    ptrs[dev] = static_cast<unsigned char*>(p);
+  }
+  *out = ptrs[dev];
+  return TOKP_OK;
+}
+}  // namespace tokp
+
+extern "C" int tokp_step_worlds_static(const tokp_model* m, const double* snapshots_in, double* snapshots_out, int count,
+                                       int nsteps, int solver_iterations, double solver_tolerance, int* status) {
+  if (!m || !snapshots_in || !snapshots_out || count <= 0 || nsteps < 0) { set_error("tokp_step_worlds_static: bad argument"); return TOKP_ERR_ARG; }
+  // the model upload allocates: it must have happened already (tokp_traj_create or tokp_step_worlds on this model)
+  if (!m->dev) {
+    set_error("tokp_step_worlds_static: the model is not on the device yet (call tokp_traj_create or tokp_step_worlds once first; "
+              "this entry point allocates nothing)");
+    return TOKP_ERR_STATE;
+  }
+  const DM& dm = m->dev->dm;
+  const int S = tokp_snapshot_size(m);
+  const size_t snap_bytes = (size_t)count * S * sizeof(double);
+  const size_t need = 2 * snap_bytes + (size_t)count * sizeof(int);
+  if (need > TOKP_STATIC_SCRATCH_BYTES) {
+    set_error("tokp_step_worlds_static: " + std::to_string(count) + " worlds of " + std::to_string(S) + " doubles need " +
+              std::to_string(need) + " bytes of scratch, the static scratch holds " + std::to_string(TOKP_STATIC_SCRATCH_BYTES) +
+              " (at most " + std::to_string(TOKP_STATIC_SCRATCH_BYTES / (2 * (size_t)S * sizeof(double) + sizeof(int))) +
+              " worlds of this model per call; use tokp_step_worlds for larger batches)");
+    return TOKP_ERR_ARG;
+  }
+  for (int wi = 0; wi < count; wi++) {
+    const double* s = snapshots_in + (size_t)wi * S + 1 + dm.nq + 3 * dm.nv;
+    for (int i = 0; i < dm.nv + 6 * dm.nbody; i++)
+      if (s[i] != 0.0) { set_error("tokp_step_worlds_static: non-zero qfrc_applied/xfrc_applied unsupported"); return TOKP_ERR_UNSUPPORTED; }
+  }
+  unsigned char* base = nullptr;
+  int rc = static_scratch_ptr(&base);
+  if (rc) return rc;
+  double* d_in = reinterpret_cast<double*>(base);
+  double* d_out = d_in + (size_t)count * S;
+  int* d_st = reinterpret_cast<int*>(d_out + (size_t)count * S);
+  TOKP_CUDA(cudaMemcpy(d_in, snapshots_in, snap_bytes, cudaMemcpyHostToDevice));
+  // the array keeps the last call's contents: outputs and status words start from zero
+  TOKP_CUDA(cudaMemset(d_out, 0, snap_bytes + (size_t)count * sizeof(int)));
+  int iters = solver_iterations < 0 ? dm.iterations : solver_iterations;
+  double tol = solver_iterations < 0 ? dm.tolerance : solver_tolerance;
+  int G = lanes_for_model(dm);
+  for (int pass = 0; pass < (needs_redo_pass(dm) ? 2 : 1); pass++) {
+    LaunchPlan lp;
+    rc = plan_launch(dm, G, pass, &lp);
+    if (rc) return rc;
+    int blocks = (count + lp.worlds_per_block - 1) / lp.worlds_per_block;
+#define LAUNCH(GG, NN)                                                                                                    \
+  TOKP_CUDA(cudaFuncSetAttribute(k_step_worlds<GG, NN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lp.smem));      \
+  k_step_worlds<GG, NN><<<blocks, lp.warps * 32, lp.smem>>>(dm, d_in, d_out, d_st, count, nsteps, iters, tol, S, lp.wsd, \
+                                                        lp.ecap, pass, 0);
+    TOKP_DISPATCH(G, dm.spec_nv, LAUNCH)
+#undef LAUNCH
+    g_launches++;
+  }
+  TOKP_CUDA(cudaGetLastError());
+  TOKP_CUDA(cudaDeviceSynchronize());
+  TOKP_CUDA(cudaMemcpy(snapshots_out, d_out, snap_bytes, cudaMemcpyDeviceToHost));
+  if (status) TOKP_CUDA(cudaMemcpy(status, d_st, (size_t)count * sizeof(int), cudaMemcpyDeviceToHost));
+  return TOKP_OK;
 }
 
 extern "C" int64_t tokp_launch_count(void) { return g_launches.load(); }

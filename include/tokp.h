@@ -203,8 +203,9 @@ int tokp_traj_get(tokp_traj* tr, int b, const char* name, double* out, int cap);
 int tokp_traj_set(tokp_traj* tr, int b, const char* name, const double* in, int count);
 /* switches of a trajectory batch: "fd_stage_sharing" (default 1: the control / velocity worlds of a key-point reuse the
  * nominal world's position / velocity stage like mj_stepSkip, Differentiator.cpp:118,155,253,276; 0: every world runs
- * the full step - same A / B bit for bit), "fd_lanes" (default 1: those worlds run one per lane in a
- * key-point-per-warp kernel when the model is small and hinge / slide only; same A / B up to rounding), "fd_blocksync" (0..3, block-synchronous walk level of the FD kernels) */
+ * the full step - same A / B bit for bit), "fd_lanes" (small hinge / slide models: 1 = those worlds run one
+ * world per lane, 2 (default) = every FD world does and the group kernel only runs the position stage, 0 = off; same
+ * A / B up to rounding), "fd_blocksync" (0..3, block-synchronous walk level of the FD kernels) */
 int tokp_traj_set_option(tokp_traj* tr, const char* name, int value);
 /* Per-trajectory step warnings, the analogue of mjData.warning: out[B][2]; out[b][0] = OR over all FD worlds of
  * trajectory b since the last clear, out[b][1] = the same over rollout worlds.  Bits: 1 bad qpos, 2 bad qvel, 4 bad qacc,

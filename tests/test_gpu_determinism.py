@@ -110,11 +110,13 @@ def test_stage_sharing_changes_no_bit(built, name, B, T, kp):
     assert np.abs(A1).max() > 0
 
 
+@pytest.mark.parametrize("lanes", [1, 2])
 @pytest.mark.parametrize("name,B,T", [("walker_run", 12, 40), ("acrobot", 8, 50)])
-def test_lane_per_world_kernel_changes_only_rounding(built, name, B, T):
-    """The control / velocity worlds of small hinge / slide models run one world per lane (k_fd_dep_lanes): sequential
-    sums instead of butterfly reductions, so A / B agree with the group kernels up to rounding amplified by 1 / eps."""
-    A1, B1, w1 = _ab(name, B, T, 1, lanes=1)
+def test_lane_per_world_kernel_changes_only_rounding(built, name, B, T, lanes):
+    """The worlds of small hinge / slide models run one world per lane (k_fd_dep_lanes; fd_lanes 1: the control / velocity
+    worlds, 2: every world after a position-stage-only group kernel): sequential sums instead of butterfly reductions, so
+    A / B agree with the group kernels up to rounding amplified by 1 / eps."""
+    A1, B1, w1 = _ab(name, B, T, 1, lanes=lanes)
     A0, B0, w0 = _ab(name, B, T, 1, lanes=0)
     assert w1 == w0 and w1 > 0
     nx = A1.shape[-1] if A1.ndim == 3 else None

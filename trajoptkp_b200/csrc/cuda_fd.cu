@@ -53,7 +53,11 @@ struct FdArgs {
   double* share;                    // [row_hi - row_lo][share_stride]
   int share_stride;
   int share_on;                     // 0: every world runs the full step (phase 0), for A/B bit-identity checks
-  int lane_mode;                    // 1: the control / velocity worlds run in k_fd_dep_lanes (one world per lane)
+  int lane_mode;                    // 1: the control / velocity worlds run in k_fd_dep_lanes (one world per lane);
+                                    // 2: ALL worlds do: the group kernel only runs the position stage of the nominal and
+                                    //    position worlds (pos_only) and publishes one slot per world (slot = index in list0)
+  int pos_only;
+  int* rowslot;                     // [row_hi - row_lo] lane_mode 2: slot of the row's nominal world
   int blocksync;                    // Grp::bsync level of this launch (0 = warps run independently)
   int* wstatus;                     // [B][2] sticky per-trajectory warning bits (column 0 = FD worlds)
   int last;                         // no further pass re-runs the worlds that overflow in this one
@@ -117,7 +121,14 @@ __global__ void k_fd_plan(DM dm, FdArgs a) {
   base0 = __shfl_sync(0xffffffffu, base0, 0);
   base1 = __shfl_sync(0xffffffffu, base1, 0);
   unsigned below = (1u << lane) - 1u;
-  if (run && !dep) a.list0[base0 + __popc(bal0 & below)] = (int)gidx;
+  if (run && !dep) {
+    const int li = base0 + __popc(bal0 & below);
+    a.list0[li] = (int)gidx;
+    if (a.lane_mode == 2 && wd.kind == 0) {  // nominal world: its slot serves the whole key-point
+      a.rowslot[(int)(gidx / a.W) - a.row_lo] = li;
+      a.list1[atomicAdd(&a.counts[2], 1)] = li;
+    }
+  }
   if (dep) a.list0[a.list_cap - 1 - (base1 + __popc(bal1 & below))] = (int)gidx;
 }
 
@@ -222,9 +233,32 @@ __global__ void __launch_bounds__(G == 16 ? 384 : 128, G == 16 ? 1 : 2) k_fd_wor
         }
       }
       g.sync();
-      double* sh = a.share + (size_t)((int)(gidx / a.W) - a.row_lo) * a.share_stride;
+      double* sh = a.share + (size_t)(a.pos_only ? li : (int)(gidx / a.W) - a.row_lo) * a.share_stride;
       w.work = 0;
-      if (a.phase == 0) {
+      if (a.pos_only) {
+        // lane_mode 2: position stage only (mj_fwdPosition) + the factor of M + h D; everything after it runs one world
+        // per lane in k_fd_dep_lanes, which reads this world's slot
+        tk::step_position(dm, w, g, st);
+        if (real) {
+          const int ne = w.nefc;
+          if (g.gl == 0) { sh[L.hdr] = (double)ne; sh[L.hdr + 2] = 0.0; }
+          cp_lanes<G>(sh + L.M, w.M, nv * nv, g.gl); cp_lanes<G>(sh + L.LD, w.LD, nv * nv, g.gl);
+          cp_lanes<G>(sh + L.LDinv, w.LDinv, nv, g.gl); cp_lanes<G>(sh + L.J, w.J, ne * nv, g.gl);
+          cp_lanes<G>(sh + L.D, w.efc_D, ne, g.gl);
+          cp_lanes<G>(sh + L.Bc, w.efc_B, ne, g.gl); cp_lanes<G>(sh + L.kterm, w.efc_kterm, ne, g.gl);
+          cp_lanes<G>(sh + L.cinert, w.cinert, 10 * dm.nbody, g.gl); cp_lanes<G>(sh + L.cdof, w.cdof, 6 * nv, g.gl);
+        }
+        g.phase();
+        tk::euler_factor(dm, w, g);
+        g.sync();
+        if (real) {
+          cp_lanes<G>(sh + L.LDe, w.LD, nv * nv, g.gl); cp_lanes<G>(sh + L.Hinv, w.Hinv, nv, g.gl);
+          int bits = 0;
+          for (int k = 0; k < 6; k++) if (g.any((st >> k) & 1)) bits |= (1 << k);
+          if (g.gl == 0) sh[L.hdr + 1] = (double)bits;
+        }
+        g.sync();
+      } else if (a.phase == 0) {
         // full step (mj_step / mj_stepSkip(mjSTAGE_NONE)); the nominal world publishes its stages
         tk::step_position(dm, w, g, st);
         tk::step_velocity(dm, w, g);
@@ -295,7 +329,7 @@ __global__ void __launch_bounds__(G == 16 ? 384 : 128, G == 16 ? 1 : 2) k_fd_wor
         tk::euler_advance(dm, w, g, time);
       }
     }
-    if (run && real) {
+    if (run && real && !a.pos_only) {
       double* o = a.fd_out + ((size_t)wd.row * a.W + wd.slot) * (nq + nv);
       for (int i = g.gl; i < nq; i += G) o[i] = w.qpos[i];
       for (int i = g.gl; i < nv; i += G) o[nq + i] = w.qvel[i];
@@ -389,20 +423,34 @@ int launch_fd(tokp_traj* tr, const unsigned long long* mask, const int* rows, in
     double tmp[3];
     tokp_fd_kernel_ms(tr, tmp);
   }
-  // share buffer: one slot per key-point row of a chunk, at most ~1 GiB (larger launches run in row chunks)
+  // lane-per-world kernel for the worlds of small hinge / slide models with an nv-specialised instantiation:
+  // fd_lanes 1 = the stage-reusing (control / velocity) worlds, 2 = every world after a position-stage-only group kernel
+  const int lane_mode = (tr->fd_stage_sharing && tr->fd_lanes && dm.lane_ok && 2 * (tr->m + tr->n) <= 64) ? (tr->fd_lanes >= 2 ? 2 : 1) : 0;
+  // share buffer: one slot per key-point row of a chunk (lane_mode 2: one per nominal / position world, 1 + 2n per row),
+  // at most ~1 GiB (fd_share_gib, default 8 GiB, in lane_mode 2: 180 GB of HBM make that cheap, and one chunk has one set
+  // of kernel tails); larger launches run in row chunks
   const ShareLayout L(dm);
+  const int slots_per_row = lane_mode == 2 ? 1 + 2 * tr->n : 1;
+  if (tr->fd_share && tr->fd_share_slots_per_row != slots_per_row) {
+    TOKP_CUDA(cudaStreamSynchronize(tr->stream));
+    cudaFree(tr->fd_share);
+    tr->fd_share = nullptr;
+  }
   if (!tr->fd_share) {
     long long want = (long long)tr->B * tr->T;
-    long long cap = (1ll << 30) / ((long long)L.total * 8);
+    long long cap = ((long long)(lane_mode == 2 ? tr->fd_share_gib : 1) << 30) / ((long long)L.total * 8 * slots_per_row);
     if (cap < 1) cap = 1;
     tr->fd_share_rows = (int)(want < cap ? want : cap);
-    TOKP_CUDA(cudaMalloc(&tr->fd_share, (size_t)tr->fd_share_rows * L.total * 8));
+    tr->fd_share_slots_per_row = slots_per_row;
+    size_t share_bytes = (size_t)tr->fd_share_rows * slots_per_row * L.total * 8;
+    TOKP_CUDA(cudaMalloc(&tr->fd_share, share_bytes + (size_t)tr->fd_share_rows * sizeof(int)));
+    tr->fd_rowslot = reinterpret_cast<int*>(reinterpret_cast<unsigned char*>(tr->fd_share) + share_bytes);
   }
   a.list0 = tr->fd_list0; a.list1 = tr->fd_list1; a.counts = tr->fd_counts; a.wstatus = tr->wstatus;
   a.list_cap = (long long)tr->B * tr->T * tr->W;
   a.share = tr->fd_share; a.share_stride = L.total; a.share_on = tr->fd_stage_sharing;
-  // lane-per-world kernel for the stage-reusing worlds: small hinge / slide models with an nv-specialised instantiation
-  a.lane_mode = (a.share_on && tr->fd_lanes && dm.lane_ok && 2 * (tr->m + tr->n) <= 64) ? 1 : 0;
+  a.lane_mode = lane_mode; a.pos_only = 0; a.rowslot = tr->fd_rowslot;
+  tr->fd_last_lane_mode = lane_mode;
   // block-synchronous walk of the step (see Grp::bsync): the warps of a block stay in the same region of the step
   // code, which is several times the instruction cache.  TOKP_FD_BLOCKSYNC=0 lets the warps run independently.
   a.blocksync = tr->fd_blocksync;
@@ -417,11 +465,13 @@ int launch_fd(tokp_traj* tr, const unsigned long long* mask, const int* rows, in
     g_launches++;
     tr->counters[2] += 1;
 
-    for (int pass = 0; pass < (needs_redo_pass(dm) ? 2 : 1); pass++) {
+    for (int pass = 0; pass < (a.lane_mode == 2 ? 1 : (needs_redo_pass(dm) ? 2 : 1)); pass++) {
       LaunchPlan lp;
-      int rc = plan_launch(dm, G, pass, &lp);
+      // lane_mode 2: the group kernel runs the position stage only, once, at the full constraint-row capacity
+      int rc = plan_launch(dm, G, a.lane_mode == 2 ? 1 : pass, &lp);
       if (rc) return rc;
-      a.ecap = lp.ecap; a.pass = pass; a.last = (pass == 1 || !needs_redo_pass(dm)) ? 1 : 0;
+      a.ecap = lp.ecap; a.pass = pass; a.last = (pass == 1 || !needs_redo_pass(dm) || a.lane_mode == 2) ? 1 : 0;
+      a.pos_only = a.lane_mode == 2 ? 1 : 0;
       // persistent grid: as many blocks as stay resident, never more than the worlds need
       long long need = (cw + lp.worlds_per_block - 1) / lp.worlds_per_block;
       int blocks = (int)(need < (long long)lp.resident_blocks ? need : (long long)lp.resident_blocks);
@@ -437,22 +487,16 @@ int launch_fd(tokp_traj* tr, const unsigned long long* mask, const int* rows, in
       }
     }
     if (a.lane_mode) {
-      // after every pass of the full-step worlds: the nominal worlds' slots are final.  Bin the stage-reusing worlds
-      // by constraint-row count, then run the light bins (small workspace, more warps per SM) and the heavy ones.
+      // after every pass of the group kernel the slots are final.  lane_mode 2 first runs the nominal worlds (they
+      // leave their work count and velocity stage in the slot); then the remaining worlds are binned by constraint rows
+      // and the nominal world's work and run in the light bins (small workspace, more warps per SM) and the heavy ones.
       LaneArgs la;
       la.counts = tr->fd_counts + 8;  // [0, kLaneBins) sizes | [kLaneBins, 2 kLaneBins) fill counters | 2 cursors
-      la.list = tr->fd_list1 + (a.list_cap - cw);  // the redo list only grows from the front: its back is free
-      la.necap = 0; la.heavy = 0;
-      TOKP_CUDA(cudaMemsetAsync(la.counts, 0, (2 * kLaneBins + 2) * sizeof(int), tr->stream));
-      k_fd_bin<<<(int)((cw + 255) / 256), 256, 0, tr->stream>>>(dm, a, la, nullptr, 0);
-      k_fd_bin<<<(int)((cw + 255) / 256), 256, 0, tr->stream>>>(dm, a, la, tr->fd_list1 + (a.list_cap - cw), 1);
-      g_launches += 2;
-      tr->counters[2] += 2;
-      a.pass = 0; a.phase = 1; a.last = 1;
-      for (int heavy = 0; heavy < 2; heavy++) {
-        la.heavy = heavy;
-        la.necap = heavy ? dm.maxefc : (dm.maxefc < kLaneLightRows ? dm.maxefc : kLaneLightRows);
-        if (heavy && dm.maxefc <= kLaneLightRows) break;
+      la.list = tr->fd_list2;
+      la.necap = 0; la.heavy = 0; la.full = a.lane_mode == 2 ? 1 : 0; la.stage = 1;
+      a.pass = 0; a.phase = 1; a.last = 1; a.pos_only = 0;
+      auto launch_lanes = [&](int necap) -> int {
+        la.necap = necap;
         const LanePlan lpn(dm, la.necap);
         size_t lsmem = (size_t)lpn.total * 8;
         int per_sm = (int)((227 * 1024) / (lsmem + 1024));
@@ -466,6 +510,21 @@ int launch_fd(tokp_traj* tr, const unsigned long long* mask, const int* rows, in
 #undef LAUNCH_LANES
         g_launches++;
         tr->counters[2] += 1;
+        return TOKP_OK;
+      };
+      for (int stage = la.full ? 0 : 1; stage < 2; stage++) {
+        la.stage = stage;
+        TOKP_CUDA(cudaMemsetAsync(la.counts, 0, (2 * kLaneBins + 2) * sizeof(int), tr->stream));
+        k_fd_bin<<<(int)((cw + 255) / 256), 256, 0, tr->stream>>>(dm, a, la, nullptr, 0);
+        k_fd_bin<<<(int)((cw + 255) / 256), 256, 0, tr->stream>>>(dm, a, la, tr->fd_list2, 1);
+        g_launches += 2;
+        tr->counters[2] += 2;
+        for (int heavy = 0; heavy < 2; heavy++) {
+          la.heavy = heavy;
+          if (heavy && dm.maxefc <= kLaneLightRows) break;
+          int rc = launch_lanes(heavy ? dm.maxefc : (dm.maxefc < kLaneLightRows ? dm.maxefc : kLaneLightRows));
+          if (rc) return rc;
+        }
       }
     }
     long long tot = (long long)(a.row_hi - a.row_lo) * (tr->m + 2 * tr->n) * tr->nx;
@@ -505,8 +564,12 @@ int update_fd_counters(tokp_traj* tr) {
   }
   tr->counters[0] = worlds;
   // worlds that overflowed the fast constraint-row capacity and were re-run (of the last row chunk)
-  tr->counters[3] = hc[2] + hc[3];
-  adapt_fast_capacity(tr, hc[0] + hc[1], hc[2] + hc[3]);
+  if (tr->fd_last_lane_mode == 2) {  // no fast pass: counts[2] is the number of nominal worlds there
+    tr->counters[3] = 0;
+  } else {
+    tr->counters[3] = hc[2] + hc[3];
+    adapt_fast_capacity(tr, hc[0] + hc[1], hc[2] + hc[3]);
+  }
   tr->counters[1] = (int64_t)((double)cols / tr->n * 1e6);
   return TOKP_OK;
 }

@@ -217,7 +217,7 @@ static int keypoints_iterative(tokp_traj* tr) {
     int hc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     if (!rows.empty()) cudaMemcpyAsync(hc, tr->fd_counts, sizeof(hc), cudaMemcpyDeviceToHost, tr->stream);
     if (cudaStreamSynchronize(tr->stream) != cudaSuccess) { set_error("iterative_error: CUDA failure"); rc = TOKP_ERR_CUDA; break; }
-    if (!rows.empty()) { adapt_fast_capacity(tr, hc[0] + hc[1], hc[2] + hc[3]); tr->counters[3] += hc[2] + hc[3]; }
+    if (!rows.empty() && tr->fd_last_lane_mode != 2) { adapt_fast_capacity(tr, hc[0] + hc[1], hc[2] + hc[3]); tr->counters[3] += hc[2] + hc[3]; }
     std::vector<Seg> next;
     for (size_t i = 0; i < check.size(); i++)
       if (!hgood[i]) {

@@ -79,7 +79,8 @@ extern "C" int tokp_traj_create(const tokp_model* m, const tokp_task_desc* td, i
   size_t o_rflags = p.take((size_t)B * NA, 4);
   size_t o_l0 = p.take((size_t)B * T * tr->W, 4);
   size_t o_l1 = p.take((size_t)B * T * tr->W, 4);
-  size_t o_cnt = p.take(256, 4);
+  size_t o_l2 = p.take((size_t)B * T * tr->W, 4);
+  size_t o_cnt = p.take(1024, 4);
   size_t o_s0 = p.take((size_t)B * tr->SD, 8);
   size_t o_u0 = p.take((size_t)B * T * mm, 8);
   size_t o_tints = p.take((size_t)(2 * n + mm), 4);
@@ -102,6 +103,7 @@ extern "C" int tokp_traj_create(const tokp_model* m, const tokp_task_desc* td, i
   tr->bp_ok = (int*)(base + o_ok);
   tr->roll_flags = (int*)(base + o_rflags);
   tr->fd_list0 = (int*)(base + o_l0); tr->fd_list1 = (int*)(base + o_l1); tr->fd_counts = (int*)(base + o_cnt);
+  tr->fd_list2 = (int*)(base + o_l2);
   tr->snap0_in = (double*)(base + o_s0); tr->U0_in = (double*)(base + o_u0);
   tr->task_ints = (int*)(base + o_tints); tr->task_reals = (double*)(base + o_treals);
   // task tables
@@ -129,6 +131,7 @@ extern "C" int tokp_traj_create(const tokp_model* m, const tokp_task_desc* td, i
   std::vector<double> tg((size_t)B * ntg);
   for (int b = 0; b < B; b++) std::memcpy(&tg[(size_t)b * ntg], td->resid_target, ntg * 8);
   cudaMemcpy(tr->target, tg.data(), tg.size() * 8, cudaMemcpyHostToDevice);
+  if (const char* e = getenv("TOKP_FD_SHARE_GIB")) { int v = atoi(e); if (v >= 1 && v <= 64) tr->fd_share_gib = v; }
   if (const char* e = getenv("TOKP_FD_BLOCKSYNC")) tr->fd_blocksync = atoi(e) < 0 ? 0 : (atoi(e) > 3 ? 3 : atoi(e));
   {
     int dev = 0, smc = 0;
@@ -179,7 +182,7 @@ extern "C" int tokp_traj_set_option(tokp_traj* tr, const char* name, int value) 
   if (!tr || !name) { set_error("tokp_traj_set_option: bad argument"); return TOKP_ERR_ARG; }
   std::string nm(name);
   if (nm == "fd_stage_sharing") { tr->fd_stage_sharing = value ? 1 : 0; return TOKP_OK; }
-  if (nm == "fd_lanes") { tr->fd_lanes = value ? 1 : 0; return TOKP_OK; }
+  if (nm == "fd_lanes") { tr->fd_lanes = value < 0 ? 0 : (value > 2 ? 2 : value); return TOKP_OK; }
   if (nm == "fd_blocksync") { tr->fd_blocksync = value < 0 ? 0 : (value > 3 ? 3 : value); return TOKP_OK; }
   set_error("tokp_traj_set_option: unknown option " + nm);
   return TOKP_ERR_ARG;

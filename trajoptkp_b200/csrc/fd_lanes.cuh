@@ -45,17 +45,23 @@ struct LanePlan {
 // for its slowest lane - free-flight worlds (no solver), resting contacts (warm start already optimal: one iteration)
 // and contact transitions (all five iterations) differ by an order of magnitude.  The major key is the row class:
 // key-points with at most kLaneLightRows constraint rows run with a small workspace (more warps per SM).
-constexpr int kLaneWorkBins = 48, kLaneBins = 2 * kLaneWorkBins;
+// The minor key separates the control worlds (no velocity stage of their own) from the others.
+constexpr int kLaneWorkBins = 48, kLaneHalf = 2 * kLaneWorkBins, kLaneBins = 2 * kLaneHalf;
 constexpr int kLaneLightRows = 24;
-__host__ __device__ inline int lane_bin(int ne, int work) {
+__host__ __device__ inline int lane_bin(int ne, int work, int control) {
   int wbin = ne == 0 ? 0 : (work >= kLaneWorkBins - 1 ? kLaneWorkBins - 1 : 1 + work);
   if (wbin >= kLaneWorkBins) wbin = kLaneWorkBins - 1;
-  return (ne > kLaneLightRows ? kLaneWorkBins : 0) + wbin;
+  return (ne > kLaneLightRows ? kLaneHalf : 0) + 2 * wbin + (control ? 1 : 0);
 }
 
 struct LaneArgs {
   int necap;        // constraint-row capacity of the warp workspace
-  int heavy;        // 0: bins [0, kLaneWorkBins), 1: bins [kLaneWorkBins, kLaneBins)
+  int heavy;        // 0: bins [0, kLaneHalf), 1: bins [kLaneHalf, kLaneBins)
+  int full;         // 1: every world of the launch runs here after a position-stage-only group kernel (FdArgs::lane_mode 2);
+                    //    list entries are then e >= 0: index into the front of list0 (nominal / position world, own slot e),
+                    //    e < 0: stage-reusing world -1 - e of the back of list0 (slot of its key-point's nominal world)
+  int stage;        // full mode: 0 = the nominal worlds (FdArgs::list1 holds their list0 indices; sorted by their own
+                    // constraint-row count, the only thing known about them yet), 1 = all others
   const int* list;  // worlds sorted by bin (k_fd_bin_scatter)
   int* counts;      // [0, kLaneBins) bin sizes, [kLaneBins, 2 kLaneBins) fill counters of the scatter, then 2 cursors
 };
@@ -66,10 +72,31 @@ __global__ void k_fd_bin(DM dm, FdArgs a, LaneArgs la, int* __restrict__ out, in
   int li = blockIdx.x * blockDim.x + threadIdx.x;
   int count = a.counts[1];
   int bin = -1, gidx = 0;
-  if (li < count) {
+  if (la.full && la.stage == 0) {
+    if (li < a.counts[2]) {
+      gidx = a.list1[li];
+      const int ne = (int)a.share[(size_t)gidx * a.share_stride + L.hdr];
+      bin = lane_bin(ne, ne, 0);
+    }
+  } else if (la.full) {
+    // all worlds but the nominal ones: the front of list0 (position worlds: own row count, the nominal's work) and the back
+    const int n0 = a.counts[0];
+    if (li < n0 + count) {
+      int g0 = li < n0 ? a.list0[li] : a.list0[a.list_cap - 1 - (li - n0)];
+      const int nom = a.rowslot[g0 / a.W - a.row_lo];
+      const double* shn = a.share + (size_t)nom * a.share_stride;
+      const int slot = g0 % a.W;
+      if (li < n0) {
+        if (slot != 0) { bin = lane_bin((int)a.share[(size_t)li * a.share_stride + L.hdr], (int)shn[L.hdr + 2], 0); gidx = li; }
+      } else {
+        bin = lane_bin((int)shn[L.hdr], (int)shn[L.hdr + 2], slot <= 2 * a.m);
+        gidx = -1 - (li - n0);
+      }
+    }
+  } else if (li < count) {
     gidx = a.list0[a.list_cap - 1 - li];
     const double* sh = a.share + (size_t)(gidx / a.W - a.row_lo) * a.share_stride;
-    bin = lane_bin((int)sh[L.hdr], (int)sh[L.hdr + 2]);
+    bin = lane_bin((int)sh[L.hdr], (int)sh[L.hdr + 2], gidx % a.W <= 2 * a.m);
   }
   const int lane = threadIdx.x & 31;
   const unsigned peers = __match_any_sync(0xffffffffu, bin);
@@ -147,10 +174,11 @@ __global__ void __launch_bounds__(32) k_fd_dep_lanes(DM dm, FdArgs a, LaneArgs l
   int begin = 0, end = 0;
   for (int k = 0; k < kLaneBins; k++) {
     int c = la.counts[k];
-    if (k < kLaneWorkBins) { if (la.heavy) begin += c; else end += c; }
+    if (k < kLaneHalf) { if (la.heavy) begin += c; else end += c; }
     else if (la.heavy) end += c;
   }
   if (la.heavy) end += begin;
+  const bool nominal_stage = la.full && la.stage == 0;
   const int count = end - begin;
   int* cursor = &la.counts[2 * kLaneBins + la.heavy];
   for (;;) {
@@ -165,21 +193,31 @@ __global__ void __launch_bounds__(32) k_fd_dep_lanes(DM dm, FdArgs a, LaneArgs l
       FdWorld wd;
       wd.kind = 0; wd.col = 0; wd.sgn = 0; wd.slot = 0; wd.row = 0; wd.b = 0; wd.t = 0;
       long long gidx = 0;
+      int own = -1;  // full mode: slot of this world's own position stage (nominal / position worlds)
       if (active) {
-        gidx = la.list[li];
+        if (!la.full) gidx = la.list[li];
+        else {
+          const int e = la.list[li];
+          if (e >= 0) { own = e; gidx = a.list0[e]; }
+          else gidx = a.list0[a.list_cap - 1 - (-1 - e)];
+        }
         fd_decode(dm, a, gidx, wd);
       }
-      const int rowi = (int)(gidx / a.W), row = wd.row, b = wd.b, slot = wd.slot - 1;
-      const double* __restrict__ sh = a.share + (size_t)(rowi - a.row_lo) * a.share_stride;
+      const int rowi = (int)(gidx / a.W), row = wd.row, b = wd.b;
+      // slot that holds the position stage this world runs on; `shn` = the slot of the key-point's nominal world
+      const int nomslot = la.full ? (active ? a.rowslot[rowi - a.row_lo] : 0) : rowi - a.row_lo;
+      double* const shn = a.share + (size_t)nomslot * a.share_stride;
+      const double* __restrict__ sh = own >= 0 ? a.share + (size_t)own * a.share_stride : shn;
+      const bool fullvel = wd.kind != 1;  // control worlds reuse the nominal world's velocity stage
       const double* __restrict__ snap = a.snap + ((size_t)b * (a.T + 1) + wd.t) * a.SD;
       const int ne = active ? (int)__ldg(&sh[L.hdr]) : 0;
       const int hbits = active ? (int)__ldg(&sh[L.hdr + 1]) : 0;
       // the key-point's shared, read-only data (through L1; lanes of the same key-point read the same addresses)
       const double* __restrict__ uM = sh + L.M; const double* __restrict__ uLD = sh + L.LD;
       const double* __restrict__ uLDinv = sh + L.LDinv; const double* __restrict__ uJ = sh + L.J;
-      const double* __restrict__ uD = sh + L.D; const double* __restrict__ uaref = sh + L.aref;
+      const double* __restrict__ uD = sh + L.D; const double* __restrict__ uaref = shn + L.aref;
       const double* __restrict__ uB = sh + L.Bc; const double* __restrict__ ukterm = sh + L.kterm;
-      const double* __restrict__ ufpas = sh + L.fpas; const double* __restrict__ ufbias = sh + L.fbias;
+      const double* __restrict__ ufpas = shn + L.fpas; const double* __restrict__ ufbias = shn + L.fbias;
       const double* __restrict__ ucinert = sh + L.cinert; const double* __restrict__ ucdof = sh + L.cdof;
       const double* __restrict__ uLDe = sh + L.LDe; const double* __restrict__ uHinv = sh + L.Hinv;
       const double* __restrict__ uqpos = snap + 1; const double* __restrict__ uqvel = snap + 1 + nq;
@@ -189,6 +227,9 @@ __global__ void __launch_bounds__(32) k_fd_dep_lanes(DM dm, FdArgs a, LaneArgs l
         const double e = wd.sgn ? -a.eps : a.eps;
         const int pd = wd.kind == 2 ? a.dof_adr[wd.col] : -1;       // perturbed dof
         const int pa = wd.kind == 1 ? a.ctrl_adr[wd.col] : -1;      // perturbed actuator
+        // perturbed qpos address (position worlds; hinge / slide joints only on this path: mj_integratePos adds eps)
+        const int pqa = wd.kind == 3 ? dm.jnt_qposadr[dm.dof_jntid[a.dof_adr[wd.col]]] : -1;
+        int work = 0;
         // ---- velocity stage --------------------------------------------------------------------------------------
 #pragma unroll
         for (int i = 0; i < nv; i++) {
@@ -197,7 +238,7 @@ __global__ void __launch_bounds__(32) k_fd_dep_lanes(DM dm, FdArgs a, LaneArgs l
           if (tk::bad_value(v)) st |= tk::ST_BAD_QVEL;
           TOKP_PL(v_qvel, i) = v;
         }
-        if (wd.kind == 2) {
+        if (fullvel) {
           // mj_comVel + mj_rne(flg_acc = 0), bodies in tree order (parents first); hinge / slide joints only
           for (int k = 0; k < 6; k++) { TOKP_PL(s_cvel, k) = 0.0; TOKP_PL(s_cfrc, k) = 0.0; }
           TOKP_PL(s_cacc, 0) = 0.0; TOKP_PL(s_cacc, 1) = 0.0; TOKP_PL(s_cacc, 2) = 0.0;
@@ -240,12 +281,13 @@ __global__ void __launch_bounds__(32) k_fd_dep_lanes(DM dm, FdArgs a, LaneArgs l
 #pragma unroll
         for (int i = 0; i < nv; i++) {
           double fp, fb;
-          if (wd.kind == 2) {
+          if (fullvel) {
             fp = -dm.dof_damping[i] * TOKP_PL(v_qvel, i);
             const int bi = dm.dof_bodyid[i];
             const double* cd = &ucdof[6 * i];
             fb = cd[0] * TOKP_PL(s_cfrc, 6 * bi) + cd[1] * TOKP_PL(s_cfrc, 6 * bi + 1) + cd[2] * TOKP_PL(s_cfrc, 6 * bi + 2) +
                  cd[3] * TOKP_PL(s_cfrc, 6 * bi + 3) + cd[4] * TOKP_PL(s_cfrc, 6 * bi + 4) + cd[5] * TOKP_PL(s_cfrc, 6 * bi + 5);
+            if (nominal_stage) { shn[L.fpas + i] = fp; shn[L.fbias + i] = fb; }
           } else {
             fp = ufpas[i]; fb = ufbias[i];
           }
@@ -259,7 +301,7 @@ __global__ void __launch_bounds__(32) k_fd_dep_lanes(DM dm, FdArgs a, LaneArgs l
             double force = dm.actuator_gainprm[ac] * ctrl;
             if (dm.actuator_biastype[ac] == 1) {
               int qa = dm.jnt_qposadr[dm.actuator_trnid[ac]];
-              force += dm.actuator_biasprm[3 * ac] + dm.actuator_biasprm[3 * ac + 1] * (gear * uqpos[qa]) +
+              force += dm.actuator_biasprm[3 * ac] + dm.actuator_biasprm[3 * ac + 1] * (gear * (uqpos[qa] + (qa == pqa ? e : 0.0))) +
                        dm.actuator_biasprm[3 * ac + 2] * (gear * TOKP_PL(v_qvel, i));
             }
             if (dm.actuator_forcelimited[ac]) force = fmin(fmax(force, dm.actuator_forcerange[2 * ac]), dm.actuator_forcerange[2 * ac + 1]);
@@ -292,11 +334,12 @@ __global__ void __launch_bounds__(32) k_fd_dep_lanes(DM dm, FdArgs a, LaneArgs l
           for (int r = 0; r < ne; r++) {
             const double* Jr = &uJ[r * nv];
             double s1 = 0.0, s2 = 0.0, ar;
-            if (wd.kind == 2) {
+            if (fullvel) {
               double vel = 0.0;
 #pragma unroll
               for (int i = 0; i < nv; i++) vel += Jr[i] * TOKP_PL(v_qvel, i);
               ar = -uB[r] * vel - ukterm[r];
+              if (nominal_stage) shn[L.aref + r] = ar;  // the control worlds of this key-point reuse it
             } else {
               ar = uaref[r];
             }
@@ -559,6 +602,7 @@ __global__ void __launch_bounds__(32) k_fd_dep_lanes(DM dm, FdArgs a, LaneArgs l
                   if (fixed_point_check && a_eval == p1.alpha) { alpha = p1.alpha; state = S_DONE; }
                 }
               }
+              work += lsiter;
             }
             if (alpha == 0.0) break;
 #pragma unroll
@@ -569,6 +613,7 @@ __global__ void __launch_bounds__(32) k_fd_dep_lanes(DM dm, FdArgs a, LaneArgs l
             for (int r = 0; r < ne; r++) TOKP_PL(s_jar, r) += alpha * TOKP_PL(s_jv, r);
           }
         }
+        if (nominal_stage) shn[L.hdr + 2] = (double)work;  // sort key of the other worlds of this key-point
         // ---- mj_EulerSkip(skipfactor) + mj_advance ---------------------------------------------------------------
 #pragma unroll
         for (int i = 0; i < nv; i++) if (tk::bad_value(TOKP_PL(v_qacc, i))) st |= tk::ST_BAD_QACC;
@@ -592,7 +637,7 @@ __global__ void __launch_bounds__(32) k_fd_dep_lanes(DM dm, FdArgs a, LaneArgs l
           for (int i = 0; i < nv; i++) TOKP_PL(v_grad, i) = TOKP_PL(v_qacc, i);
         }
         const double hstep = dm.timestep;
-        double* o = a.fd_out + ((size_t)row * a.W + 1 + slot) * (nq + nv);
+        double* o = a.fd_out + ((size_t)row * a.W + wd.slot) * (nq + nv);
 #pragma unroll
         for (int i = 0; i < nv; i++) {
           double v = TOKP_PL(v_qvel, i) + TOKP_PL(v_grad, i) * hstep;
@@ -601,7 +646,7 @@ __global__ void __launch_bounds__(32) k_fd_dep_lanes(DM dm, FdArgs a, LaneArgs l
         }
         for (int j = 0; j < dm.njnt; j++) {  // hinge / slide joints only (checked when the lane path is selected)
           int pq = dm.jnt_qposadr[j], va = dm.jnt_dofadr[j];
-          double q = uqpos[pq];
+          double q = uqpos[pq] + (pq == pqa ? e : 0.0);
           if (tk::bad_value(q)) st |= tk::ST_BAD_QPOS;
           o[pq] = q + hstep * TOKP_PL(v_qvel, va);
         }
@@ -609,7 +654,7 @@ __global__ void __launch_bounds__(32) k_fd_dep_lanes(DM dm, FdArgs a, LaneArgs l
         st |= tk::ST_OVERFLOW;  // more constraint rows than the lane workspace holds
       }
       if (active) {
-        a.status[(size_t)row * a.W + 1 + slot] = (st & 63) | (1 << 30);
+        a.status[(size_t)row * a.W + wd.slot] = (st & 63) | (1 << 30);
         if (st & 63) atomicOr(&a.wstatus[2 * b], st & 63);
       }
     }

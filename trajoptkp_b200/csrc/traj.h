@@ -94,12 +94,17 @@ struct tokp_traj {
   double *cost, *deltaJ, *lambda_d;  // [B]
   double *snap0_in, *U0_in;          // resident copies of the last host inputs of tokp_optimise ([B][SD], [B][T][m])
   int* bp_ok;         // [B]
+  int* fd_list2;      // [B*T*W] FD worlds sorted for the lane kernel
   int *fd_list0, *fd_list1;  // [B*T*W] compacted FD world lists
-  int* fd_counts;     // [256] list sizes and cursors of the FD launch, bin sizes of the lane kernel (cuda_fd.cu, fd_lanes.cuh)
+  int* fd_counts;     // [1024] list sizes and cursors of the FD launch, bin sizes of the lane kernel (cuda_fd.cu, fd_lanes.cuh)
   double* fd_share = nullptr;  // [fd_share_rows][ShareLayout.total] stage-sharing slots (own allocation, made on first use)
-  int fd_share_rows = 0;
+  int fd_share_rows = 0, fd_share_slots_per_row = 1;
+  int* fd_rowslot = nullptr;   // [fd_share_rows] slot of each row's nominal world (tail of the fd_share allocation)
+  int fd_last_lane_mode = 0;
+  int fd_share_gib = 8;        // cap of the lane_mode-2 share buffer (TOKP_FD_SHARE_GIB, read once at creation)
   int fd_stage_sharing = 1;    // mj_stepSkip-style stage reuse between the worlds of a key-point (tokp_traj_set_option)
-  int fd_lanes = 1;            // lane-per-world kernel for the stage-reusing FD worlds where the model allows it
+  int fd_lanes = 2;            // lane-per-world FD kernel where the model allows it: 1 = the stage-reusing worlds, 2 = every
+                               // world (the group kernel then runs the position stage only), 0 = off
   int sm_count = 148;
   int fd_blocksync = 2;        // Grp::bsync level of the FD kernels (TOKP_FD_BLOCKSYNC, read once at creation)
   int* roll_flags;    // [B][NA] rollout worlds that overflowed the fast constraint-row capacity

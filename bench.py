@@ -285,12 +285,18 @@ def run_task(args, task, rank, world, local, dist, torch, headline):
     t0 = time.perf_counter()
     jac = 0.0
     phase = np.zeros(3)
+    step_ms = []
     for _ in range(args.steps):
+        ts = time.perf_counter()
         stats = tr.optimise_resident(1, 1, lam=0.1)
         jac += tr.counters()[1] / 1e6
         phase += stats[:, 5:8].max(axis=0)
+        step_ms.append(1e3 * (time.perf_counter() - ts))
     barrier()
     dt = time.perf_counter() - t0
+    if os.environ.get("TOKP_BENCH_VERBOSE"):
+        print("rank %d %s resident steps ms: %s  derivs/bp/fp of last: %s  reruns %d" % (
+            rank, task, ["%.1f" % x for x in step_ms], stats[:, 5:8].max(axis=0).tolist(), tr.counters()[3]), file=sys.stderr)
     fd1 = tr.fd_kernel_ms()
     l1 = capi.lib().tokp_launch_count()
     # ---- timed region 2: end to end through the C ABI with host buffers -------------------------------------------------

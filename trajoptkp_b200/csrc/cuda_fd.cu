@@ -605,23 +605,24 @@ extern "C" int tokp_dynamics_derivs_cols(tokp_traj* tr, int b, int t, const int*
     mk |= 1ull << cols[i];
   }
   int row = b * tr->T + t;
-  // temporary one-row mask + row list live at the end of the status array's row (reuse small scratch allocations)
-  unsigned long long* d_mask;
-  int* d_row;
-  TOKP_CUDA(cudaMalloc(&d_mask, (size_t)tr->B * tr->T * 8));
-  TOKP_CUDA(cudaMalloc(&d_row, 4));
-  TOKP_CUDA(cudaMemsetAsync(d_mask, 0, (size_t)tr->B * tr->T * 8, tr->stream));
+  // persistent scratch of the trajectory (allocated once, on the first call): an all-zero [B*T] mask in which only this
+  // call's row is set for the duration of the launch, and the one-entry row list
+  if (!tr->cols_scratch) {
+    TOKP_CUDA(cudaMalloc(&tr->cols_scratch, (size_t)tr->B * tr->T * 8 + 8));
+    TOKP_CUDA(cudaMemsetAsync(tr->cols_scratch, 0, (size_t)tr->B * tr->T * 8 + 8, tr->stream));
+  }
+  unsigned long long* d_mask = static_cast<unsigned long long*>(tr->cols_scratch);
+  int* d_row = reinterpret_cast<int*>(d_mask + (size_t)tr->B * tr->T);
   TOKP_CUDA(cudaMemcpyAsync(d_mask + row, &mk, 8, cudaMemcpyHostToDevice, tr->stream));
   TOKP_CUDA(cudaMemcpyAsync(d_row, &row, 4, cudaMemcpyHostToDevice, tr->stream));
   int rc = launch_fd(tr, d_mask, d_row, 1, central_diff, eps);
-  if (rc) { cudaFree(d_mask); cudaFree(d_row); return rc; }
+  cudaMemsetAsync(d_mask + row, 0, 8, tr->stream);  // leave the mask all-zero again, whatever happened
+  if (rc) return rc;
   int nx = tr->nx, m = tr->m, n = tr->n;
   std::vector<double> hA((size_t)nx * nx), hB((size_t)nx * (m > 0 ? m : 1));
   TOKP_CUDA(cudaMemcpyAsync(hA.data(), tr->A + (size_t)row * nx * nx, hA.size() * 8, cudaMemcpyDeviceToHost, tr->stream));
   if (m > 0) TOKP_CUDA(cudaMemcpyAsync(hB.data(), tr->Bm + (size_t)row * nx * m, (size_t)nx * m * 8, cudaMemcpyDeviceToHost, tr->stream));
   TOKP_CUDA(cudaStreamSynchronize(tr->stream));
-  cudaFree(d_mask);
-  cudaFree(d_row);
   for (int i = 0; i < ncols; i++) {
     int c = cols[i];
     for (int j = 0; j < nx; j++) {

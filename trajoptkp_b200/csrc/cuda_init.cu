@@ -331,11 +331,12 @@ extern "C" int tokp_init_controls_gravcomp(tokp_traj* tr, const double* snapshot
     if (rc) return rc;
     pack_snapshot(tr, snapshot0 + (size_t)b * tr->S, d.data() + (size_t)b * tr->SD);
   }
-  double *d_snap = nullptr, *d_U = nullptr;
-  int* d_st = nullptr;
-  TOKP_CUDA(cudaMalloc(&d_snap, d.size() * 8));
-  TOKP_CUDA(cudaMalloc(&d_U, (size_t)B * T * m * 8));
-  TOKP_CUDA(cudaMalloc(&d_st, (size_t)B * 4));
+  // one scratch allocation (snapshots | controls | status), released on every return path
+  struct Scratch { void* p = nullptr; ~Scratch() { if (p) cudaFree(p); } } scratch;
+  TOKP_CUDA(cudaMalloc(&scratch.p, d.size() * 8 + (size_t)B * T * m * 8 + (size_t)B * 4));
+  double* d_snap = static_cast<double*>(scratch.p);
+  double* d_U = d_snap + d.size();
+  int* d_st = reinterpret_cast<int*>(d_U + (size_t)B * T * m);
   TOKP_CUDA(cudaMemcpyAsync(d_snap, d.data(), d.size() * 8, cudaMemcpyHostToDevice, tr->stream));
   // full constraint-row capacity: this is a one-off generator, not a hot loop
   int G = tr->G < 8 ? 8 : tr->G;
@@ -358,7 +359,6 @@ extern "C" int tokp_init_controls_gravcomp(tokp_traj* tr, const double* snapshot
   TOKP_CUDA(cudaMemcpyAsync(U_out, d_U, (size_t)B * T * m * 8, cudaMemcpyDeviceToHost, tr->stream));
   TOKP_CUDA(cudaMemcpyAsync(hst.data(), d_st, (size_t)B * 4, cudaMemcpyDeviceToHost, tr->stream));
   TOKP_CUDA(cudaStreamSynchronize(tr->stream));
-  cudaFree(d_snap); cudaFree(d_U); cudaFree(d_st);
   if (status_out) for (int b = 0; b < B; b++) status_out[b] = hst[b];
   return TOKP_OK;
 }

@@ -170,13 +170,13 @@ static int keypoints_iterative(tokp_traj* tr) {
   for (int b = 0; b < B; b++)
     for (int i = 0; i < n; i++) list.push_back({b, i, 0, T - 1});
   std::vector<unsigned long long> computed((size_t)B * T, 0ull), need((size_t)B * T);
-  unsigned long long* d_need;
-  int *d_rows, *d_seg, *d_good;
-  TOKP_CUDA(cudaMalloc(&d_need, (size_t)B * T * 8));
-  TOKP_CUDA(cudaMalloc(&d_rows, (size_t)B * T * 4));
+  // scratch of the bisection, allocated once per trajectory batch: need mask | row list | segments | verdicts
   size_t segcap = (size_t)B * n * (T + 1);
-  TOKP_CUDA(cudaMalloc(&d_seg, segcap * 16));
-  TOKP_CUDA(cudaMalloc(&d_good, segcap * 4));
+  if (!tr->ie_scratch) TOKP_CUDA(cudaMalloc(&tr->ie_scratch, (size_t)B * T * 8 + (size_t)B * T * 4 + segcap * 16 + segcap * 4));
+  unsigned long long* d_need = static_cast<unsigned long long*>(tr->ie_scratch);
+  int* d_rows = reinterpret_cast<int*>(d_need + (size_t)B * T);
+  int* d_seg = d_rows + (size_t)B * T;
+  int* d_good = d_seg + segcap * 4;
   int rc = TOKP_OK;
   while (!list.empty()) {
     // segments short enough are accepted before anything is computed (KeyPointGenerator.cpp:561-563)
@@ -234,7 +234,6 @@ static int keypoints_iterative(tokp_traj* tr) {
     for (auto mk : computed) cols += __builtin_popcountll(mk);
     tr->counters[1] = (int64_t)((double)cols / n * 1e6);
   }
-  cudaFree(d_need); cudaFree(d_rows); cudaFree(d_seg); cudaFree(d_good);
   return rc;
 }
 

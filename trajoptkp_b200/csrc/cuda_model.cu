@@ -20,6 +20,13 @@ void device_model_free(DeviceModel* dm) {
   delete dm;
 }
 
+void read_env_options(DM& dm) {
+  dm.opt_warps = 0; dm.opt_efc_cap = 0;
+  if (const char* e = getenv("TOKP_WARPS")) { int v = atoi(e); if (v > 0) dm.opt_warps = v; }
+  if (const char* e = getenv("TOKP_EFC_CAP")) { int v = atoi(e); if (v > 0) dm.opt_efc_cap = v; }
+}
+
+// called at model upload / tokp_traj_create only (reads TOKP_LANES)
 int lanes_for_model(const DM& dm) {
   if (const char* e = getenv("TOKP_LANES")) {  // tuning override (8 / 16 / 32)
     int v = atoi(e);
@@ -35,7 +42,7 @@ int lanes_for_model(const DM& dm) {
 
 int fast_ecap(const DM& dm) {
   int cap = dm.fast_ecap > 0 ? dm.fast_ecap : 32;
-  if (const char* e = getenv("TOKP_EFC_CAP")) { int v = atoi(e); if (v > 0) cap = v; }
+  if (dm.opt_efc_cap > 0) cap = dm.opt_efc_cap;
   return cap < dm.maxefc ? cap : dm.maxefc;
 }
 
@@ -61,7 +68,7 @@ int plan_launch(const DM& dm, int G, int pass, LaunchPlan* out) {
     best = total / 2;
     if (best < 1 && per_warp <= sm_bytes) best = 1;
   }
-  if (const char* e = getenv("TOKP_WARPS")) { int v = atoi(e); if (v > 0 && v <= (G == 16 ? 12 : 4) && per_world * v * p.gpw <= sm_bytes) best = v; }
+  if (dm.opt_warps > 0 && dm.opt_warps <= (G == 16 ? 12 : 4) && per_world * dm.opt_warps * p.gpw <= sm_bytes) best = dm.opt_warps;
   if (best == 0) { set_error("model too large for the shared-memory workspace"); return TOKP_ERR_UNSUPPORTED; }
   p.warps = best; p.worlds_per_block = best * p.gpw; p.smem = per_world * best * p.gpw;
   {
@@ -141,6 +148,8 @@ int ensure_device_model(const tokp_model* mc, const DM** out) {
   }
   dm.treedepth = h.dims[10];
   dm.fast_ecap = 0;
+  read_env_options(dm);
+  d->lanes = 0;
   dm.iterations = h.opt_int[0]; dm.ls_iterations = h.opt_int[1];
   dm.timestep = h.opt_real[0];
   dm.gravity[0] = h.opt_real[1]; dm.gravity[1] = h.opt_real[2]; dm.gravity[2] = h.opt_real[3];
@@ -246,7 +255,8 @@ static int step_worlds_impl(const tokp_model* m, const double* snapshots_in, dou
   TOKP_CUDA(cudaMemcpy(d_in, snapshots_in, bytes, cudaMemcpyHostToDevice));
   int iters = solver_iterations < 0 ? dm.iterations : solver_iterations;
   double tol = solver_iterations < 0 ? dm.tolerance : solver_tolerance;
-  int G = lanes_for_model(dm);
+  if (!m->dev->lanes) m->dev->lanes = lanes_for_model(dm);
+  int G = m->dev->lanes;
   for (int pass = 0; pass < (needs_redo_pass(dm) ? 2 : 1); pass++) {
     LaunchPlan lp;
     rc = plan_launch(dm, G, pass, &lp);
@@ -348,7 +358,8 @@ extern "C" int tokp_step_worlds_static(const tokp_model* m, const double* snapsh
   TOKP_CUDA(cudaMemset(d_out, 0, snap_bytes + (size_t)count * sizeof(int)));
   int iters = solver_iterations < 0 ? dm.iterations : solver_iterations;
   double tol = solver_iterations < 0 ? dm.tolerance : solver_tolerance;
-  int G = lanes_for_model(dm);
+  if (!m->dev->lanes) m->dev->lanes = lanes_for_model(dm);
+  int G = m->dev->lanes;
   for (int pass = 0; pass < (needs_redo_pass(dm) ? 2 : 1); pass++) {
     LaunchPlan lp;
     rc = plan_launch(dm, G, pass, &lp);

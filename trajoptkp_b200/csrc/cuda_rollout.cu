@@ -158,7 +158,7 @@ int launch_rollout(tokp_traj* tr, int mode, const double* d_Uin, const double* d
   // few worlds: latency layout - one world per warp with all 32 lanes on it (fewer trips through every strided
   // loop), one warp per block so that the worlds spread over the SMs
   a.spread = nworlds <= 148 * 4;
-  if (a.spread && !getenv("TOKP_SPREAD_KEEP_LANES")) G = 32;
+  if (a.spread && !tr->spread_keep_lanes) G = 32;
   for (int pass = 0; pass < (needs_redo_pass(dm) ? 2 : 1); pass++) {
     LaunchPlan lp;
     int rc = plan_launch(dm, G, pass, &lp);
@@ -171,14 +171,14 @@ int launch_rollout(tokp_traj* tr, int mode, const double* d_Uin, const double* d
       // so that the warps of an SM walk the step together
       warps = (nworlds + 147) / 148;
       if (warps > 4) warps = 4;
-      if (const char* e = getenv("TOKP_SPREAD_WARPS")) { int v = atoi(e); if (v >= 1 && v <= 4) warps = v; }
+      if (tr->spread_warps) warps = tr->spread_warps;
       while (warps > 1 && (size_t)lp.wsd * 8 * warps > 226 * 1024) warps--;  // large models: fewer worlds per block
       blocks = (nworlds + warps - 1) / warps;
       lp.smem = (size_t)lp.wsd * 8 * warps;
     }
     // the redo pass runs a sparse subset of the worlds: no block walk; neither for one-warp blocks
     a.bsync = (pass == 0 && (!a.spread || (warps > 1 && G == 32))) ? 2 : 0;
-    if (const char* e = getenv("TOKP_ROLL_BLOCKSYNC")) if (a.bsync) a.bsync = atoi(e) > 3 ? 3 : (atoi(e) < 0 ? 0 : atoi(e));
+    if (tr->roll_blocksync >= 0 && a.bsync) a.bsync = tr->roll_blocksync;
 #define LAUNCH(GG, NN)                                                                                              \
   TOKP_CUDA(cudaFuncSetAttribute(k_rollout<GG, NN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lp.smem));    \
   k_rollout<GG, NN><<<blocks, warps * 32, lp.smem, tr->stream>>>(dm, a, lp.wsd);

@@ -131,6 +131,10 @@ extern "C" int tokp_traj_create(const tokp_model* m, const tokp_task_desc* td, i
   std::vector<double> tg((size_t)B * ntg);
   for (int b = 0; b < B; b++) std::memcpy(&tg[(size_t)b * ntg], td->resid_target, ntg * 8);
   cudaMemcpy(tr->target, tg.data(), tg.size() * 8, cudaMemcpyHostToDevice);
+  read_env_options(tr->dm);
+  if (const char* e = getenv("TOKP_ROLL_BLOCKSYNC")) tr->roll_blocksync = atoi(e) > 3 ? 3 : (atoi(e) < 0 ? 0 : atoi(e));
+  if (const char* e = getenv("TOKP_SPREAD_WARPS")) { int v = atoi(e); if (v >= 1 && v <= 4) tr->spread_warps = v; }
+  if (getenv("TOKP_SPREAD_KEEP_LANES")) tr->spread_keep_lanes = 1;
   if (const char* e = getenv("TOKP_FD_SHARE_GIB")) { int v = atoi(e); if (v >= 1 && v <= 64) tr->fd_share_gib = v; }
   if (const char* e = getenv("TOKP_FD_BLOCKSYNC")) tr->fd_blocksync = atoi(e) < 0 ? 0 : (atoi(e) > 3 ? 3 : atoi(e));
   {
@@ -158,6 +162,8 @@ extern "C" void tokp_traj_destroy(tokp_traj* tr) {
   if (tr->ev3) cudaEventDestroy(tr->ev3);
   if (tr->arena) cudaFree(tr->arena);
   if (tr->fd_share) cudaFree(tr->fd_share);
+  if (tr->cols_scratch) cudaFree(tr->cols_scratch);
+  if (tr->ie_scratch) cudaFree(tr->ie_scratch);
   delete tr;
 }
 

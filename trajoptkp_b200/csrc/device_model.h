@@ -11,6 +11,9 @@ struct DM {
                   // convex-collider code: every collision pair must be plane-{sphere, capsule, box}); 0 = generic kernels
   int lane_ok;    // the lane-per-world FD kernel applies: spec_nv in {2, 9}, hinge / slide joints only, no gravity
                   // compensation, at most 64 constraint rows
+  // tuning overrides, read from the environment ONCE (model upload; again at tokp_traj_create for the batch's own copy):
+  // TOKP_WARPS (warps per block of the world kernels, 0 = planned), TOKP_EFC_CAP (fast constraint-row capacity, 0 = 32)
+  int opt_warps, opt_efc_cap;
   int fast_ecap;  // constraint-row capacity of the fast pass (0 = default 32); a trajectory batch raises its own copy
                   // when many of its FD worlds overflow (update_fd_counters)
   double timestep, gravity[3], tolerance, ls_tolerance, meaninertia;
@@ -35,4 +38,5 @@ struct DM {
 struct DeviceModel {
   DM dm;
   void* arena = nullptr;  // single device allocation holding every array
+  int lanes = 0;          // lanes per world of tokp_step_worlds (TOKP_LANES read once, on the first call)
 };

@@ -28,6 +28,8 @@ int ensure_device_model(const tokp_model* m, const DM** out);
 
 // number of lanes per world for a model (8, 16 or 32)
 int lanes_for_model(const DM& dm);
+// TOKP_WARPS / TOKP_EFC_CAP into dm.opt_* (called where a DM copy is made, never on a launch path)
+void read_env_options(DM& dm);
 
 // Shared-memory launch plan of the world kernels.  pass 0 = fast pass with a small constraint-row capacity
 // (TOKP_EFC_CAP, default min(maxefc, 32)); pass 1 = redo pass with ecap = maxefc for the worlds that overflowed.
@@ -101,6 +103,10 @@ struct tokp_traj {
   int fd_share_rows = 0, fd_share_slots_per_row = 1;
   int* fd_rowslot = nullptr;   // [fd_share_rows] slot of each row's nominal world (tail of the fd_share allocation)
   int fd_last_lane_mode = 0;
+  // rollout tuning (TOKP_ROLL_BLOCKSYNC, TOKP_SPREAD_WARPS, TOKP_SPREAD_KEEP_LANES; read once at creation)
+  int roll_blocksync = -1, spread_warps = 0, spread_keep_lanes = 0;
+  void* cols_scratch = nullptr;  // tokp_dynamics_derivs_cols: zero [B*T] mask + one row index (allocated on first use)
+  void* ie_scratch = nullptr;    // iterative_error: need mask | row list | segments | verdicts (allocated on first use)
   int fd_share_gib = 8;        // cap of the lane_mode-2 share buffer (TOKP_FD_SHARE_GIB, read once at creation)
   int fd_stage_sharing = 1;    // mj_stepSkip-style stage reuse between the worlds of a key-point (tokp_traj_set_option)
   int fd_lanes = 2;            // lane-per-world FD kernel where the model allows it: 1 = the stage-reusing worlds, 2 = every

@@ -2,8 +2,12 @@
 // RolloutTrajectory -> GenerateKeyPoints -> DynamicsDerivatives -> InterpolateDerivatives -> Optimise) on the acrobot
 // task through the shim classes and prints one JSON object that tests/test_gpu_shim.py compares with the ctypes path
 // and the oracle.  usage: shim_test <acrobot.xml> [--no-gpu]
+//                        shim_test <boxSweep.xml> --boxsweep <input.txt>   (a target config: 7 arm joints + the goal
+//                        body's x, y, z, vector targets, aux bodies, iterative_error key-points; the input file holds
+//                        T, the start snapshot, the goal and the initial controls - written by tests/test_gpu_shim.py)
 #include <cmath>
 #include <cstdio>
+#include <fstream>
 
 #include "tokp_shim_optimiser.h"
 
@@ -13,8 +17,92 @@ static void print_vec(const char* name, const std::vector<double>& v, bool last 
   std::printf("]%s\n", last ? "" : ",");
 }
 
+// BASELINE configs[2] through the shim: InitModelTranslator with rigid bodies -> RolloutTrajectory -> SetCurrentKeypointMethod
+// (iterative_error) -> GenerateKeyPoints -> GenerateDerivatives -> DynamicsDerivatives (per-call) -> Optimise
+static int run_boxsweep(const char* xml, const char* input) {
+  std::ifstream in(input);
+  if (!in) { std::fprintf(stderr, "shim_test: cannot read %s\n", input); return 2; }
+  int T = 0;
+  in >> T;
+  auto helper = std::make_shared<MuJoCoHelper>();
+  helper->InitSimulator(0.008, xml);  // box_sweep.yaml: timeStep 0.008
+  mjData start = *helper->master_reset_data;
+  for (int i = 0; i < helper->S; i++) in >> start.v[i];
+  double gx, gy;
+  in >> gx >> gy;
+  std::vector<MatrixXd> U0(T, MatrixXd(7, 1));
+  for (int t = 0; t < T; t++) for (int i = 0; i < 7; i++) in >> U0[t](i, 0);
+  if (!in) { std::fprintf(stderr, "shim_test: short input file\n"); return 2; }
+  // TaskConfigs/rigid_body_manipulation/box_sweep.yaml
+  keypoint_method kp;
+  kp.name = "iterative_error"; kp.min_N = 1; kp.max_N = 50; kp.iterative_error_threshold = 1e-5;
+  kp.jerk_thresholds.assign(7, 1.0);
+  kp.velocity_change_thresholds.assign(7, 0.5);
+  rigid_body goal;
+  goal.name = "goal";
+  for (int k = 0; k < 3; k++) { goal.active_linear_dof[k] = true; goal.linear_jerk_threshold[k] = 1.0; goal.linear_vel_change_threshold[k] = 0.05; }
+  std::vector<std::string> joints, acts;
+  for (int i = 1; i <= 7; i++) { joints.push_back("panda0_joint" + std::to_string(i)); acts.push_back("panda0_joint" + std::to_string(i)); }
+  auto mt = std::make_shared<ModelTranslator>();
+  mt->InitModelTranslator(helper, TOKP_TASK_BOXSWEEP, joints, acts, {goal}, {gx, gy, 0.0, 0.0, 0.05}, {0.0, 0.2, 0.0},
+                          {1000.0, 100.0, 0.0}, kp, {"goal", "franka_gripper"});
+  std::printf("{\"dof\": %d, \"num_ctrl\": %d, \"num_resid\": %d,\n", mt->dof, mt->num_ctrl, (int)mt->resid_weight.size());
+  {
+    MatrixXd x = mt->ReturnStateVector(&start), r;
+    std::vector<double> xs(x.data(), x.data() + 2 * mt->dof);
+    print_vec("start_state", xs);
+    mt->Residuals(&start, r);
+    print_vec("start_residuals", {r(0, 0), r(1, 0), r(2, 0)});
+  }
+  auto traj = std::make_shared<TrajHandle>(mt, T);
+  auto diff = std::make_shared<Differentiator>(mt, helper, traj);
+  iLQR opt(mt, helper, diff, T);
+  double cost = opt.RolloutTrajectory(&start, true, U0);
+  std::printf("\"rollout_cost\": %.17g,\n", cost);
+  opt.SetCurrentKeypointMethod(mt->current_kp);  // thresholds of all 10 state DoFs (robot joints, then the body's)
+  opt.keypoint_generator->GenerateKeyPoints(opt.X_old, opt.A, opt.B);
+  std::vector<double> rows;
+  int tq = -1;
+  for (int t = 0; t < T; t++) {
+    rows.push_back((double)opt.keypoint_generator->keypoints[t].size());
+    if (tq < 0 && t > 0 && (int)opt.keypoint_generator->keypoints[t].size() == mt->dof) tq = t;
+  }
+  if (tq < 0) tq = T - 1;
+  print_vec("keypoint_counts", rows);
+  print_vec("percentages", opt.keypoint_generator->last_percentages);
+  opt.GenerateDerivatives();
+  const int nx = 2 * mt->dof;
+  MatrixXd At(nx, nx), Bt(nx, 7);
+  std::vector<int> cols;
+  for (int i = 0; i < mt->dof; i++) cols.push_back(i);
+  diff->DynamicsDerivatives(At, Bt, cols, tq, 0, true, 1e-6);
+  double dmax = 0;
+  for (int i = 0; i < nx; i++) {
+    for (int j = 0; j < nx; j++) dmax = std::fmax(dmax, std::fabs(At(i, j) - opt.A[tq](i, j)));
+    for (int j = 0; j < 7; j++) dmax = std::fmax(dmax, std::fabs(Bt(i, j) - opt.B[tq](i, j)));
+  }
+  std::printf("\"t_query\": %d, \"cols_vs_batched_maxabs\": %.3g,\n", tq, dmax);
+  print_vec("A_t", std::vector<double>(At.data(), At.data() + nx * nx));
+  opt.lambda = 0.1;
+  auto Uopt = opt.Optimise(&start, U0, 2, 1, T);
+  std::vector<double> uo;
+  for (auto& u : Uopt) for (int i = 0; i < 7; i++) uo.push_back(u(i, 0));
+  print_vec("U_opt", uo);
+  std::printf("\"initial_cost\": %.17g, \"final_cost\": %.17g, \"iterations\": %d}\n", opt.initial_cost, opt.new_cost,
+              opt.num_iterations);
+  return 0;
+}
+
 int main(int argc, char** argv) {
-  if (argc < 2) { std::fprintf(stderr, "usage: shim_test model.xml [--no-gpu]\n"); return 2; }
+  if (argc < 2) { std::fprintf(stderr, "usage: shim_test model.xml [--no-gpu | --boxsweep input.txt]\n"); return 2; }
+  if (argc > 3 && std::string(argv[2]) == "--boxsweep") {
+    try {
+      return run_boxsweep(argv[1], argv[3]);
+    } catch (const std::exception& e) {
+      std::fprintf(stderr, "shim_test: %s\n", e.what());
+      return 1;
+    }
+  }
   bool no_gpu = argc > 2 && std::string(argv[2]) == "--no-gpu";
   const int T = 50;
   try {

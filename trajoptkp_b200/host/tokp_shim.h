@@ -105,6 +105,12 @@ class MuJoCoHelper {
   // name -> index (mj_name2id call sites MuJoCoHelper.cpp:36-438)
   int JointId(const std::string& n) const { return tokp_model_name2id(model, TOKP_OBJ_JOINT, n.c_str()); }
   int ActuatorId(const std::string& n) const { return tokp_model_name2id(model, TOKP_OBJ_ACTUATOR, n.c_str()); }
+  int BodyId(const std::string& n) const { return tokp_model_name2id(model, TOKP_OBJ_BODY, n.c_str()); }
+  // GetBodyPoseQuatViaXpos (MuJoCoHelper.cpp:400-410) after mj_kinematics: world position of a body at d's qpos
+  void BodyXpos(const std::string& n, mjData* d, double pos[3]) const {
+    double quat[4];
+    tokp_shim::check(tokp_model_body_pose(model, qpos(d), BodyId(n), pos, quat), "BodyXpos");
+  }
   double* qpos(mjData* d) const { return d->v.data() + 1; }
   double* qvel(mjData* d) const { return d->v.data() + 1 + nq; }
   double* ctrl(mjData* d) const { return d->v.data() + S - nu; }

@@ -5,8 +5,67 @@
 
 // ---- ModelTranslator: state-vector <-> qpos/qvel maps and the task description ---------------------------------
 // (InitModelTranslator ModelTranslator.cpp:18-96; ComputeStateDofAdrIndices :1548-1610; ReturnStateVector :882)
+// one rigid body of the state vector (struct rigid_body, include/StdInclude.h:119-188): the active linear DoFs of its
+// free joint become state elements after the robot joints (ComputeStateDofAdrIndices, ModelTranslator.cpp:1548-1610);
+// angular elements (axis-angle read-out) are outside the supported subset
+struct rigid_body {
+  std::string name;
+  bool active_linear_dof[3] = {false, false, false};
+  bool active_angular_dof[3] = {false, false, false};
+  double linear_jerk_threshold[3] = {0, 0, 0};
+  double linear_vel_change_threshold[3] = {0, 0, 0};
+};
+
 class ModelTranslator {
  public:
+  // Signature note: the reference's InitModelTranslator takes the task YAML path
+  // (include/ModelTranslator/ModelTranslator.h:91) and reads these lists through yaml-cpp, which is not available here.
+  // This overload adds what the manipulation tasks need on top of the joint-only form below: rigid bodies of the
+  // state vector, residual targets that are vectors (residual_list[i].target[j]: `target` then holds them
+  // concatenated while weight / weight_terminal have one entry per residual), and the bodies the residuals read.
+  void InitModelTranslator(std::shared_ptr<MuJoCoHelper> helper, int task_kind, const std::vector<std::string>& joints,
+                           const std::vector<std::string>& actuators, const std::vector<rigid_body>& bodies,
+                           const std::vector<double>& target, const std::vector<double>& weight,
+                           const std::vector<double>& weight_terminal, keypoint_method kp,
+                           const std::vector<std::string>& aux_bodies) {
+    std::vector<int> bj(helper->nbody + 8), jq(helper->nq + 64), jd(helper->nv + 64);
+    tokp_model_get_int(helper->model, "body_jntadr", bj.data(), (int)bj.size());
+    tokp_model_get_int(helper->model, "jnt_qposadr", jq.data(), (int)jq.size());
+    tokp_model_get_int(helper->model, "jnt_dofadr", jd.data(), (int)jd.size());
+    size_t nj = joints.size();
+    // thresholds: the robot's come first in kp, the bodies' are appended in state order
+    if (kp.jerk_thresholds.size() != nj) kp.jerk_thresholds.assign(nj, 0.0);
+    if (kp.velocity_change_thresholds.size() != nj) kp.velocity_change_thresholds.assign(nj, 0.0);
+    std::vector<int> bq, bd;
+    for (const auto& b : bodies) {
+      int id = helper->BodyId(b.name);
+      if (id < 0) throw std::runtime_error("body not in model: " + b.name);
+      if (b.active_angular_dof[0] || b.active_angular_dof[1] || b.active_angular_dof[2])
+        throw std::runtime_error("angular rigid-body state elements are not supported");
+      for (int k = 0; k < 3; k++)
+        if (b.active_linear_dof[k]) {
+          bq.push_back(jq[bj[id]] + k);
+          bd.push_back(jd[bj[id]] + k);
+          kp.jerk_thresholds.push_back(b.linear_jerk_threshold[k]);
+          kp.velocity_change_thresholds.push_back(b.linear_vel_change_threshold[k]);
+        }
+    }
+    keypoint_method robot_kp = kp;
+    robot_kp.jerk_thresholds.resize(nj);
+    robot_kp.velocity_change_thresholds.resize(nj);
+    InitModelTranslator(helper, task_kind, joints, actuators, target, weight, weight_terminal, robot_kp);
+    qpos_adr.insert(qpos_adr.end(), bq.begin(), bq.end());
+    state_dof_adr_indices.insert(state_dof_adr_indices.end(), bd.begin(), bd.end());
+    dof = (int)qpos_adr.size();
+    current_kp = kp;
+    aux.clear();
+    aux_names = aux_bodies;
+    for (const auto& n : aux_bodies) {
+      int id = helper->BodyId(n);
+      if (id < 0) throw std::runtime_error("body not in model: " + n);
+      aux.push_back(id);
+    }
+  }
   // joint / actuator names in YAML order (robots[].jointNames / actuatorNames), residual terms flattened with
   // resid_dimension replication (FileHandler.cpp:276-287)
   void InitModelTranslator(std::shared_ptr<MuJoCoHelper> helper, int task_kind, const std::vector<std::string>& joints,
@@ -39,14 +98,15 @@ class ModelTranslator {
     tokp_task_desc d;
     d.kind = kind; d.n = dof; d.m = num_ctrl;
     d.qpos_adr = qpos_adr.data(); d.dof_adr = state_dof_adr_indices.data(); d.ctrl_adr = ctrl_adr.data();
-    d.num_resid = (int)resid_target.size();
+    d.num_resid = (int)resid_weight.size();
     d.resid_target = resid_target.data(); d.resid_weight = resid_weight.data();
     d.resid_weight_terminal = resid_weight_terminal.data();
     d.kp_method = tokp_kp_code(current_kp.name); d.min_N = current_kp.min_N; d.max_N = current_kp.max_N;
     d.jerk_thresholds = current_kp.jerk_thresholds.data();
     d.velchange_thresholds = current_kp.velocity_change_thresholds.data();
     d.iterative_error_threshold = current_kp.iterative_error_threshold;
-    d.num_target = 0; d.num_aux = 0; d.aux = nullptr;
+    d.num_target = resid_target.size() != resid_weight.size() ? (int)resid_target.size() : 0;
+    d.num_aux = (int)aux.size(); d.aux = aux.empty() ? nullptr : aux.data();
     return d;
   }
   // ReturnStateVector (ModelTranslator.cpp:882-897): [pos(n); vel(n)]
@@ -120,8 +180,23 @@ class ModelTranslator {
     const double* v = MuJoCo_helper->qvel(d);
     const double* u = MuJoCo_helper->ctrl(d);
     const std::vector<double>& t = resid_target;
-    if ((int)residuals.rows() != (int)t.size()) residuals.resize((int)t.size(), 1);
+    if ((int)residuals.rows() != (int)resid_weight.size()) residuals.resize((int)resid_weight.size(), 1);
     int k = 0;
+    if (kind == TOKP_TASK_BOXSWEEP) {
+      // BoxSweep::Residuals (BoxSweep.cpp:101-139): goal body to its target (x, y), its velocity (x, y), gripper to the
+      // goal body minus the reach distance; the goal body's linear elements follow the robot joints in the state
+      if (aux_names.size() < 2) throw std::runtime_error("box_sweep needs aux bodies {goal, franka_gripper}");
+      int nj = dof - 3;
+      double gp[3] = {q[qpos_adr[nj]], q[qpos_adr[nj + 1]], q[qpos_adr[nj + 2]]};
+      double gv[2] = {v[state_dof_adr_indices[nj]], v[state_dof_adr_indices[nj + 1]]};
+      residuals(k++, 0) = std::sqrt(std::pow(gp[0] - t[0], 2) + std::pow(gp[1] - t[1], 2));
+      residuals(k++, 0) = std::sqrt(std::pow(gv[0] - t[2], 2) + std::pow(gv[1] - t[3], 2));
+      double ee[3];
+      MuJoCo_helper->BodyXpos(aux_names[1], d, ee);
+      double dist = std::sqrt(std::pow(ee[0] - gp[0], 2) + std::pow(ee[1] - gp[1], 2) + std::pow(ee[2] - gp[2], 2));
+      residuals(k++, 0) = dist - t[4];
+      return;
+    }
     if (kind == TOKP_TASK_ACROBOT) {
       residuals(k++, 0) = q[qpos_adr[0]] - t[0];
       residuals(k++, 0) = q[qpos_adr[1]] - t[1];
@@ -136,18 +211,19 @@ class ModelTranslator {
     } else {
       throw std::runtime_error("residuals not implemented for this model");
     }
-    if (k != (int)t.size()) throw std::runtime_error("Error: Residuals size mismatch");
+    if (k != (int)resid_weight.size()) throw std::runtime_error("Error: Residuals size mismatch");
   }
   double CostFunction(const MatrixXd& residuals, bool terminal) const {
     double cost = 0.0;
-    for (size_t i = 0; i < resid_target.size(); i++)
+    for (size_t i = 0; i < resid_weight.size(); i++)
       cost += (terminal ? resid_weight_terminal[i] : resid_weight[i]) * std::pow(residuals((int)i, 0), 2);
     return cost;
   }
 
   std::shared_ptr<MuJoCoHelper> MuJoCo_helper;
   int kind = 0, dof = 0, num_ctrl = 0;
-  std::vector<int> qpos_adr, state_dof_adr_indices, ctrl_adr;
+  std::vector<int> qpos_adr, state_dof_adr_indices, ctrl_adr, aux;
+  std::vector<std::string> aux_names;
   std::vector<double> resid_target, resid_weight, resid_weight_terminal;
   keypoint_method current_kp;
 };
@@ -187,7 +263,7 @@ class Differentiator {
   void ResidualDerivatives(std::vector<MatrixXd>& r_x, std::vector<MatrixXd>& r_u, int data_index, int /*tid*/,
                            bool central_diff, double eps) {
     const int nx = 2 * model_translator->dof, m = model_translator->num_ctrl;
-    const int nr = (int)model_translator->resid_target.size();
+    const int nr = (int)model_translator->resid_weight.size();
     const auto& s = MuJoCo_helper->saved_systems_state_list.at(data_index)->v;
     tokp_shim::check(tokp_traj_set_snapshot(traj->h, 0, data_index, s.data()), "set_snapshot");
     std::vector<double> rx((size_t)nx * nr), ru((size_t)(m ? m : 1) * nr);

@@ -6,7 +6,7 @@ key-points, FD dynamics derivatives at the key-points, interpolation, cost deriv
 6-alpha line-search rollouts and acceptance.  `value` times the step with inputs resident in HBM; `e2e` times
 the same call through the C ABI with host buffers (H2D of start snapshots + controls, D2H of controls + stats).
 
-The headline line is walker_run (BASELINE configs[4], velocity_change key-points, H = 80, 512 replans per GPU); the
+The headline line is walker_run (BASELINE configs[4], velocity_change key-points, H = 80, 592 replans per GPU); the
 same line carries `targets.box_sweep` - north_star's second target config (BASELINE configs[2]: iterative_error
 key-points, the task's MPC horizon, the reference's Jacobian end-effector initial controls) with its own value / e2e /
 roofline / cpu_baseline.
@@ -29,8 +29,10 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 KP_METHOD = {"velocity_change": 4, "set_interval": 0, "adaptive_jerk": 1, "iterative_error": 3}
-# per task: (key-point method BASELINE.json names, horizon, replans per GPU)
-DEFAULTS = {"walker_run": ("velocity_change", 80, 512), "box_sweep": ("iterative_error", 100, 256),
+# per task: (key-point method BASELINE.json names, horizon, replans per GPU).  The two target configs are sized to
+# whole waves of the rollout kernel: 148 SMs x 24 resident walker worlds = 3552 = 6 alphas x 592 replans;
+# 148 x 6 resident box_sweep worlds = 888, so 6 x 296 = two full waves.
+DEFAULTS = {"walker_run": ("velocity_change", 80, 592), "box_sweep": ("iterative_error", 100, 296),
             "acrobot": ("set_interval", 500, 512), "reaching": ("adaptive_jerk", 50, 512),
             "push_ncl": ("adaptive_jerk", 50, 256), "push_lcl": ("iterative_error", 100, 64),
             "push_mcl": ("set_interval", 50, 16)}

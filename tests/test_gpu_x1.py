@@ -93,7 +93,7 @@ def test_push_mcl_keypoints_jacobians_cost(built):
 
 
 @pytest.mark.parametrize("name,B,T,kp,setup", [("reaching", 512, 50, capi.KP_ADAPTIVE_JERK, 0),
-                                               ("box_sweep", 256, 100, capi.KP_ITERATIVE_ERROR, 0),
+                                               ("box_sweep", 296, 100, capi.KP_ITERATIVE_ERROR, 0),
                                                ("push_ncl", 256, 50, capi.KP_ADAPTIVE_JERK, 1000),
                                                ("push_lcl", 64, 100, capi.KP_ITERATIVE_ERROR, 1000),
                                                ("push_mcl", 16, 50, capi.KP_SET_INTERVAL, 1000)])

@@ -427,7 +427,7 @@ int launch_fd(tokp_traj* tr, const unsigned long long* mask, const int* rows, in
   // fd_lanes 1 = the stage-reusing (control / velocity) worlds, 2 = every world after a position-stage-only group kernel
   const int lane_mode = (tr->fd_stage_sharing && tr->fd_lanes && dm.lane_ok && 2 * (tr->m + tr->n) <= 64) ? (tr->fd_lanes >= 2 ? 2 : 1) : 0;
   // share buffer: one slot per key-point row of a chunk (lane_mode 2: one per nominal / position world, 1 + 2n per row),
-  // at most ~1 GiB (fd_share_gib, default 8 GiB, in lane_mode 2: 180 GB of HBM make that cheap, and one chunk has one set
+  // at most ~1 GiB (fd_share_gib, default 16 GiB, in lane_mode 2: 180 GB of HBM make that cheap, and one chunk has one set
   // of kernel tails); larger launches run in row chunks
   const ShareLayout L(dm);
   const int slots_per_row = lane_mode == 2 ? 1 + 2 * tr->n : 1;
@@ -455,9 +455,12 @@ int launch_fd(tokp_traj* tr, const unsigned long long* mask, const int* rows, in
   // code, which is several times the instruction cache.  TOKP_FD_BLOCKSYNC=0 lets the warps run independently.
   a.blocksync = tr->fd_blocksync;
   cudaEventRecord(tr->ev2, tr->stream);
-  for (int row_lo = 0; row_lo < nrows; row_lo += tr->fd_share_rows) {
+  // even chunks: every chunk pays the same kernel tails, a short remainder chunk would pay them for little work
+  const int nchunks = (nrows + tr->fd_share_rows - 1) / tr->fd_share_rows;
+  const int chunk_rows = nchunks > 0 ? (nrows + nchunks - 1) / nchunks : 1;
+  for (int row_lo = 0; row_lo < nrows; row_lo += chunk_rows) {
     a.row_lo = row_lo;
-    a.row_hi = row_lo + tr->fd_share_rows < nrows ? row_lo + tr->fd_share_rows : nrows;
+    a.row_hi = row_lo + chunk_rows < nrows ? row_lo + chunk_rows : nrows;
     long long cw = (long long)(a.row_hi - a.row_lo) * tr->W;
     a.ecap = 0; a.pass = 0; a.phase = 0; a.last = 0;
     TOKP_CUDA(cudaMemsetAsync(tr->fd_counts, 0, 8 * sizeof(int), tr->stream));

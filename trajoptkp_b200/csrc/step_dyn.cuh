@@ -250,6 +250,31 @@ TK_DEV void chol_solve(const double* L, int n, double* x, const double* b, const
   }
 }
 
+// The same solve for n <= G with the vector in registers (lane i holds x[i]) and the pivots broadcast by shuffles: no
+// barrier and no shared-memory round trip per column, the reciprocal pivots are formed once, off the dependent chain.
+// Same elimination order as chol_solve; the result differs from it only by the rounding of x * (1 / l) against x / l.
+template <int G, int NV>
+TK_DEV void chol_solve_reg(const double* L, int n, double* x, const double* b, const Grp<G, NV>& g) {
+  const int i = g.gl;
+  const bool mine = i < n;
+  double xi = mine ? b[i] : 0.0;
+  const double dinv = mine ? 1.0 / L[i * n + i] : 0.0;
+#pragma unroll 1
+  for (int j = 0; j < n; j++) {
+    const double xj = __shfl_sync(g.mask, xi * dinv, j, G);
+    if (i == j) xi = xj;
+    else if (mine && i > j) xi -= L[i * n + j] * xj;
+  }
+#pragma unroll 1
+  for (int j = n - 1; j >= 0; j--) {
+    const double xj = __shfl_sync(g.mask, xi * dinv, j, G);
+    if (i == j) xi = xj;
+    else if (i < j) xi -= L[j * n + i] * xj;
+  }
+  if (mine) x[i] = xi;
+  g.sync();
+}
+
 }  // namespace tk
 #include "step_ls.cuh"
 namespace tk {
@@ -329,7 +354,8 @@ TK_DEV void fwd_constraint(const DM& m, WS& w, const Grp<G, NV>& g, int iteratio
       g.sync();
       chol_factor(w.H, nv, g);
     }
-    chol_solve(w.H, nv, w.Mgrad, w.grad, g);
+    if (nv <= G) chol_solve_reg(w.H, nv, w.Mgrad, w.grad, g);
+    else chol_solve(w.H, nv, w.Mgrad, w.grad, g);
     for (int i = g.gl; i < nv; i += G) w.search[i] = -w.Mgrad[i];
     g.sync();
   };

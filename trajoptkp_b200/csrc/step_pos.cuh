@@ -232,15 +232,35 @@ TK_DEV void solve_ldl(const DM& m, const double* LD, const double* dinv, double*
   }
   for (int i = g.gl; i < nv; i += G) x[i] *= dinv[i];
   g.sync();
-  // x <- inv(L) x : row i needs the final values of its ancestors
-#pragma unroll 1
-  for (int i = 1; i < nv; i++) {
-    if (g.gl == 0) {
-      double s = x[i];
-      for (int j = m.dof_parentid[i]; j >= 0; j = m.dof_parentid[j]) s -= LD[i * nv + j] * x[j];
-      x[i] = s;
+  // x <- inv(L) x : row i needs the final values of its ancestors.  Level-synchronous over the depth of the dof in the
+  // tree (= its number of ancestors): all dofs of one depth are independent, each lane walks its own parent chain in
+  // the order of the sequential algorithm, so the values are the same bits.
+  {
+    int depth[(64 + G - 1) / G];  // nv <= 64 (ancestor masks have 64 bits)
+    int maxd = 0;
+#pragma unroll
+    for (int k = 0; k < (64 + G - 1) / G; k++) {
+      const int i = g.gl + k * G;
+      depth[k] = i < nv ? __popc(m.dof_ancmask_lo[i]) + __popc(m.dof_ancmask_hi[i]) : -1;
+      maxd = depth[k] > maxd ? depth[k] : maxd;
     }
-    g.sync();
+#pragma unroll
+    for (int off = G / 2; off > 0; off >>= 1) {
+      const int o = __shfl_xor_sync(g.mask, maxd, off, G);
+      maxd = o > maxd ? o : maxd;
+    }
+#pragma unroll 1
+    for (int d = 1; d <= maxd; d++) {
+#pragma unroll
+      for (int k = 0; k < (64 + G - 1) / G; k++) {
+        if (depth[k] != d) continue;
+        const int i = g.gl + k * G;
+        double s = x[i];
+        for (int j = m.dof_parentid[i]; j >= 0; j = m.dof_parentid[j]) s -= LD[i * nv + j] * x[j];
+        x[i] = s;
+      }
+      g.sync();
+    }
   }
 }
 

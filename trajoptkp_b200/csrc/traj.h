@@ -107,7 +107,7 @@ struct tokp_traj {
   int roll_blocksync = -1, spread_warps = 0, spread_keep_lanes = 0;
   void* cols_scratch = nullptr;  // tokp_dynamics_derivs_cols: zero [B*T] mask + one row index (allocated on first use)
   void* ie_scratch = nullptr;    // iterative_error: need mask | row list | segments | verdicts (allocated on first use)
-  int fd_share_gib = 8;        // cap of the lane_mode-2 share buffer (TOKP_FD_SHARE_GIB, read once at creation)
+  int fd_share_gib = 16;       // cap of the lane_mode-2 share buffer (TOKP_FD_SHARE_GIB, read once at creation)
   int fd_stage_sharing = 1;    // mj_stepSkip-style stage reuse between the worlds of a key-point (tokp_traj_set_option)
   int fd_lanes = 2;            // lane-per-world FD kernel where the model allows it: 1 = the stage-reusing worlds, 2 = every
                                // world (the group kernel then runs the position stage only), 0 = off

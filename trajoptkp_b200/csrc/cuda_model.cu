@@ -164,6 +164,7 @@ int ensure_device_model(const tokp_model* mc, const DM** out) {
   dm.any_damping = 0; dm.any_gravcomp = 0;
   for (double v : h.dof_damping) if (v > 0) dm.any_damping = 1;
   for (double v : h.body_gravcomp) if (v != 0) dm.any_gravcomp = 1;
+  if (const char* e = getenv("TOKP_SPEC_NV")) { if (atoi(e) == 0) dm.spec_nv = 0; }  // tuning: generic kernels only
   dm.lane_ok = (dm.spec_nv == 2 || dm.spec_nv == 9) && !dm.any_gravcomp && dm.maxefc <= 64;
   for (int jt : h.jnt_type) if (jt != JNT_HINGE && jt != JNT_SLIDE) dm.lane_ok = 0;
   m->dev = d;
@@ -202,7 +203,16 @@ __global__ void k_step_worlds(DM dm, const double* __restrict__ in, double* __re
   for (int i = g.gl; i < dm.nu; i += G) w.ctrl[i] = s[S - dm.nu + i];
   g.sync();
   int st = 0;
+#ifdef TOKP_STAGE_CLOCKS
+  w.clk_on = gidx == 0;
+  for (int k = 0; k < nsteps; k++) {
+    w.clk = clock64();
+    TK_CNT(w, g, 22);
+    tk::step(dm, w, g, iterations, tolerance, time, st);
+  }
+#else
   for (int k = 0; k < nsteps; k++) tk::step(dm, w, g, iterations, tolerance, time, st);
+#endif
   if (forward_after) {  // mj_forward: the state stays, qacc and qacc_warmstart become the solution at this state
     tk::step_smooth(dm, w, g, st);
     g.sync();
@@ -282,6 +292,15 @@ extern "C" int tokp_step_worlds(const tokp_model* m, const double* snapshots_in,
                                 int nsteps, int solver_iterations, double solver_tolerance, int* status) {
   return step_worlds_impl(m, snapshots_in, snapshots_out, count, nsteps, solver_iterations, solver_tolerance, status, 0);
 }
+
+#ifdef TOKP_STAGE_CLOCKS
+// development builds only: cycles per stage of world 0 of the tokp_step_worlds launches so far (tools/stage_clocks.py)
+extern "C" int tokp_stage_clocks(unsigned long long* out, int clear) {
+  TOKP_CUDA(cudaMemcpyFromSymbol(out, tk::g_stage_clk, 32 * sizeof(unsigned long long)));
+  if (clear) { unsigned long long z[32] = {0}; TOKP_CUDA(cudaMemcpyToSymbol(tk::g_stage_clk, z, sizeof(z))); }
+  return TOKP_OK;
+}
+#endif
 
 extern "C" int tokp_forward_worlds(const tokp_model* m, const double* snapshots_in, double* snapshots_out, int count,
                                    int nsteps, int solver_iterations, double solver_tolerance, int* status) {

@@ -315,13 +315,13 @@ __global__ void __launch_bounds__(32) k_fd_dep_lanes(DM dm, FdArgs a, LaneArgs l
         for (int i = nv - 1; i > 0; i--) {
           double xi = TOKP_PL(v_asm, i);
           if (xi != 0.0)
-            for (int j = dm.dof_parentid[i]; j >= 0; j = dm.dof_parentid[j]) TOKP_PL(v_asm, j) -= uLD[i * nv + j] * xi;
+            for (unsigned long long ch = tk::anc_mask<NV>(dm, i) & ~(1ull << i); ch;) { const int j = tk::pop_top(ch); TOKP_PL(v_asm, j) -= uLD[i * nv + j] * xi; }
         }
 #pragma unroll
         for (int i = 0; i < nv; i++) TOKP_PL(v_asm, i) *= uLDinv[i];
         for (int i = 1; i < nv; i++) {
           double s = TOKP_PL(v_asm, i);
-          for (int j = dm.dof_parentid[i]; j >= 0; j = dm.dof_parentid[j]) s -= uLD[i * nv + j] * TOKP_PL(v_asm, j);
+          for (unsigned long long ch = tk::anc_mask<NV>(dm, i) & ~(1ull << i); ch;) { const int j = tk::pop_top(ch); s -= uLD[i * nv + j] * TOKP_PL(v_asm, j); }
           TOKP_PL(v_asm, i) = s;
         }
         // ---- mj_fwdConstraint: Newton solver ---------------------------------------------------------------------
@@ -623,13 +623,13 @@ __global__ void __launch_bounds__(32) k_fd_dep_lanes(DM dm, FdArgs a, LaneArgs l
           for (int i = nv - 1; i > 0; i--) {
             double xi = TOKP_PL(v_grad, i);
             if (xi != 0.0)
-              for (int j = dm.dof_parentid[i]; j >= 0; j = dm.dof_parentid[j]) TOKP_PL(v_grad, j) -= uLDe[i * nv + j] * xi;
+              for (unsigned long long ch = tk::anc_mask<NV>(dm, i) & ~(1ull << i); ch;) { const int j = tk::pop_top(ch); TOKP_PL(v_grad, j) -= uLDe[i * nv + j] * xi; }
           }
 #pragma unroll
           for (int i = 0; i < nv; i++) TOKP_PL(v_grad, i) *= uHinv[i];
           for (int i = 1; i < nv; i++) {
             double s = TOKP_PL(v_grad, i);
-            for (int j = dm.dof_parentid[i]; j >= 0; j = dm.dof_parentid[j]) s -= uLDe[i * nv + j] * TOKP_PL(v_grad, j);
+            for (unsigned long long ch = tk::anc_mask<NV>(dm, i) & ~(1ull << i); ch;) { const int j = tk::pop_top(ch); s -= uLDe[i * nv + j] * TOKP_PL(v_grad, j); }
             TOKP_PL(v_grad, i) = s;
           }
         } else {

@@ -26,6 +26,17 @@ enum { ROW_LIMIT = 0, ROW_FRICTIONLESS = 1, ROW_PYRAMIDAL = 2 };
 // status bits (per world)
 enum { ST_BAD_QPOS = 1, ST_BAD_QVEL = 2, ST_BAD_QACC = 4, ST_OVERFLOW = 8, ST_UNSUPPORTED = 32 };
 
+// stage clocks of one tracked world (development builds with -DTOKP_STAGE_CLOCKS only; tools/stage_clocks.py)
+#ifdef TOKP_STAGE_CLOCKS
+static __device__ unsigned long long g_stage_clk[32];
+#define TK_CLK(w, g, i) do { if ((w).clk_on && (g).gl == 0) { long long t_ = clock64(); \
+  atomicAdd(&tk::g_stage_clk[i], (unsigned long long)(t_ - (w).clk)); (w).clk = t_; } } while (0)
+#define TK_CNT(w, g, i) do { if ((w).clk_on && (g).gl == 0) atomicAdd(&tk::g_stage_clk[i], 1ull); } while (0)
+#else
+#define TK_CLK(w, g, i) do {} while (0)
+#define TK_CNT(w, g, i) do {} while (0)
+#endif
+
 // ---- group of G lanes -----------------------------------------------------------------------------
 template <int G, int NV = 0>
 struct Grp {
@@ -59,6 +70,8 @@ struct Grp {
     for (int off = G / 2; off > 0; off >>= 1) v += __shfl_xor_sync(mask, v, off, G);
     return v;
   }
+  // bit l = predicate of lane l of this group
+  TK_DEV unsigned ballot(int p) const { return __ballot_sync(mask, p) >> ((threadIdx.x & 31) - gl); }
   TK_DEV int any(int p) const { return __any_sync(mask, p); }
   TK_DEV int all(int p) const { return __all_sync(mask, p); }
 };
@@ -158,6 +171,19 @@ TK_DEV void cross_force(double* res, const double* vel, const double* f) {
   res[3] = c[0]; res[4] = c[1]; res[5] = c[2];
 }
 TK_DEV bool in_mask(unsigned lo, unsigned hi, int bit) { return bit < 32 ? ((lo >> bit) & 1u) : ((hi >> (bit - 32)) & 1u); }
+// The parent chain of a dof as a bit set: dof_ancmask has bit j set when j is the dof itself or one of its ancestors, and
+// parents have smaller indices, so taking the set bits from the top visits i, parent(i), parent(parent(i)), ... in the
+// order of a walk through dof_parentid - without a dependent global load per hop.
+template <int NV>
+TK_DEV unsigned long long anc_mask(const DM& m, int i) {
+  if (NV > 0 && NV <= 32) return (unsigned long long)m.dof_ancmask_lo[i];
+  return ((unsigned long long)m.dof_ancmask_hi[i] << 32) | (unsigned long long)m.dof_ancmask_lo[i];
+}
+TK_DEV int pop_top(unsigned long long& mk) {
+  int j = 63 - __clzll((long long)mk);
+  mk &= ~(1ull << j);
+  return j;
+}
 TK_DEV bool bad_value(double x) { return !(fabs(x) <= 1e10); }
 
 // ---- per-world workspace (shared memory) ---------------------------------------------------------
@@ -187,6 +213,9 @@ struct WS {
   double *frc_passive, *frc_bias, *frc_act, *frc_smooth, *acc_smooth, *frc_con, *Ma, *Mv, *grad, *Mgrad, *search, *tmpv;
   int ncon, nefc, ecap;
   int work;  // cost evaluations of the line searches of this world so far (a measure of its solver work)
+#ifdef TOKP_STAGE_CLOCKS
+  long long clk; int clk_on;
+#endif
 };
 
 __host__ __device__ inline int ws_imax(int a, int b) { return a > b ? a : b; }
@@ -240,6 +269,9 @@ TK_DEV void ws_init(WS& w, double* base, const DM& m, int ecap, int lanes) {
   w.H = take(nv * nv);
   w.jar = take(ne); w.jv = take(ne); w.efc_force = take(ne); w.quad = take(ws_quad_doubles(ne, lanes));
   w.ncon = 0; w.nefc = 0; w.ecap = ecap; w.work = 0;
+#ifdef TOKP_STAGE_CLOCKS
+  w.clk = 0; w.clk_on = 0;
+#endif
 }
 
 }  // namespace tk

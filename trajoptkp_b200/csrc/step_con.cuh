@@ -150,10 +150,12 @@ TK_DEV void collision(const DM& m, WS& w, const Grp<G, NV>& g, int& status) {
     w.cnt[p] = n;
   }
   g.sync();
+  TK_CLK(w, g, 16);
   if (NV == 0) {
     // convex narrow phase: the pairs that passed the filters, one after the other, all lanes of the group on each
     for (int p = 0; p < m.npair; p++) {
       if (w.cnt[p] < 0) {  // group-uniform: every lane reads the same flag
+        TK_CNT(w, g, 23);
         int g1 = m.pair_geom1[p], g2 = m.pair_geom2[p];
         int t1 = m.geom_type[g1];
         int slot = m.pair_slotadr[p];
@@ -177,6 +179,7 @@ TK_DEV void collision(const DM& m, WS& w, const Grp<G, NV>& g, int& status) {
       }
     }
   }
+  TK_CLK(w, g, 17);
   // ordered compaction (pair order, then contact order), done by one lane: contact counts are tiny
   if (g.gl == 0) {
     int dst = 0;
@@ -216,7 +219,9 @@ TK_DEV void make_kbip(const DM& m, const double* solref_in, const double* solimp
       imp = (x >= 1.0) ? dmax : dmin;
     } else {
       double y;
+      // power 2 (the default solimp) needs no pow(): pow(a, 1) = a and pow(a, 2) = a * a, correctly rounded
       if (power == 1.0) y = x;
+      else if (power == 2.0) y = (x <= mid) ? (1.0 / mid) * (x * x) : 1.0 - (1.0 / (1.0 - mid)) * ((1.0 - x) * (1.0 - x));
       else if (x <= mid) y = (1.0 / pow(mid, power - 1.0)) * pow(x, power);
       else y = 1.0 - (1.0 / pow(1.0 - mid, power - 1.0)) * pow(1.0 - x, power);
       imp = dmin + y * (dmax - dmin);
@@ -230,76 +235,144 @@ TK_DEV void make_kbip(const DM& m, const double* solref_in, const double* solimp
 template <int G, int NV>
 TK_DEV void make_constraint(const DM& m, WS& w, const Grp<G, NV>& g, int& status) {
   const int nv = NV ? NV : m.nv;
-  // 1. row table by one lane (ordered; counts are tiny)
-  if (g.gl == 0) {
-    int r = 0;
-    for (int j = 0; j < m.njnt; j++) {
-      if (!m.jnt_limited[j]) continue;
-      int jt = m.jnt_type[j];
-      if (jt != JNT_HINGE && jt != JNT_SLIDE) continue;
-      double value = w.qpos[m.jnt_qposadr[j]], margin = m.jnt_margin[j];
-      for (int side = -1; side <= 1; side += 2) {
-        double dist = side * (m.jnt_range[2 * j + (side + 1) / 2] - value);
-        if (dist < margin) {
-          if (r >= w.ecap) { status |= ST_OVERFLOW; continue; }
-          w.row_info[r] = row_pack(ROW_LIMIT, j, side);
-          w.efc_pos[r] = dist; w.efc_margin[r] = margin;
+  const int cnt_slot = (m.npair > m.njnt ? m.npair : m.njnt) + 1;
+  // 1. row table: limit rows in joint order (lower side first), then 1 or 4 rows per included contact in contact order.
+  // Lanes take one joint / one contact each and find their first row from ballots over the group; w.con_pair[c] gets
+  // the contact's first row in its upper half (0 = no rows).  Counts that do not fit the row capacity are rare (the
+  // world is then flagged and, below full capacity, re-run): one lane redoes the table in sequence with the
+  // reference's skip rules.
+  const unsigned below = (1u << g.gl) - 1u;
+  int r = 0;
+  bool fits = true;
+  for (int j0 = 0; j0 < m.njnt; j0 += G) {
+    const int j = j0 + g.gl;
+    int bits = 0;
+    double dlo = 0.0, dhi = 0.0, margin = 0.0;
+    if (j < m.njnt && m.jnt_limited[j]) {
+      const int jt = m.jnt_type[j];
+      if (jt == JNT_HINGE || jt == JNT_SLIDE) {
+        const double value = w.qpos[m.jnt_qposadr[j]];
+        margin = m.jnt_margin[j];
+        dlo = -1 * (m.jnt_range[2 * j] - value);
+        dhi = 1 * (m.jnt_range[2 * j + 1] - value);
+        bits = (dlo < margin ? 1 : 0) | (dhi < margin ? 2 : 0);
+      }
+    }
+    const unsigned b0 = g.ballot(bits & 1), b1 = g.ballot(bits & 2);
+    int mine = r + __popc(b0 & below) + __popc(b1 & below);
+    r += __popc(b0) + __popc(b1);
+    if (r <= w.ecap) {
+      if (bits & 1) { w.row_info[mine] = row_pack(ROW_LIMIT, j, -1); w.efc_pos[mine] = dlo; w.efc_margin[mine] = margin; mine++; }
+      if (bits & 2) { w.row_info[mine] = row_pack(ROW_LIMIT, j, 1); w.efc_pos[mine] = dhi; w.efc_margin[mine] = margin; }
+    } else {
+      fits = false;
+    }
+  }
+  for (int c0 = 0; c0 < w.ncon && fits; c0 += G) {
+    const int c = c0 + g.gl;
+    int rows = 0, pr = 0;
+    double inc = 0.0;
+    if (c < w.ncon) {
+      pr = w.con_pair[c];
+      ConParam cp;
+      contact_param(m, m.pair_geom1[pr], m.pair_geom2[pr], cp);
+      inc = cp.margin - cp.gap;
+      if (w.con_dist[c] < inc) {  // otherwise excluded (in the gap)
+        rows = cp.dim == 1 ? 1 : (cp.dim == 3 ? 4 : 0);
+        if (rows == 0) status |= ST_UNSUPPORTED;
+      }
+    }
+    const unsigned b1 = g.ballot(rows == 1), b4 = g.ballot(rows == 4);
+    const int mine = r + __popc(b1 & below) + 4 * __popc(b4 & below);
+    r += __popc(b1) + 4 * __popc(b4);
+    if (r <= w.ecap) {
+      if (c < w.ncon) w.con_pair[c] = pr | ((rows ? mine + 1 : 0) << 16);
+      for (int k = 0; k < rows; k++) {
+        w.row_info[mine + k] = row_pack(rows == 1 ? ROW_FRICTIONLESS : ROW_PYRAMIDAL, c, k);
+        w.efc_pos[mine + k] = w.con_dist[c]; w.efc_margin[mine + k] = inc;
+      }
+    } else {
+      fits = false;
+    }
+  }
+  g.sync();
+  if (!fits) {
+    if (g.gl == 0) {
+      r = 0;
+      for (int j = 0; j < m.njnt; j++) {
+        if (!m.jnt_limited[j]) continue;
+        int jt = m.jnt_type[j];
+        if (jt != JNT_HINGE && jt != JNT_SLIDE) continue;
+        double value = w.qpos[m.jnt_qposadr[j]], margin = m.jnt_margin[j];
+        for (int side = -1; side <= 1; side += 2) {
+          double dist = side * (m.jnt_range[2 * j + (side + 1) / 2] - value);
+          if (dist < margin) {
+            if (r >= w.ecap) { status |= ST_OVERFLOW; continue; }
+            w.row_info[r] = row_pack(ROW_LIMIT, j, side);
+            w.efc_pos[r] = dist; w.efc_margin[r] = margin;
+            r++;
+          }
+        }
+      }
+      for (int c = 0; c < w.ncon; c++) {
+        int pr = w.con_pair[c] & 0xffff;
+        w.con_pair[c] = pr;
+        ConParam cp;
+        contact_param(m, m.pair_geom1[pr], m.pair_geom2[pr], cp);
+        double inc = cp.margin - cp.gap;
+        if (w.con_dist[c] >= inc) continue;  // excluded (in the gap)
+        int rows = cp.dim == 1 ? 1 : (cp.dim == 3 ? 4 : -1);
+        if (rows < 0) { status |= ST_UNSUPPORTED; continue; }
+        if (r + rows > w.ecap) { status |= ST_OVERFLOW; continue; }
+        w.con_pair[c] = pr | ((r + 1) << 16);
+        for (int k = 0; k < rows; k++) {
+          w.row_info[r] = row_pack(rows == 1 ? ROW_FRICTIONLESS : ROW_PYRAMIDAL, c, k);
+          w.efc_pos[r] = w.con_dist[c]; w.efc_margin[r] = inc;
           r++;
         }
       }
+      w.cnt[cnt_slot] = r;
     }
-    for (int c = 0; c < w.ncon; c++) {
-      int p = w.con_pair[c];
-      int g1 = m.pair_geom1[p], g2 = m.pair_geom2[p];
-      ConParam cp;
-      contact_param(m, g1, g2, cp);
-      double inc = cp.margin - cp.gap;
-      if (w.con_dist[c] >= inc) continue;  // excluded (in the gap)
-      int rows = cp.dim == 1 ? 1 : (cp.dim == 3 ? 4 : -1);
-      if (rows < 0) { status |= ST_UNSUPPORTED; continue; }
-      if (r + rows > w.ecap) { status |= ST_OVERFLOW; continue; }
-      for (int k = 0; k < rows; k++) {
-        w.row_info[r] = row_pack(rows == 1 ? ROW_FRICTIONLESS : ROW_PYRAMIDAL, c, k);
-        w.efc_pos[r] = w.con_dist[c]; w.efc_margin[r] = inc;
-        r++;
-      }
-    }
-    w.cnt[(m.npair > m.njnt ? m.npair : m.njnt) + 1] = r;
+    g.sync();
+    r = w.cnt[cnt_slot];
   }
-  g.sync();
-  int nefc = w.cnt[(m.npair > m.njnt ? m.npair : m.njnt) + 1];
+  const int nefc = r;
   w.nefc = nefc;
-  // 2. Jacobian entries: lanes over (row, dof)
+  // 2. Jacobian: limit rows are +-1 at the joint's dof; a contact's rows share the difference of the two bodies' point
+  // Jacobians, computed once per (contact, dof) (mj_makeConstraint builds the pyramid edges from one contact Jacobian)
   for (int e = g.gl; e < nefc * nv; e += G) {
-    int r = e / nv, i = e - r * nv;
-    double val = 0.0;
-    const int info = w.row_info[r], rtype = row_type_of(info);
-    if (rtype == ROW_LIMIT) {
-      int j = row_id_of(info);
-      if (m.jnt_dofadr[j] == i) val = (double)(-row_sub_of(info));
+    const int rr = e / nv, i = e - rr * nv;
+    const int info = w.row_info[rr];
+    if (row_type_of(info) != ROW_LIMIT) break;  // limit rows come first
+    w.J[e] = (m.jnt_dofadr[row_id_of(info)] == i) ? (double)(-row_sub_of(info)) : 0.0;
+  }
+  for (int e = g.gl; e < w.ncon * nv; e += G) {
+    const int c = e / nv, i = e - c * nv;
+    const int packed = w.con_pair[c], row0 = (packed >> 16) - 1;
+    if (row0 < 0) continue;
+    const int pr = packed & 0xffff;
+    const int g1 = m.pair_geom1[pr], g2 = m.pair_geom2[pr];
+    double c1[3], c2[3], d[3];
+    jac_col(m, w, c1, &w.con_pos[3 * c], m.geom_bodyid[g1], i);
+    jac_col(m, w, c2, &w.con_pos[3 * c], m.geom_bodyid[g2], i);
+    d[0] = c2[0] - c1[0]; d[1] = c2[1] - c1[1]; d[2] = c2[2] - c1[2];
+    const double* f = &w.con_frame[6 * c];
+    const double jn = f[0] * d[0] + f[1] * d[1] + f[2] * d[2];
+    if (row_type_of(w.row_info[row0]) == ROW_FRICTIONLESS) {
+      w.J[row0 * nv + i] = jn;
     } else {
-      int c = row_id_of(info), p = w.con_pair[c];
-      int g1 = m.pair_geom1[p], g2 = m.pair_geom2[p];
-      double c1[3], c2[3], d[3];
-      jac_col(m, w, c1, &w.con_pos[3 * c], m.geom_bodyid[g1], i);
-      jac_col(m, w, c2, &w.con_pos[3 * c], m.geom_bodyid[g2], i);
-      d[0] = c2[0] - c1[0]; d[1] = c2[1] - c1[1]; d[2] = c2[2] - c1[2];
-      const double* f = &w.con_frame[6 * c];
-      double jn = f[0] * d[0] + f[1] * d[1] + f[2] * d[2];
-      if (rtype == ROW_FRICTIONLESS) {
-        val = jn;
-      } else {
-        int k = row_sub_of(info);      // 0:+t1 1:-t1 2:+t2 3:-t2
-        double ft[3] = {f[3], f[4], f[5]};
-        if (k >= 2) cross3(ft, f, f + 3);
-        double jt = ft[0] * d[0] + ft[1] * d[1] + ft[2] * d[2];
-        double mu = fmax(m.geom_friction[3 * g1], m.geom_friction[3 * g2]);
-        if (m.geom_priority[g1] != m.geom_priority[g2])
-          mu = m.geom_friction[3 * (m.geom_priority[g1] > m.geom_priority[g2] ? g1 : g2)];
-        val = (k & 1) ? (jn - mu * jt) : (jn + mu * jt);
-      }
+      double t2[3];
+      cross3(t2, f, f + 3);
+      const double jt1 = f[3] * d[0] + f[4] * d[1] + f[5] * d[2];
+      const double jt2 = t2[0] * d[0] + t2[1] * d[1] + t2[2] * d[2];
+      double mu = fmax(m.geom_friction[3 * g1], m.geom_friction[3 * g2]);
+      if (m.geom_priority[g1] != m.geom_priority[g2])
+        mu = m.geom_friction[3 * (m.geom_priority[g1] > m.geom_priority[g2] ? g1 : g2)];
+      w.J[row0 * nv + i] = jn + mu * jt1;        // rows: +t1, -t1, +t2, -t2
+      w.J[(row0 + 1) * nv + i] = jn - mu * jt1;
+      w.J[(row0 + 2) * nv + i] = jn + mu * jt2;
+      w.J[(row0 + 3) * nv + i] = jn - mu * jt2;
     }
-    w.J[e] = val;
   }
   // 3. per-row impedance and regularisation
   for (int r = g.gl; r < nefc; r += G) {
@@ -311,7 +384,7 @@ TK_DEV void make_constraint(const DM& m, WS& w, const Grp<G, NV>& g, int& status
       diag = m.dof_invweight0[m.jnt_dofadr[j]];
       Rr = fmax(kMinVal, (1.0 - imp) * diag / imp);
     } else {
-      int c = row_id_of(info), p = w.con_pair[c];
+      int c = row_id_of(info), p = w.con_pair[c] & 0xffff;
       int g1 = m.pair_geom1[p], g2 = m.pair_geom2[p];
       ConParam cp;
       contact_param(m, g1, g2, cp);

@@ -322,6 +322,7 @@ TK_DEV void fwd_constraint(const DM& m, WS& w, const Grp<G, NV>& g, int iteratio
     }
     gauss = 0.5 * g.sum(gsum);
     cost = c + gauss;
+    TK_CLK(w, g, 7); TK_CNT(w, g, 20);
     if (same_factor) {
       // keep the factor
     } else if (tri) {
@@ -341,6 +342,7 @@ TK_DEV void fwd_constraint(const DM& m, WS& w, const Grp<G, NV>& g, int iteratio
       for (int k = 0; k < TRI_MAX; k++)
         if (k < tm.cnt) w.H[tm.ei[k] * nv + tm.ej[k]] = h[k];
       g.sync();
+      TK_CLK(w, g, 8); TK_CNT(w, g, 21);
       chol_factor_tri(w.H, nv, g, tm);
     } else {
       for (int e = g.gl; e < nv * nv; e += G) {
@@ -354,10 +356,12 @@ TK_DEV void fwd_constraint(const DM& m, WS& w, const Grp<G, NV>& g, int iteratio
       g.sync();
       chol_factor(w.H, nv, g);
     }
+    TK_CLK(w, g, 9);
     if (nv <= G) chol_solve_reg(w.H, nv, w.Mgrad, w.grad, g);
     else chol_solve(w.H, nv, w.Mgrad, w.grad, g);
     for (int i = g.gl; i < nv; i += G) w.search[i] = -w.Mgrad[i];
     g.sync();
+    TK_CLK(w, g, 10);
   };
   if (!has) {
     for (int i = g.gl; i < nv; i += G) { w.qacc[i] = w.acc_smooth[i]; w.warm[i] = w.acc_smooth[i]; w.frc_con[i] = 0.0; }
@@ -387,6 +391,7 @@ TK_DEV void fwd_constraint(const DM& m, WS& w, const Grp<G, NV>& g, int iteratio
     }
     g.sync();
   }
+  TK_CLK(w, g, 6);
   double scale = 1.0 / (m.meaninertia * (double)max(1, nv));
   // iter == -1 is the initial update(); sharing the call site keeps one copy of the Hessian/Cholesky code and lets
   // all running worlds of the warp execute it together
@@ -404,6 +409,7 @@ TK_DEV void fwd_constraint(const DM& m, WS& w, const Grp<G, NV>& g, int iteratio
           g.sync();
         }
         oldcost = cost;
+        TK_CLK(w, g, 12);
         update();
         if (iter >= 0) {
           double gn = 0.0;
@@ -416,7 +422,9 @@ TK_DEV void fwd_constraint(const DM& m, WS& w, const Grp<G, NV>& g, int iteratio
         if (iter >= iterations) run = false;
       }
     }
-    alpha = primal_search(m, w, g, gauss, tolerance, run);
+    TK_CLK(w, g, 12);
+      alpha = primal_search(m, w, g, gauss, tolerance, run);
+    TK_CLK(w, g, 11);
   }
   if (has) {
     for (int i = g.gl; i < nv; i += G) w.warm[i] = w.qacc[i];
@@ -485,13 +493,18 @@ TK_DEV void step_position(const DM& m, WS& w, const Grp<G, NV>& g, int& status) 
   kinematics(m, w, g);
   com_pos(m, w, g);
   g.phase();
+  TK_CLK(w, g, 0);
   crb_factor(m, w, g);
+  TK_CLK(w, g, 15);
   factor_ldl(m, w.M, w.LD, w.LDinv, g);
   g.phase();
+  TK_CLK(w, g, 1);
   collision(m, w, g, status);
   g.phase();
+  TK_CLK(w, g, 2);
   make_constraint(m, w, g, status);
   g.phase();
+  TK_CLK(w, g, 3);
 }
 
 // velocity stage + actuation + smooth acceleration (mj_fwdVelocity, mj_fwdActuation, mj_fwdAcceleration)
@@ -500,8 +513,10 @@ TK_DEV void step_velocity(const DM& m, WS& w, const Grp<G, NV>& g) {
   com_vel(m, w, g);
   passive_and_bias(m, w, g);
   g.phase();
+  TK_CLK(w, g, 4);
   reference_constraint(m, w, g);
   actuation_acceleration(m, w, g);
+  TK_CLK(w, g, 5);
 }
 
 // the part of a step after the smooth acceleration, with the Euler factor either computed here (share = nullptr) or
@@ -523,7 +538,9 @@ TK_DEV void step_constrained(const DM& m, WS& w, const Grp<G, NV>& g, int iterat
   fwd_constraint(m, w, g, iterations, tolerance);
   g.phase();
   for (int i = g.gl; i < m.nv; i += G) if (bad_value(w.qacc[i])) status |= ST_BAD_QACC;
+  TK_CLK(w, g, 12);
   euler(m, w, g, time);
+  TK_CLK(w, g, 13);
 }
 
 // one full step (mj_step).  `iterations`/`tolerance`: solver options of this launch.

@@ -67,6 +67,7 @@ TK_DEV void kinematics(const DM& m, WS& w, const Grp<G, NV>& g) {
       for (int k = 0; k < 3; k++) w.xipos[3 * i + k] = xpos[k] + v[k];
     }
     g.sync();
+    TK_CLK(w, g, 23 + (depth < 4 ? depth : 4));
   }
 }
 
@@ -180,7 +181,9 @@ TK_DEV void crb_factor(const DM& m, WS& w, const Grp<G, NV>& g) {
   for (int i = g.gl; i < nv; i += G) {
     double buf[6];
     mul_inert_vec(buf, &w.crb[10 * m.dof_bodyid[i]], &w.cdof[6 * i]);
-    for (int j = i; j >= 0; j = m.dof_parentid[j]) {
+    unsigned long long chain = anc_mask<NV>(m, i);
+    while (chain) {
+      const int j = pop_top(chain);
       const double* c = &w.cdof[6 * j];
       double v = c[0] * buf[0] + c[1] * buf[1] + c[2] * buf[2] + c[3] * buf[3] + c[4] * buf[4] + c[5] * buf[5];
       if (j == i) w.M[i * nv + i] = m.dof_armature[i] + v;
@@ -200,16 +203,25 @@ TK_DEV void factor_ldl(const DM& m, const double* A, double* LD, double* dinv, c
   for (int k = nv - 1; k >= 0; k--) {
     double Mkk = LD[k * nv + k];
     if (Mkk < kMinVal) Mkk = kMinVal;
-    unsigned lo = m.dof_ancmask_lo[k], hi = m.dof_ancmask_hi[k];
-    // each ancestor i of k updates its own row; row k is only read
+    const unsigned long long anck = anc_mask<NV>(m, k);
+    // each ancestor i of k updates its own row; row k is only read.  The quotient is also the new LD[k][i]: the lane
+    // keeps it for its first row and writes it once the other lanes have read the old value
+    double a0 = 0.0;
+    bool have0 = false;
     for (int i = g.gl; i < k; i += G) {
-      if (!in_mask(lo, hi, i)) continue;
+      if (!((anck >> i) & 1ull)) continue;
       double a = LD[k * nv + i] / Mkk;
-      for (int j = i; j >= 0; j = m.dof_parentid[j]) LD[i * nv + j] -= a * LD[k * nv + j];
+      if (i == g.gl) { a0 = a; have0 = true; }
+      unsigned long long chain = anc_mask<NV>(m, i);
+      while (chain) {
+        const int j = pop_top(chain);
+        LD[i * nv + j] -= a * LD[k * nv + j];
+      }
     }
     g.sync();
-    for (int i = g.gl; i < k; i += G)
-      if (in_mask(lo, hi, i)) LD[k * nv + i] = LD[k * nv + i] / Mkk;
+    if (have0) LD[k * nv + g.gl] = a0;
+    for (int i = g.gl + G; i < k; i += G)
+      if ((anck >> i) & 1ull) LD[k * nv + i] = LD[k * nv + i] / Mkk;
     if (g.gl == 0) { LD[k * nv + k] = Mkk; dinv[k] = 1.0 / Mkk; }
     g.sync();
   }
@@ -224,9 +236,9 @@ TK_DEV void solve_ldl(const DM& m, const double* LD, const double* dinv, double*
   for (int i = nv - 1; i > 0; i--) {
     double xi = x[i];
     if (xi != 0.0) {
-      unsigned lo = m.dof_ancmask_lo[i], hi = m.dof_ancmask_hi[i];
+      const unsigned long long anci = anc_mask<NV>(m, i);
       for (int j = g.gl; j < i; j += G)
-        if (in_mask(lo, hi, j)) x[j] -= LD[i * nv + j] * xi;
+        if ((anci >> j) & 1ull) x[j] -= LD[i * nv + j] * xi;
     }
     g.sync();
   }
@@ -256,7 +268,11 @@ TK_DEV void solve_ldl(const DM& m, const double* LD, const double* dinv, double*
         if (depth[k] != d) continue;
         const int i = g.gl + k * G;
         double s = x[i];
-        for (int j = m.dof_parentid[i]; j >= 0; j = m.dof_parentid[j]) s -= LD[i * nv + j] * x[j];
+        unsigned long long chain = anc_mask<NV>(m, i) & ~(1ull << i);
+        while (chain) {
+          const int j = pop_top(chain);
+          s -= LD[i * nv + j] * x[j];
+        }
         x[i] = s;
       }
       g.sync();

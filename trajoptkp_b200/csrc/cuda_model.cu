@@ -115,7 +115,7 @@ int ensure_device_model(const tokp_model* mc, const DM** out) {
   AI(body_parentid) AI(body_rootid) AI(body_weldid) AI(body_jntadr) AI(body_jntnum) AI(body_dofadr) AI(body_dofnum)
   AI(body_depth) AI(body_subtreemask_lo) AI(body_subtreemask_hi)
   AI(jnt_type) AI(jnt_qposadr) AI(jnt_dofadr) AI(jnt_bodyid) AI(jnt_limited)
-  AI(dof_bodyid) AI(dof_jntid) AI(dof_parentid) AI(dof_ancmask_lo) AI(dof_ancmask_hi)
+  AI(dof_bodyid) AI(dof_jntid) AI(dof_parentid) AI(dof_ancmask_lo) AI(dof_ancmask_hi) AI(dof_treelast)
   AI(geom_type) AI(geom_bodyid) AI(geom_condim) AI(geom_priority) AI(pair_geom1) AI(pair_geom2) AI(pair_slotadr) AI(geom_meshadr) AI(geom_meshnum)
   AI(actuator_trnid) AI(actuator_dofadr) AI(actuator_ctrllimited) AI(actuator_forcelimited) AI(actuator_biastype)
   AR(qpos0) AR(body_pos) AR(body_quat) AR(body_ipos) AR(body_iquat) AR(body_mass) AR(body_inertia) AR(body_invweight0)
@@ -160,6 +160,10 @@ int ensure_device_model(const tokp_model* mc, const DM** out) {
   for (size_t p = 0; p < h.pair_geom1.size(); p++) {
     int t1 = h.geom_type[h.pair_geom1[p]], t2 = h.geom_type[h.pair_geom2[p]];
     if (!(t1 == GEOM_PLANE && (t2 == GEOM_SPHERE || t2 == GEOM_CAPSULE || t2 == GEOM_BOX))) dm.spec_nv = 0;
+  }
+  dm.max_tree_dofs = 0;
+  for (int d = 0; d < dm.nv; d++) {  // a tree's first dof has no parent
+    if (h.dof_parentid[d] < 0 && h.dof_treelast[d] - d + 1 > dm.max_tree_dofs) dm.max_tree_dofs = h.dof_treelast[d] - d + 1;
   }
   dm.any_damping = 0; dm.any_gravcomp = 0;
   for (double v : h.dof_damping) if (v > 0) dm.any_damping = 1;

@@ -23,6 +23,8 @@ struct DM {
   const int *jnt_type, *jnt_qposadr, *jnt_dofadr, *jnt_bodyid, *jnt_limited;
   const int *dof_bodyid, *dof_jntid, *dof_parentid;
   const unsigned *dof_ancmask_lo, *dof_ancmask_hi;
+  const int* dof_treelast;  // last dof of the dof's kinematic tree
+  int max_tree_dofs;        // dofs of the largest kinematic tree (= nv for a single tree)
   const int *geom_type, *geom_bodyid, *geom_condim, *geom_priority, *pair_geom1, *pair_geom2, *pair_slotadr, *geom_meshadr, *geom_meshnum;
   const int *actuator_trnid, *actuator_dofadr, *actuator_ctrllimited, *actuator_forcelimited, *actuator_biastype;
   // real arrays

@@ -785,6 +785,18 @@ struct Compiler {
       m.dof_ancmask_lo[d] = (int32_t)(uint32_t)(mask & 0xffffffffull);
       m.dof_ancmask_hi[d] = (int32_t)(uint32_t)(mask >> 32);
     }
+    // last dof of each dof's kinematic tree (bodies are in depth-first order, so a tree's dofs are one index range)
+    m.dof_treelast.assign(nv, 0);
+    {
+      std::vector<int> root(nv), last(nv, -1);
+      for (int d = 0; d < nv; d++) {
+        int r = d;
+        while (m.dof_parentid[r] >= 0) r = m.dof_parentid[r];
+        root[d] = r;
+        if (d > last[r]) last[r] = d;
+      }
+      for (int d = 0; d < nv; d++) m.dof_treelast[d] = last[root[d]];
+    }
     treedepth_ = maxdepth;
   }
   int treedepth_ = 0;

@@ -25,6 +25,7 @@ enum GeomType { GEOM_PLANE = 0, GEOM_HFIELD = 1, GEOM_SPHERE = 2, GEOM_CAPSULE =
   X(jnt_type) X(jnt_qposadr) X(jnt_dofadr) X(jnt_bodyid) X(jnt_limited)                            \
   X(dof_bodyid) X(dof_jntid) X(dof_parentid)                                                       \
   X(dof_ancmask_lo) X(dof_ancmask_hi) /* bit j set: dof j is dof i or one of its ancestors */      \
+  X(dof_treelast) /* last dof of the kinematic tree of dof i (trees are contiguous dof ranges) */   \
   X(geom_type) X(geom_bodyid) X(geom_contype) X(geom_conaffinity) X(geom_condim)                   \
   X(geom_priority) X(geom_meshadr) X(geom_meshnum)                                                 \
   X(pair_geom1) X(pair_geom2) X(pair_slotadr) /* first contact slot of the pair (prefix of its maximum contacts) */ \

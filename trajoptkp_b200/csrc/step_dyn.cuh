@@ -206,7 +206,16 @@ TK_DEV void chol_factor_tri(double* H, int n, const Grp<G, NV>& g, const TriMap<
   }
 }
 
-// in-place dense Cholesky (lower) of the nv x nv matrix in w.H, right-looking, lanes over the trailing block
+// Walk over the entries of a lower triangle in row-major order (entry e = row * (row + 1) / 2 + col, col <= row), G
+// entries at a time: no integer division, no iterations spent on the upper triangle.
+struct TriWalk {
+  int row, col;
+  TK_DEV explicit TriWalk(int first) : row(0), col(first) { settle(); }
+  TK_DEV void settle() { while (col > row) { col -= row + 1; row++; } }
+  TK_DEV void advance(int by) { col += by; settle(); }
+};
+
+// in-place dense Cholesky (lower) of the nv x nv matrix in w.H, right-looking, lanes over the trailing triangle
 template <int G, int NV>
 TK_DEV void chol_factor(double* H, int n, const Grp<G, NV>& g) {
 #pragma unroll 1
@@ -218,10 +227,11 @@ TK_DEV void chol_factor(double* H, int n, const Grp<G, NV>& g) {
     g.sync();
     for (int i = j + g.gl; i < n; i += G) H[i * n + j] = (i == j) ? d : H[i * n + j] * inv;
     g.sync();
-    int rem = n - j - 1;
-    for (int e = g.gl; e < rem * rem; e += G) {
-      int i = j + 1 + e / rem, k = j + 1 + e % rem;
-      if (k <= i) H[i * n + k] -= H[i * n + j] * H[k * n + j];
+    const int rem = n - j - 1, ntri = rem * (rem + 1) / 2;
+    TriWalk t(g.gl);
+    for (int e = g.gl; e < ntri; e += G, t.advance(G)) {
+      const int i = j + 1 + t.row, k = j + 1 + t.col;
+      H[i * n + k] -= H[i * n + j] * H[k * n + j];
     }
     g.sync();
   }
@@ -281,6 +291,34 @@ namespace tk {
 
 // mj_fwdConstraint with the Newton solver.  The Newton and line-search loops are warp-uniform (Grp::any_warp): every
 // running world of the warp passes through them together; worlds without constraints or already converged idle.
+// chol_solve_reg for G < n <= 2 G: two entries of x per lane (rows gl and gl + G)
+template <int G, int NV>
+TK_DEV void chol_solve_reg2(const double* L, int n, double* x, const double* b, const Grp<G, NV>& g) {
+  const int i0 = g.gl, i1 = g.gl + G;
+  const bool m1 = i1 < n;  // i0 < G < n always
+  double x0 = b[i0], x1 = m1 ? b[i1] : 0.0;
+  const double d0 = 1.0 / L[i0 * n + i0], d1 = m1 ? 1.0 / L[i1 * n + i1] : 0.0;
+#pragma unroll 1
+  for (int j = 0; j < n; j++) {
+    const bool lowj = j < G;
+    const double xj = __shfl_sync(g.mask, lowj ? x0 * d0 : x1 * d1, j & (G - 1), G);
+    if (lowj) { if (i0 == j) x0 = xj; else if (i0 > j) x0 -= L[i0 * n + j] * xj; }
+    if (!lowj && i1 == j) x1 = xj;
+    else if (m1 && i1 > j) x1 -= L[i1 * n + j] * xj;
+  }
+#pragma unroll 1
+  for (int j = n - 1; j >= 0; j--) {
+    const bool lowj = j < G;
+    const double xj = __shfl_sync(g.mask, lowj ? x0 * d0 : x1 * d1, j & (G - 1), G);
+    if (!lowj) { if (i1 == j) x1 = xj; else if (i1 < j) x1 -= L[j * n + i1] * xj; }
+    if (lowj && i0 == j) x0 = xj;
+    else if (i0 < j) x0 -= L[j * n + i0] * xj;
+  }
+  x[i0] = x0;
+  if (m1) x[i1] = x1;
+  g.sync();
+}
+
 template <int G, int NV>
 TK_DEV void fwd_constraint(const DM& m, WS& w, const Grp<G, NV>& g, int iterations, double tolerance) {
   const int nv = NV ? NV : m.nv, nefc = w.nefc;
@@ -345,19 +383,21 @@ TK_DEV void fwd_constraint(const DM& m, WS& w, const Grp<G, NV>& g, int iteratio
       TK_CLK(w, g, 8); TK_CNT(w, g, 21);
       chol_factor_tri(w.H, nv, g, tm);
     } else {
-      for (int e = g.gl; e < nv * nv; e += G) {
-        int i = e / nv, j = e - i * nv;
-        if (j > i) continue;
-        double h = w.M[e];
+      TriWalk t(g.gl);
+      for (int e = g.gl; e < nv * (nv + 1) / 2; e += G, t.advance(G)) {
+        const int i = t.row, j = t.col;
+        double h = w.M[i * nv + j];
         for (int r = 0; r < nefc; r++)
           if (w.efc_force[r] != 0.0) h += w.efc_D[r] * w.J[r * nv + i] * w.J[r * nv + j];
-        w.H[e] = h;
+        w.H[i * nv + j] = h;
       }
       g.sync();
+      TK_CLK(w, g, 8); TK_CNT(w, g, 21);
       chol_factor(w.H, nv, g);
     }
     TK_CLK(w, g, 9);
     if (nv <= G) chol_solve_reg(w.H, nv, w.Mgrad, w.grad, g);
+    else if (nv <= 2 * G) chol_solve_reg2(w.H, nv, w.Mgrad, w.grad, g);
     else chol_solve(w.H, nv, w.Mgrad, w.grad, g);
     for (int i = g.gl; i < nv; i += G) w.search[i] = -w.Mgrad[i];
     g.sync();

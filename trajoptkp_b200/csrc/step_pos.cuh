@@ -199,6 +199,49 @@ TK_DEV void factor_ldl(const DM& m, const double* A, double* LD, double* dinv, c
   const int nv = NV ? NV : m.nv;
   for (int e = g.gl; e < nv * nv; e += G) LD[e] = A[e];
   g.sync();
+  if (NV == 0 && m.max_tree_dofs < nv) {
+    // several kinematic trees (an arm and free bodies): M is block diagonal over them and the elimination of one
+    // tree never touches another, so trip t eliminates dof treelast - t of EVERY tree at once - as many trips as the
+    // largest tree has dofs instead of nv, every entry through the same operations as in the sequential order
+#pragma unroll 1
+    for (int t = 0; t < m.max_tree_dofs; t++) {
+      double a0 = 0.0;
+      bool have0 = false;
+      for (int i = g.gl; i < nv; i += G) {
+        const int k = m.dof_treelast[i] - t;
+        if (k <= i) continue;
+        if (!((anc_mask<NV>(m, k) >> i) & 1ull)) continue;
+        double Mkk = LD[k * nv + k];
+        if (Mkk < kMinVal) Mkk = kMinVal;
+        double a = LD[k * nv + i] / Mkk;
+        if (i == g.gl) { a0 = a; have0 = true; }
+        unsigned long long chain = anc_mask<NV>(m, i);
+        while (chain) {
+          const int j = pop_top(chain);
+          LD[i * nv + j] -= a * LD[k * nv + j];
+        }
+      }
+      g.sync();
+      for (int i = g.gl; i < nv; i += G) {
+        const int k = m.dof_treelast[i] - t;
+        if (k == i) {  // this trip's dof of the tree: clamp the pivot, keep its inverse
+          double Mkk = LD[k * nv + k];
+          if (Mkk < kMinVal) Mkk = kMinVal;
+          LD[k * nv + k] = Mkk; dinv[k] = 1.0 / Mkk;
+        } else if (k > i && ((anc_mask<NV>(m, k) >> i) & 1ull)) {
+          if (i == g.gl && have0) {
+            LD[k * nv + i] = a0;
+          } else {
+            double Mkk = LD[k * nv + k];
+            if (Mkk < kMinVal) Mkk = kMinVal;
+            LD[k * nv + i] = LD[k * nv + i] / Mkk;
+          }
+        }
+      }
+      g.sync();
+    }
+    return;
+  }
 #pragma unroll 1
   for (int k = nv - 1; k >= 0; k--) {
     double Mkk = LD[k * nv + k];
@@ -231,16 +274,28 @@ TK_DEV void factor_ldl(const DM& m, const double* A, double* LD, double* dinv, c
 template <int G, int NV>
 TK_DEV void solve_ldl(const DM& m, const double* LD, const double* dinv, double* x, const Grp<G, NV>& g) {
   const int nv = NV ? NV : m.nv;
-  // x <- inv(L') x : once x[i] is final, push it to its ancestors
+  // x <- inv(L') x : once x[i] is final, push it to its ancestors (several trees: one dof of every tree per trip, see
+  // factor_ldl)
+  if (NV == 0 && m.max_tree_dofs < nv) {
 #pragma unroll 1
-  for (int i = nv - 1; i > 0; i--) {
-    double xi = x[i];
-    if (xi != 0.0) {
-      const unsigned long long anci = anc_mask<NV>(m, i);
-      for (int j = g.gl; j < i; j += G)
-        if ((anci >> j) & 1ull) x[j] -= LD[i * nv + j] * xi;
+    for (int t = 0; t < m.max_tree_dofs - 1; t++) {
+      for (int j = g.gl; j < nv; j += G) {
+        const int i = m.dof_treelast[j] - t;
+        if (i > j && ((anc_mask<NV>(m, i) >> j) & 1ull)) x[j] -= LD[i * nv + j] * x[i];
+      }
+      g.sync();
     }
-    g.sync();
+  } else {
+#pragma unroll 1
+    for (int i = nv - 1; i > 0; i--) {
+      double xi = x[i];
+      if (xi != 0.0) {
+        const unsigned long long anci = anc_mask<NV>(m, i);
+        for (int j = g.gl; j < i; j += G)
+          if ((anci >> j) & 1ull) x[j] -= LD[i * nv + j] * xi;
+      }
+      g.sync();
+    }
   }
   for (int i = g.gl; i < nv; i += G) x[i] *= dinv[i];
   g.sync();

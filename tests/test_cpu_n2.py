@@ -184,3 +184,36 @@ def test_unsupported_pairs_fail_at_load_time(built):
     rc = capi.lib().tokp_model_compile_string(xml.encode(), b".", 0.01, C.byref(h))
     assert rc == 2  # TOKP_ERR_MODEL
     assert b"unsupported collision pair" in capi.lib().tokp_last_error()
+
+
+def _compile_rc(xml, base=b"."):
+    import ctypes as C
+    h = C.c_void_p()
+    rc = capi.lib().tokp_model_compile_string(xml.encode(), base, 0.01, C.byref(h))
+    return rc, capi.lib().tokp_last_error()
+
+
+def test_dynamics_outside_the_subset_fail_at_load_time(built):
+    """frictionloss / joint springs / tendons / equality constraints change the dynamics and are not
+    modelled by the step; a model that uses them must not load as if they were absent."""
+    body = '<body pos="0 0 1"><joint type="hinge" axis="0 1 0" %s/><geom type="sphere" size="0.1"/></body>'
+    ok = "<mujoco><worldbody>%s</worldbody></mujoco>" % (body % 'damping="0.1"')
+    assert _compile_rc(ok)[0] == 0
+    for attr in ('frictionloss="0.2"', 'stiffness="3"'):
+        rc, err = _compile_rc("<mujoco><worldbody>%s</worldbody></mujoco>" % (body % attr))
+        assert rc == 2 and b"outside the supported subset" in err, (attr, err)
+    # a default class nobody uses may carry the attribute (the Franka scenes' panda_overlay does)
+    unused = '<mujoco><default><default class="x"><joint frictionloss="10"/></default></default><worldbody>%s</worldbody></mujoco>'
+    assert _compile_rc(unused % (body % ""))[0] == 0
+    for section in ('<tendon><fixed name="t"/></tendon>', '<equality><weld body1="a"/></equality>'):
+        rc, err = _compile_rc("<mujoco><worldbody>%s</worldbody>%s</mujoco>" % (body % "", section))
+        assert rc == 2 and b"outside the supported subset" in err, (section, err)
+
+
+def test_obj_face_index_outside_the_vertex_list_is_rejected(built, tmp_path):
+    """read_obj used the indices unchecked (out-of-bounds read in the inertia pass)."""
+    (tmp_path / "bad.obj").write_text("v 0 0 0\nv 1 0 0\nv 0 1 0\nv 0 0 1\nf 1 2 3\nf 1 2 4\nf 1 3 4\nf 2 3 9\n")
+    xml = ('<mujoco><asset><mesh name="m" file="bad.obj"/></asset><worldbody><geom type="plane" size="1 1 1"/>'
+           '<body pos="0 0 1"><freejoint/><geom type="mesh" mesh="m"/></body></worldbody></mujoco>')
+    rc, err = _compile_rc(xml, str(tmp_path).encode())
+    assert rc == 2 and b"face index outside" in err, err

@@ -72,12 +72,13 @@ int plan_launch(const DM& dm, int G, int pass, LaunchPlan* out) {
   if (best == 0) { set_error("model too large for the shared-memory workspace"); return TOKP_ERR_UNSUPPORTED; }
   p.warps = best; p.worlds_per_block = best * p.gpw; p.smem = per_world * best * p.gpw;
   {
-    static int sm_count = 0;
-    if (!sm_count) {
-      int dev = 0;
-      cudaGetDevice(&dev);
-      if (cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sm_count <= 0) sm_count = 148;
-    }
+    static int sm_counts[64] = {0};  // per device
+    int dev = 0;
+    cudaGetDevice(&dev);
+    int& sm_count = sm_counts[dev & 63];
+    if (!sm_count &&
+        (cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sm_count <= 0))
+      sm_count = 148;
     int resident = (int)(sm_bytes / (p.smem + block_overhead));
     if (resident > 32) resident = 32;
     if (resident * best > reg_warps) resident = reg_warps / best;
@@ -91,7 +92,17 @@ int plan_launch(const DM& dm, int G, int pass, LaunchPlan* out) {
 int ensure_device_model(const tokp_model* mc, const DM** out) {
   tokp_model* m = const_cast<tokp_model*>(mc);
   std::lock_guard<std::mutex> lock(g_upload_mutex);
-  if (m->dev) { *out = &m->dev->dm; return TOKP_OK; }
+  if (m->dev) {
+    int cur = -1;
+    cudaGetDevice(&cur);
+    if (cur != m->dev->device) {  // the cached pointers belong to another GPU
+      set_error("tokp_model was uploaded to CUDA device " + std::to_string(m->dev->device) + ", the current device is " +
+                std::to_string(cur) + ": load the model once per device");
+      return TOKP_ERR_STATE;
+    }
+    *out = &m->dev->dm;
+    return TOKP_OK;
+  }
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
     set_error("no CUDA device available (tokp has no CPU fallback)");
@@ -171,6 +182,7 @@ int ensure_device_model(const tokp_model* mc, const DM** out) {
   if (const char* e = getenv("TOKP_SPEC_NV")) { if (atoi(e) == 0) dm.spec_nv = 0; }  // tuning: generic kernels only
   dm.lane_ok = (dm.spec_nv == 2 || dm.spec_nv == 9) && !dm.any_gravcomp && dm.maxefc <= 64;
   for (int jt : h.jnt_type) if (jt != JNT_HINGE && jt != JNT_SLIDE) dm.lane_ok = 0;
+  cudaGetDevice(&d->device);
   m->dev = d;
   *out = &m->dev->dm;
   return TOKP_OK;

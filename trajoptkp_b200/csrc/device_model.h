@@ -40,5 +40,6 @@ struct DM {
 struct DeviceModel {
   DM dm;
   void* arena = nullptr;  // single device allocation holding every array
+  int device = -1;        // CUDA device the arena lives on: the handle is valid on that device only
   int lanes = 0;          // lanes per world of tokp_step_worlds (TOKP_LANES read once, on the first call)
 };

@@ -234,6 +234,9 @@ struct Compiler {
       }
     } else if (ext == ".obj") {
       read_obj(path, v, face);
+      for (int idx : face)
+        if (idx < 0 || idx >= (int)v.size() / 3)
+          throw std::runtime_error("mjcf: mesh '" + name + "' has a face index outside its vertex list");
     } else {
       throw std::runtime_error("mjcf: mesh format of '" + a.file + "' unsupported (binary STL and OBJ only)");
     }
@@ -397,6 +400,8 @@ struct Compiler {
     push_n(m.jnt_solimp, solimp, 5);
     m.jnt_margin.push_back(g.real("margin", 0.0));
     // dofs / qpos
+    if (g.real("frictionloss", 0.0) != 0.0 || g.real("stiffness", 0.0) != 0.0)
+      throw std::runtime_error("mjcf: joint frictionloss / stiffness are outside the supported subset");
     double armature = jt == JNT_FREE ? 0.0 : g.real("armature", 0.0);
     double damping = jt == JNT_FREE ? 0.0 : g.real("damping", 0.0);
     int ndof = jt == JNT_FREE ? 6 : 1;
@@ -1046,6 +1051,10 @@ struct Compiler {
           if (*a != "Newton") throw std::runtime_error("mjcf: only the Newton solver is supported");
       }
     }
+    // dynamics the step does not model must not be dropped silently
+    for (auto& ch : root.children)
+      if ((ch->tag == "tendon" || ch->tag == "equality") && !ch->children.empty())
+        throw std::runtime_error("mjcf: <" + ch->tag + "> elements are outside the supported subset");
     for (auto& ch : root.children)
       if (ch->tag == "default") parse_default(*ch, nullptr, true);
     for (auto& ch : root.children)

@@ -215,7 +215,7 @@ struct TriWalk {
   TK_DEV void advance(int by) { col += by; settle(); }
 };
 
-// in-place dense Cholesky (lower) of the nv x nv matrix in w.H, right-looking, lanes over the trailing triangle
+// in-place dense Cholesky (lower) of the nv x nv matrix in w.H, right-looking, lanes over the rows of the trailing block
 template <int G, int NV>
 TK_DEV void chol_factor(double* H, int n, const Grp<G, NV>& g) {
 #pragma unroll 1
@@ -227,11 +227,18 @@ TK_DEV void chol_factor(double* H, int n, const Grp<G, NV>& g) {
     g.sync();
     for (int i = j + g.gl; i < n; i += G) H[i * n + j] = (i == j) ? d : H[i * n + j] * inv;
     g.sync();
-    const int rem = n - j - 1, ntri = rem * (rem + 1) / 2;
-    TriWalk t(g.gl);
-    for (int e = g.gl; e < ntri; e += G, t.advance(G)) {
-      const int i = j + 1 + t.row, k = j + 1 + t.col;
-      H[i * n + k] -= H[i * n + j] * H[k * n + j];
+    // trailing update, a lane per row i of the block below / right of column j: H[i][k] -= L[i][j] L[k][j] for
+    // j < k <= i.  No index arithmetic; column j is not written here, so four entries are loaded ahead of their stores
+    for (int i = j + 1 + g.gl; i < n; i += G) {
+      const double lij = H[i * n + j];
+      double* Hi = &H[i * n];
+      int k = j + 1;
+      for (; k + 3 <= i; k += 4) {
+        const double a0 = Hi[k], a1 = Hi[k + 1], a2 = Hi[k + 2], a3 = Hi[k + 3];
+        const double b0 = H[k * n + j], b1 = H[(k + 1) * n + j], b2 = H[(k + 2) * n + j], b3 = H[(k + 3) * n + j];
+        Hi[k] = a0 - lij * b0; Hi[k + 1] = a1 - lij * b1; Hi[k + 2] = a2 - lij * b2; Hi[k + 3] = a3 - lij * b3;
+      }
+      for (; k <= i; k++) Hi[k] -= lij * H[k * n + j];
     }
     g.sync();
   }
@@ -383,13 +390,29 @@ TK_DEV void fwd_constraint(const DM& m, WS& w, const Grp<G, NV>& g, int iteratio
       TK_CLK(w, g, 8); TK_CNT(w, g, 21);
       chol_factor_tri(w.H, nv, g, tm);
     } else {
+      // four entries of the triangle per lane and pass over the rows (independent accumulators)
+      const int ntri = nv * (nv + 1) / 2;
       TriWalk t(g.gl);
-      for (int e = g.gl; e < nv * (nv + 1) / 2; e += G, t.advance(G)) {
-        const int i = t.row, j = t.col;
-        double h = w.M[i * nv + j];
-        for (int r = 0; r < nefc; r++)
-          if (w.efc_force[r] != 0.0) h += w.efc_D[r] * w.J[r * nv + i] * w.J[r * nv + j];
-        w.H[i * nv + j] = h;
+      for (int e = g.gl; e < ntri; e += 4 * G) {
+        int ei[4], ej[4];
+        double h[4];
+#pragma unroll
+        for (int b = 0; b < 4; b++) {
+          const bool ok = e + b * G < ntri;
+          ei[b] = ok ? t.row : -1; ej[b] = ok ? t.col : 0;
+          h[b] = ok ? w.M[t.row * nv + t.col] : 0.0;
+          t.advance(G);
+        }
+        for (int r = 0; r < nefc; r++) {
+          if (w.efc_force[r] == 0.0) continue;
+          const double D = w.efc_D[r];
+          const double* Jr = &w.J[r * nv];
+#pragma unroll
+          for (int b = 0; b < 4; b++) h[b] += D * Jr[ei[b] < 0 ? 0 : ei[b]] * Jr[ej[b]];
+        }
+#pragma unroll
+        for (int b = 0; b < 4; b++)
+          if (ei[b] >= 0) w.H[ei[b] * nv + ej[b]] = h[b];
       }
       g.sync();
       TK_CLK(w, g, 8); TK_CNT(w, g, 21);

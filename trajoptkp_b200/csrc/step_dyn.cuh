@@ -274,19 +274,27 @@ template <int G, int NV>
 TK_DEV void chol_solve_reg(const double* L, int n, double* x, const double* b, const Grp<G, NV>& g) {
   const int i = g.gl;
   const bool mine = i < n;
+  const int ic = mine ? i : 0;  // a valid row / column for the lanes past n (their loads are not used)
   double xi = mine ? b[i] : 0.0;
   const double dinv = mine ? 1.0 / L[i * n + i] : 0.0;
+  // the entry of L for the next trip is loaded before this trip's shuffle: it is off the dependent chain
+  double lnext = L[ic * n];
 #pragma unroll 1
   for (int j = 0; j < n; j++) {
+    const double l = lnext;
+    if (j + 1 < n) lnext = L[ic * n + j + 1];
     const double xj = __shfl_sync(g.mask, xi * dinv, j, G);
     if (i == j) xi = xj;
-    else if (mine && i > j) xi -= L[i * n + j] * xj;
+    else if (mine && i > j) xi -= l * xj;
   }
+  lnext = L[(n - 1) * n + ic];
 #pragma unroll 1
   for (int j = n - 1; j >= 0; j--) {
+    const double l = lnext;
+    if (j > 0) lnext = L[(j - 1) * n + ic];
     const double xj = __shfl_sync(g.mask, xi * dinv, j, G);
     if (i == j) xi = xj;
-    else if (i < j) xi -= L[j * n + i] * xj;
+    else if (i < j) xi -= l * xj;
   }
   if (mine) x[i] = xi;
   g.sync();
@@ -305,21 +313,28 @@ TK_DEV void chol_solve_reg2(const double* L, int n, double* x, const double* b, 
   const bool m1 = i1 < n;  // i0 < G < n always
   double x0 = b[i0], x1 = m1 ? b[i1] : 0.0;
   const double d0 = 1.0 / L[i0 * n + i0], d1 = m1 ? 1.0 / L[i1 * n + i1] : 0.0;
+  const int i1c = m1 ? i1 : i0;
+  double l0n = L[i0 * n], l1n = L[i1c * n];  // next trip's entries, loaded ahead of the shuffle
 #pragma unroll 1
   for (int j = 0; j < n; j++) {
+    const double l0 = l0n, l1 = l1n;
+    if (j + 1 < n) { l0n = L[i0 * n + j + 1]; l1n = L[i1c * n + j + 1]; }
     const bool lowj = j < G;
     const double xj = __shfl_sync(g.mask, lowj ? x0 * d0 : x1 * d1, j & (G - 1), G);
-    if (lowj) { if (i0 == j) x0 = xj; else if (i0 > j) x0 -= L[i0 * n + j] * xj; }
+    if (lowj) { if (i0 == j) x0 = xj; else if (i0 > j) x0 -= l0 * xj; }
     if (!lowj && i1 == j) x1 = xj;
-    else if (m1 && i1 > j) x1 -= L[i1 * n + j] * xj;
+    else if (m1 && i1 > j) x1 -= l1 * xj;
   }
+  l0n = L[(n - 1) * n + i0]; l1n = L[(n - 1) * n + i1c];
 #pragma unroll 1
   for (int j = n - 1; j >= 0; j--) {
+    const double l0 = l0n, l1 = l1n;
+    if (j > 0) { l0n = L[(j - 1) * n + i0]; l1n = L[(j - 1) * n + i1c]; }
     const bool lowj = j < G;
     const double xj = __shfl_sync(g.mask, lowj ? x0 * d0 : x1 * d1, j & (G - 1), G);
-    if (!lowj) { if (i1 == j) x1 = xj; else if (i1 < j) x1 -= L[j * n + i1] * xj; }
+    if (!lowj) { if (i1 == j) x1 = xj; else if (i1 < j) x1 -= l1 * xj; }
     if (lowj && i0 == j) x0 = xj;
-    else if (i0 < j) x0 -= L[j * n + i0] * xj;
+    else if (i0 < j) x0 -= l0 * xj;
   }
   x[i0] = x0;
   if (m1) x[i1] = x1;

@@ -550,31 +550,95 @@ void adapt_fast_capacity(tokp_traj* tr, long long worlds, long long overflowed) 
   }
 }
 
-// counters: worlds actually simulated and Jacobians (|C|/n per row) for the current key-point masks
-int update_fd_counters(tokp_traj* tr) {
-  std::vector<unsigned long long> hm((size_t)tr->B * tr->T);
-  TOKP_CUDA(cudaMemcpyAsync(hm.data(), tr->kp_mask, hm.size() * 8, cudaMemcpyDeviceToHost, tr->stream));
-  int hc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-  TOKP_CUDA(cudaMemcpyAsync(hc, tr->fd_counts, sizeof(hc), cudaMemcpyDeviceToHost, tr->stream));
-  TOKP_CUDA(cudaStreamSynchronize(tr->stream));
+// Key-point statistics of one trajectory per block, without copying the masks to the host: FD worlds and columns of the
+// current masks, and the sum over the dofs of the percentage of rows that are key-points of that dof - with the
+// velocity_change quirk of the last row (the scan's own hits, then every dof once more; KeyPointGenerator.cpp:724-727),
+// per dof ((double)count / T) * 100 summed in dof order exactly as read_keypoints does on the host.
+__global__ void k_kp_stats(const unsigned long long* __restrict__ mask, const unsigned long long* __restrict__ last,
+                           const int* __restrict__ flags, double* __restrict__ out, int T, int n, int m) {
+  __shared__ double pct[64];
+  const int b = blockIdx.x, lane = threadIdx.x;
+  const unsigned long long* mk = mask + (size_t)b * T;
+  const bool quirk = (flags[b] & 1) != 0;
+  const unsigned long long cmask = m >= 64 ? ~0ull : ((1ull << m) - 1);
   long long worlds = 0, cols = 0;
-  for (auto mk : hm) {
-    if (!mk) continue;
-    int c = __builtin_popcountll(mk);
-    int cm = __builtin_popcountll(mk & ((tr->m >= 64) ? ~0ull : ((1ull << tr->m) - 1)));
-    worlds += 1 + 2 * cm + 4 * c;
+  for (int t = lane; t < T; t += 32) {
+    const unsigned long long v = mk[t];
+    if (!v) continue;
+    const int c = __popcll(v);
+    worlds += 1 + 2 * __popcll(v & cmask) + 4 * c;
     cols += c;
   }
-  tr->counters[0] = worlds;
-  // worlds that overflowed the fast constraint-row capacity and were re-run (of the last row chunk)
-  if (tr->fd_last_lane_mode == 2) {  // no fast pass: counts[2] is the number of nominal worlds there
-    tr->counters[3] = 0;
-  } else {
-    tr->counters[3] = hc[2] + hc[3];
-    adapt_fast_capacity(tr, hc[0] + hc[1], hc[2] + hc[3]);
+  for (int off = 16; off > 0; off >>= 1) {
+    worlds += __shfl_xor_sync(0xffffffffu, worlds, off);
+    cols += __shfl_xor_sync(0xffffffffu, cols, off);
   }
-  tr->counters[1] = (int64_t)((double)cols / tr->n * 1e6);
+  for (int j = lane; j < n; j += 32) {
+    int cnt = 0;
+    for (int t = 0; t < T; t++) {
+      const unsigned long long v = (t == T - 1 && quirk) ? last[b] : mk[t];
+      cnt += (int)((v >> j) & 1ull);
+    }
+    if (quirk) cnt++;
+    pct[j] = ((double)cnt / (double)T) * 100;
+  }
+  __syncwarp();
+  if (lane == 0) {
+    double s = 0;
+    for (int j = 0; j < n; j++) s += pct[j];
+    out[3 * b] = s; out[3 * b + 1] = (double)worlds; out[3 * b + 2] = (double)cols;
+  }
+}
+
+// the statistics, the FD list counters and the status words travel to pinned host memory behind the work already on
+// the stream; nothing waits here
+int kp_stats_enqueue(tokp_traj* tr) {
+  const int B = tr->B;
+  k_kp_stats<<<B, 32, 0, tr->stream>>>(tr->kp_mask, tr->kp_last, tr->kp_flags, tr->kp_stats, tr->T, tr->n, tr->m);
+  g_launches++;
+  TOKP_CUDA(cudaGetLastError());
+  TOKP_CUDA(cudaMemcpyAsync(tr->h_kp_stats, tr->kp_stats, (size_t)B * 3 * 8, cudaMemcpyDeviceToHost, tr->stream));
+  TOKP_CUDA(cudaMemcpyAsync(tr->h_fd_counts, tr->fd_counts, 8 * sizeof(int), cudaMemcpyDeviceToHost, tr->stream));
+  TOKP_CUDA(cudaMemcpyAsync(tr->h_wstatus, tr->wstatus, (size_t)B * 2 * sizeof(int), cudaMemcpyDeviceToHost, tr->stream));
   return TOKP_OK;
+}
+
+// after the stream has been synchronised: counters (unless the caller keeps its own, as the iterative_error level loop
+// does) and the status words of the derivative phase
+int kp_stats_finish(tokp_traj* tr, bool set_counters, const char* what) {
+  if (set_counters) {
+    double worlds = 0, cols = 0;
+    for (int b = 0; b < tr->B; b++) { worlds += tr->h_kp_stats[3 * b + 1]; cols += tr->h_kp_stats[3 * b + 2]; }
+    tr->counters[0] = (long long)worlds;
+    // worlds that overflowed the fast constraint-row capacity and were re-run (of the last row chunk)
+    const int* hc = tr->h_fd_counts;
+    if (tr->fd_last_lane_mode == 2) {  // no fast pass: counts[2] is the number of nominal worlds there
+      tr->counters[3] = 0;
+    } else {
+      tr->counters[3] = hc[2] + hc[3];
+      adapt_fast_capacity(tr, hc[0] + hc[1], hc[2] + hc[3]);
+    }
+    tr->counters[1] = (int64_t)(cols / tr->n * 1e6);
+  }
+  if (!what) return TOKP_OK;
+  for (int b = 0; b < tr->B; b++) {
+    const int bits = tr->h_wstatus[2 * b];
+    if (bits & 32) { set_error(std::string(what) + ": a world hit an unsupported collision pair or contact dimension"); return TOKP_ERR_UNSUPPORTED; }
+    if (bits & 8) {
+      set_error(std::string(what) + ": constraint rows of an FD world exceed TOKP_EFC_MAX, contacts were dropped (trajectory " +
+                std::to_string(b) + ")");
+      return TOKP_ERR_STATE;
+    }
+  }
+  return TOKP_OK;
+}
+
+// counters: worlds actually simulated and Jacobians (|C|/n per row) for the current key-point masks
+int update_fd_counters(tokp_traj* tr) {
+  int rc = kp_stats_enqueue(tr);
+  if (rc) return rc;
+  TOKP_CUDA(cudaStreamSynchronize(tr->stream));
+  return kp_stats_finish(tr, true, nullptr);
 }
 
 }  // namespace tokp

@@ -442,6 +442,8 @@ void pack_snapshot(const tokp_traj* tr, const double* s, double* d);
 int check_applied_zero(const tokp_traj* tr, const double* s);
 int read_keypoints(tokp_traj* tr, int* counts, int* indices, double* pct);
 int update_fd_counters(tokp_traj* tr);
+int kp_stats_enqueue(tokp_traj* tr);
+int kp_stats_finish(tokp_traj* tr, bool set_counters, const char* what);
 int check_world_status(tokp_traj* tr, int column, const char* what);
 
 static int cost_derivs(tokp_traj* tr, int central, double eps) {
@@ -512,9 +514,9 @@ static int generate_derivatives(tokp_traj* tr) {
   if (tr->task.kp_method != TOKP_KP_ITERATIVE_ERROR) {
     rc = launch_fd(tr, tr->kp_mask, nullptr, tr->B * tr->T, 1, 1e-6);
     if (rc) return rc;
-    rc = update_fd_counters(tr);
-    if (rc) return rc;
   }
+  rc = kp_stats_enqueue(tr);  // finished by the caller once it has synchronised (kp_stats_finish)
+  if (rc) return rc;
   rc = interpolate(tr);
   if (rc) return rc;
   rc = cost_derivs(tr, 1, 1e-6);
@@ -652,7 +654,8 @@ extern "C" int tokp_generate_derivatives(tokp_traj* tr) {
   if (rc) return rc;
   tr->timers[0] = tm.stop();
   TOKP_CUDA(cudaStreamSynchronize(tr->stream));
-  return TOKP_OK;
+  // the iterative_error level loop keeps its own world / column counters
+  return kp_stats_finish(tr, tr->task.kp_method != TOKP_KP_ITERATIVE_ERROR, "tokp_generate_derivatives");
 }
 
 extern "C" int tokp_backward_pass(tokp_traj* tr, const double* lambda, int* ok, double* delta_J) {
@@ -718,7 +721,7 @@ extern "C" int tokp_optimise(tokp_traj* tr, const double* snapshot0, const doubl
   initial = old_cost;
   double alphas[tokp_traj::NA];
   for (int i = 1; i < NA + 1; i++) { double lin = (double)i / NA; alphas[i - 1] = lin * lin; }
-  std::vector<double> costs((size_t)B * NA), dJ(B), pct((size_t)B * tr->n);
+  std::vector<double> costs((size_t)B * NA), dJ(B);
   std::vector<int> ok(B);
   for (int it = 0; it < max_iterations; it++) {
     bool any_active = false;
@@ -729,16 +732,11 @@ extern "C" int tokp_optimise(tokp_traj* tr, const double* snapshot0, const doubl
     bool need = false;
     for (int b = 0; b < B; b++) if (!done[b] && reduced[b]) need = true;
     if (need) {
-      rc = tokp_generate_derivatives(tr);
-      if (rc) return rc;
-      rc = check_world_status(tr, 0, "tokp_optimise");
-      if (rc) return rc;
-      rc = read_keypoints(tr, nullptr, nullptr, pct.data());
+      rc = tokp_generate_derivatives(tr);  // also checks the status words of the FD worlds
       if (rc) return rc;
       for (int b = 0; b < B; b++)
         if (!done[b] && reduced[b]) {
-          double s = 0;
-          for (int j = 0; j < tr->n; j++) s += pct[(size_t)b * tr->n + j];
+          const double s = tr->h_kp_stats[3 * b];  // sum over the dofs of the key-point percentages (k_kp_stats)
           pct_sum[b] += s / tr->n; pct_cnt[b]++;
           t_der[b] += tr->timers[0];
         }

@@ -237,6 +237,11 @@ static int keypoints_iterative(tokp_traj* tr) {
   return rc;
 }
 
+__global__ void k_fill_int(int* p, int v, int count) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < count) p[i] = v;
+}
+
 int generate_keypoints(tokp_traj* tr) {
   int B = tr->B, T = tr->T, n = tr->n;
   const TaskDev& t = tr->task;
@@ -257,9 +262,8 @@ int generate_keypoints(tokp_traj* tr) {
     g_launches++;
     if (mode == 2) flags = 1;
   }
-  std::vector<int> hf(B, flags);
-  cudaMemcpyAsync(tr->kp_flags, hf.data(), B * 4, cudaMemcpyHostToDevice, tr->stream);
-  TOKP_CUDA(cudaStreamSynchronize(tr->stream));
+  k_fill_int<<<(B + 127) / 128, 128, 0, tr->stream>>>(tr->kp_flags, flags, B);  // no host buffer, no wait
+  g_launches++;
   TOKP_CUDA(cudaGetLastError());
   return TOKP_OK;
 }

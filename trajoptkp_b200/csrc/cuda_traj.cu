@@ -131,6 +131,11 @@ extern "C" int tokp_traj_create(const tokp_model* m, const tokp_task_desc* td, i
   std::vector<double> tg((size_t)B * ntg);
   for (int b = 0; b < B; b++) std::memcpy(&tg[(size_t)b * ntg], td->resid_target, ntg * 8);
   cudaMemcpy(tr->target, tg.data(), tg.size() * 8, cudaMemcpyHostToDevice);
+  cudaMalloc(&tr->kp_stats, (size_t)B * 3 * 8);
+  cudaMallocHost(&tr->h_kp_stats, (size_t)B * 3 * 8);
+  cudaMallocHost(&tr->h_fd_counts, 8 * sizeof(int));
+  cudaMallocHost(&tr->h_wstatus, (size_t)B * 2 * sizeof(int));
+  if (!tr->kp_stats || !tr->h_kp_stats || !tr->h_fd_counts || !tr->h_wstatus) { set_error("tokp_traj_create: statistics buffers"); tokp_traj_destroy(tr); return TOKP_ERR_CUDA; }
   read_env_options(tr->dm);
   if (const char* e = getenv("TOKP_ROLL_BLOCKSYNC")) tr->roll_blocksync = atoi(e) > 3 ? 3 : (atoi(e) < 0 ? 0 : atoi(e));
   if (const char* e = getenv("TOKP_SPREAD_WARPS")) { int v = atoi(e); if (v >= 1 && v <= 4) tr->spread_warps = v; }
@@ -162,6 +167,10 @@ extern "C" void tokp_traj_destroy(tokp_traj* tr) {
   if (tr->ev3) cudaEventDestroy(tr->ev3);
   if (tr->arena) cudaFree(tr->arena);
   if (tr->fd_share) cudaFree(tr->fd_share);
+  if (tr->kp_stats) cudaFree(tr->kp_stats);
+  if (tr->h_kp_stats) cudaFreeHost(tr->h_kp_stats);
+  if (tr->h_fd_counts) cudaFreeHost(tr->h_fd_counts);
+  if (tr->h_wstatus) cudaFreeHost(tr->h_wstatus);
   if (tr->cols_scratch) cudaFree(tr->cols_scratch);
   if (tr->ie_scratch) cudaFree(tr->ie_scratch);
   delete tr;

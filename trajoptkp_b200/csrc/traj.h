@@ -105,6 +105,12 @@ struct tokp_traj {
   int fd_last_lane_mode = 0;
   // rollout tuning (TOKP_ROLL_BLOCKSYNC, TOKP_SPREAD_WARPS, TOKP_SPREAD_KEEP_LANES; read once at creation)
   int roll_blocksync = -1, spread_warps = 0, spread_keep_lanes = 0;
+  // key-point statistics without a bulk readback: k_kp_stats leaves [B][3] (sum of per-dof percentages, FD worlds,
+  // columns) in kp_stats; it, the FD list counters and the status words land in pinned host memory with the stream
+  double* kp_stats = nullptr;
+  double* h_kp_stats = nullptr;  // pinned [B][3]
+  int* h_fd_counts = nullptr;    // pinned [8]
+  int* h_wstatus = nullptr;      // pinned [B][2]
   void* cols_scratch = nullptr;  // tokp_dynamics_derivs_cols: zero [B*T] mask + one row index (allocated on first use)
   void* ie_scratch = nullptr;    // iterative_error: need mask | row list | segments | verdicts (allocated on first use)
   int fd_share_gib = 16;       // cap of the lane_mode-2 share buffer (TOKP_FD_SHARE_GIB, read once at creation)

@@ -3,7 +3,7 @@
 command (tools/capture_profiles.sh): dram__bytes_read.sum + dram__bytes_write.sum, summed over the kernels that make up
 the launch.  The entry carries the hash of the kernel sources; bench.py reports `roofline.traffic` only while the
 sources still have that hash (a capture describes the build it was taken on).
-usage: make_fd_traffic.py task batch horizon kp rep [rep ...]"""
+usage: make_fd_traffic.py task batch horizon kp rep-or-raw-page-csv [...]"""
 import csv
 import json
 import os
@@ -17,7 +17,8 @@ import bench  # noqa: E402
 task, batch, horizon, kp = sys.argv[1], int(sys.argv[2]), int(sys.argv[3]), sys.argv[4]
 total, parts = 0.0, []
 for rep in sys.argv[5:]:
-    raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    raw = open(rep).read() if rep.endswith(".csv") else \
+        subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(raw.splitlines()))
     hdr, units = rows[0], rows[1]
     for r in rows[2:]:

@@ -31,6 +31,15 @@ for r in rows[2:]:
         if k in hdr:
             i = hdr.index(k)
             print("%-75s %-14s %s" % (k, units[i], r[i]))
+    # warp stall reasons, cycles per issued instruction (the metric names differ between ncu versions)
+    stalls = [(float(r[i].replace(",", "")), k) for i, k in enumerate(hdr)
+              if "issue_stalled" in k and k.endswith("_per_issue_active.ratio") and "not_issued" not in k and r[i] not in ("", "n/a")]
+    for v, k in sorted(stalls, reverse=True)[:10]:
+        print("%-75s %-14s %.3f" % (k, "per issue", v))
+    for k in ("sm__icc_request_hit_rate.pct", "l1tex__t_sector_hit_rate.pct", "sm__warps_active.avg.per_cycle_active",
+              "smsp__issue_active.avg.per_cycle_active"):
+        if k in hdr:
+            print("%-75s %-14s %s" % (k, units[hdr.index(k)], r[hdr.index(k)]))
     print("---")
 src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "cuda,sass"], capture_output=True, text=True).stdout
 cur = None

@@ -126,3 +126,20 @@ def test_summary_yaml_is_byte_identical_to_a_published_file():
             "  - 10\n  - 10\n  - 10\n  - 10")
     got = sweep.summary_yaml(80, 0.5, 0.005, "velocity_change", 2, 20, vel_thr=[2, 2, 2, 10, 10, 10, 10, 10, 10])
     assert got == want
+
+
+def test_save_trajec_information_matches_the_reference_format(tmp_path):
+    """FileHandler.cpp:312-383: four CSVs, row-major, trailing commas, default ostream number format, horizon - 1 lines."""
+    from trajoptkp_b200 import sweep
+    T, dof, m = 3, 1, 1
+    A = np.array([[[1.0, 0.004], [-2.5e-7, 0.999999]], [[1.0, 0.004], [0.0, 123456789.0]], [[9.0, 9.0], [9.0, 9.0]]])
+    B = np.array([[[0.0], [0.004]], [[1e-5], [-0.0]], [[9.0], [9.0]]])
+    X = np.array([[3.14159265, 0.0], [3.1, -0.25], [9.0, 9.0]])
+    U = np.array([[0.5], [-1.0], [9.0]])
+    root = sweep.save_trajec_information(str(tmp_path), A, B, X, U, "/acrobot")
+    assert root == str(tmp_path) + "/savedTrajecInfo/acrobot"
+    read = lambda n: open(root + "/" + n).read()
+    assert read("A_matrices.csv") == "1,0.004,-2.5e-07,0.999999,\n1,0.004,0,1.23457e+08,\n"
+    assert read("B_matrices.csv") == "0,0.004,\n1e-05,-0,\n"
+    assert read("states.csv") == "3.14159,0,\n3.1,-0.25,\n"
+    assert read("controls.csv") == "0.5,\n-1,\n"

@@ -219,3 +219,26 @@ def test_residual_derivs_per_call(built, name):
     assert np.allclose(rx_f, rx_all[7], atol=1e-4)
     with pytest.raises(capi.TokpError):
         tr.residual_derivs(0, T + 1)
+
+
+def test_dump_trajectory_writes_the_reference_csv_files(built, tmp_path):
+    """SURVEY N1: FileHandler::SaveTrajecInformation (FileHandler.cpp:312-383) from a device trajectory."""
+    from trajoptkp_b200 import sweep
+    T = 30
+    tc, snap0, U, tr = _setup("acrobot", T, capi.KP_SET_INTERVAL, 1, 1)
+    tr.rollout(snap0, U)
+    tr.generate_derivatives()
+    root = sweep.dump_trajectory(tr, 0, str(tmp_path), "/acrobot_trial0")
+    nx, m = tr.nx, tr.m
+    A = np.array([[float(v) for v in line.rstrip(",\n").split(",")] for line in open(root + "/A_matrices.csv")])
+    Bm = np.array([[float(v) for v in line.rstrip(",\n").split(",")] for line in open(root + "/B_matrices.csv")])
+    X = np.array([[float(v) for v in line.rstrip(",\n").split(",")] for line in open(root + "/states.csv")])
+    Uf = np.array([[float(v) for v in line.rstrip(",\n").split(",")] for line in open(root + "/controls.csv")])
+    assert A.shape == (T - 1, nx * nx) and Bm.shape == (T - 1, nx * m) and X.shape == (T - 1, nx) and Uf.shape == (T - 1, m)
+    # row-major A_t / B_t (the device stores them column-major), to the 6 printed digits
+    A_dev = tr.get(0, "A").reshape(T, nx, nx).transpose(0, 2, 1)[:T - 1].reshape(T - 1, -1)
+    B_dev = tr.get(0, "B").reshape(T, m, nx).transpose(0, 2, 1)[:T - 1].reshape(T - 1, -1)
+    assert np.allclose(A, A_dev, rtol=1e-5, atol=1e-9) and np.allclose(Bm, B_dev, rtol=1e-5, atol=1e-9)
+    assert abs(A[0].reshape(nx, nx)[0, 0] - 1.0) < 1e-3  # dq'/dq on the diagonal: row-major, not transposed garbage
+    assert np.allclose(X, tr.get(0, "X_old").reshape(T + 1, nx)[:T - 1], rtol=1e-5, atol=1e-6)
+    assert np.allclose(Uf, np.asarray(U).reshape(T, m)[:T - 1], rtol=1e-5, atol=1e-6)

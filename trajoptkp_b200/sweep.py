@@ -10,6 +10,8 @@ Record columns follow the reference's summary.csv (GenTestingData.cpp:236-247) p
   cost_reduction, opt_time_ms, iterations, avg_dofs, avg_pct_derivs, t_derivs_ms, t_bp_ms, t_fp_ms,
   jacobians, trial_index
 """
+import os
+
 import numpy as np
 
 RECORD_FIELDS = ("cost_reduction", "opt_time_ms", "iterations", "avg_dofs", "avg_pct_derivs", "t_derivs_ms",
@@ -216,3 +218,40 @@ def run_openloop_sweep(tc, horizon, num_trials=100, rank=0, world=1, dist=None, 
                          stats[r, 6], stats[r, 7], jac / B])
     local = pack_records(mine, recs, num_trials, world)
     return gather_records(local, num_trials, dist=dist, device=device)
+
+
+def save_trajec_information(project_parent_path, A, B, states, controls, file_prefix=""):
+    """FileHandler::SaveTrajecInformation (src/FileHandler/FileHandler.cpp:312-383): the four CSV files the reference's
+    analysis scripts read - `<parent>/savedTrajecInfo<prefix>/{A_matrices,B_matrices,states,controls}.csv`.  One line
+    per time step, matrices flattened row-major, every value followed by a comma, numbers in the default ostream format
+    (6 significant digits, "%g"), and - as in the reference - only the first `horizon - 1` steps are written.
+    A [T][2 dof][2 dof], B [T][2 dof][num_ctrl], states [T][2 dof], controls [T][num_ctrl] (mathematical indexing)."""
+    A = np.asarray(A, dtype=np.float64)
+    B = np.asarray(B, dtype=np.float64)
+    states = np.asarray(states, dtype=np.float64)
+    controls = np.asarray(controls, dtype=np.float64)
+    horizon = A.shape[0]
+    root = project_parent_path + "/savedTrajecInfo" + file_prefix
+    os.makedirs(root, exist_ok=True)
+
+    def write(name, rows):
+        with open(os.path.join(root, name), "w") as f:
+            for r in rows:
+                f.write("".join("%g," % v for v in np.ravel(r)) + "\n")
+
+    write("A_matrices.csv", A[:horizon - 1])
+    write("B_matrices.csv", B[:horizon - 1])
+    write("states.csv", states[:horizon - 1])
+    write("controls.csv", controls[:horizon - 1])
+    return root
+
+
+def dump_trajectory(tr, b, project_parent_path, file_prefix=""):
+    """save_trajec_information for trajectory b of a device batch: A / B as interpolated by the last
+    generate_derivatives, the nominal states and controls."""
+    T, nx, m = tr.T, tr.nx, tr.m
+    A = tr.get(b, "A").reshape(T, nx, nx).transpose(0, 2, 1)  # device matrices are column-major
+    B = tr.get(b, "B").reshape(T, m, nx).transpose(0, 2, 1)
+    X = tr.get(b, "X_old").reshape(T + 1, nx)[:T]
+    U = tr.get(b, "U_old").reshape(T, m)
+    return save_trajec_information(project_parent_path, A, B, X, U, file_prefix)

@@ -315,13 +315,13 @@ __global__ void __launch_bounds__(32) k_fd_dep_lanes(DM dm, FdArgs a, LaneArgs l
         for (int i = nv - 1; i > 0; i--) {
           double xi = TOKP_PL(v_asm, i);
           if (xi != 0.0)
-            for (unsigned long long ch = tk::anc_mask<NV>(dm, i) & ~(1ull << i); ch;) { const int j = tk::pop_top(ch); TOKP_PL(v_asm, j) -= uLD[i * nv + j] * xi; }
+            for (tk::anc_t<NV> ch = tk::anc_mask<NV>(dm, i) & ~(tk::anc_t<NV>(1) << i); ch;) { const int j = tk::pop_top(ch); TOKP_PL(v_asm, j) -= uLD[i * nv + j] * xi; }
         }
 #pragma unroll
         for (int i = 0; i < nv; i++) TOKP_PL(v_asm, i) *= uLDinv[i];
         for (int i = 1; i < nv; i++) {
           double s = TOKP_PL(v_asm, i);
-          for (unsigned long long ch = tk::anc_mask<NV>(dm, i) & ~(1ull << i); ch;) { const int j = tk::pop_top(ch); s -= uLD[i * nv + j] * TOKP_PL(v_asm, j); }
+          for (tk::anc_t<NV> ch = tk::anc_mask<NV>(dm, i) & ~(tk::anc_t<NV>(1) << i); ch;) { const int j = tk::pop_top(ch); s -= uLD[i * nv + j] * TOKP_PL(v_asm, j); }
           TOKP_PL(v_asm, i) = s;
         }
         // ---- mj_fwdConstraint: Newton solver ---------------------------------------------------------------------
@@ -623,13 +623,13 @@ __global__ void __launch_bounds__(32) k_fd_dep_lanes(DM dm, FdArgs a, LaneArgs l
           for (int i = nv - 1; i > 0; i--) {
             double xi = TOKP_PL(v_grad, i);
             if (xi != 0.0)
-              for (unsigned long long ch = tk::anc_mask<NV>(dm, i) & ~(1ull << i); ch;) { const int j = tk::pop_top(ch); TOKP_PL(v_grad, j) -= uLDe[i * nv + j] * xi; }
+              for (tk::anc_t<NV> ch = tk::anc_mask<NV>(dm, i) & ~(tk::anc_t<NV>(1) << i); ch;) { const int j = tk::pop_top(ch); TOKP_PL(v_grad, j) -= uLDe[i * nv + j] * xi; }
           }
 #pragma unroll
           for (int i = 0; i < nv; i++) TOKP_PL(v_grad, i) *= uHinv[i];
           for (int i = 1; i < nv; i++) {
             double s = TOKP_PL(v_grad, i);
-            for (unsigned long long ch = tk::anc_mask<NV>(dm, i) & ~(1ull << i); ch;) { const int j = tk::pop_top(ch); s -= uLDe[i * nv + j] * TOKP_PL(v_grad, j); }
+            for (tk::anc_t<NV> ch = tk::anc_mask<NV>(dm, i) & ~(tk::anc_t<NV>(1) << i); ch;) { const int j = tk::pop_top(ch); s -= uLDe[i * nv + j] * TOKP_PL(v_grad, j); }
             TOKP_PL(v_grad, i) = s;
           }
         } else {

@@ -10,6 +10,7 @@
 // dofs / constraint rows / matrix entries; reductions are xor-butterflies inside the group, so every
 // lane of a group holds bit-identical scalars and control flow is uniform per group.
 #pragma once
+#include <type_traits>
 #include <cuda_runtime.h>
 
 #include "device_model.h"
@@ -174,14 +175,22 @@ TK_DEV bool in_mask(unsigned lo, unsigned hi, int bit) { return bit < 32 ? ((lo 
 // The parent chain of a dof as a bit set: dof_ancmask has bit j set when j is the dof itself or one of its ancestors, and
 // parents have smaller indices, so taking the set bits from the top visits i, parent(i), parent(parent(i)), ... in the
 // order of a walk through dof_parentid - without a dependent global load per hop.
+// The nv-specialised kernels with nv <= 32 keep the mask in one 32-bit register (clz and shifts are single instructions).
 template <int NV>
-TK_DEV unsigned long long anc_mask(const DM& m, int i) {
-  if (NV > 0 && NV <= 32) return (unsigned long long)m.dof_ancmask_lo[i];
-  return ((unsigned long long)m.dof_ancmask_hi[i] << 32) | (unsigned long long)m.dof_ancmask_lo[i];
+using anc_t = typename std::conditional<(NV > 0 && NV <= 32), unsigned, unsigned long long>::type;
+template <int NV>
+TK_DEV anc_t<NV> anc_mask(const DM& m, int i) {
+  if constexpr (NV > 0 && NV <= 32) return m.dof_ancmask_lo[i];
+  else return ((unsigned long long)m.dof_ancmask_hi[i] << 32) | (unsigned long long)m.dof_ancmask_lo[i];
 }
 TK_DEV int pop_top(unsigned long long& mk) {
   int j = 63 - __clzll((long long)mk);
   mk &= ~(1ull << j);
+  return j;
+}
+TK_DEV int pop_top(unsigned& mk) {
+  int j = 31 - __clz((int)mk);
+  mk &= ~(1u << j);
   return j;
 }
 TK_DEV bool bad_value(double x) { return !(fabs(x) <= 1e10); }

@@ -181,7 +181,7 @@ TK_DEV void crb_factor(const DM& m, WS& w, const Grp<G, NV>& g) {
   for (int i = g.gl; i < nv; i += G) {
     double buf[6];
     mul_inert_vec(buf, &w.crb[10 * m.dof_bodyid[i]], &w.cdof[6 * i]);
-    unsigned long long chain = anc_mask<NV>(m, i);
+    anc_t<NV> chain = anc_mask<NV>(m, i);
     while (chain) {
       const int j = pop_top(chain);
       const double* c = &w.cdof[6 * j];
@@ -210,12 +210,12 @@ TK_DEV void factor_ldl(const DM& m, const double* A, double* LD, double* dinv, c
       for (int i = g.gl; i < nv; i += G) {
         const int k = m.dof_treelast[i] - t;
         if (k <= i) continue;
-        if (!((anc_mask<NV>(m, k) >> i) & 1ull)) continue;
+        if (!((anc_mask<NV>(m, k) >> i) & 1)) continue;
         double Mkk = LD[k * nv + k];
         if (Mkk < kMinVal) Mkk = kMinVal;
         double a = LD[k * nv + i] / Mkk;
         if (i == g.gl) { a0 = a; have0 = true; }
-        unsigned long long chain = anc_mask<NV>(m, i);
+        anc_t<NV> chain = anc_mask<NV>(m, i);
         while (chain) {
           const int j = pop_top(chain);
           LD[i * nv + j] -= a * LD[k * nv + j];
@@ -228,7 +228,7 @@ TK_DEV void factor_ldl(const DM& m, const double* A, double* LD, double* dinv, c
           double Mkk = LD[k * nv + k];
           if (Mkk < kMinVal) Mkk = kMinVal;
           LD[k * nv + k] = Mkk; dinv[k] = 1.0 / Mkk;
-        } else if (k > i && ((anc_mask<NV>(m, k) >> i) & 1ull)) {
+        } else if (k > i && ((anc_mask<NV>(m, k) >> i) & 1)) {
           if (i == g.gl && have0) {
             LD[k * nv + i] = a0;
           } else {
@@ -246,16 +246,16 @@ TK_DEV void factor_ldl(const DM& m, const double* A, double* LD, double* dinv, c
   for (int k = nv - 1; k >= 0; k--) {
     double Mkk = LD[k * nv + k];
     if (Mkk < kMinVal) Mkk = kMinVal;
-    const unsigned long long anck = anc_mask<NV>(m, k);
+    const anc_t<NV> anck = anc_mask<NV>(m, k);
     // each ancestor i of k updates its own row; row k is only read.  The quotient is also the new LD[k][i]: the lane
     // keeps it for its first row and writes it once the other lanes have read the old value
     double a0 = 0.0;
     bool have0 = false;
     for (int i = g.gl; i < k; i += G) {
-      if (!((anck >> i) & 1ull)) continue;
+      if (!((anck >> i) & 1)) continue;
       double a = LD[k * nv + i] / Mkk;
       if (i == g.gl) { a0 = a; have0 = true; }
-      unsigned long long chain = anc_mask<NV>(m, i);
+      anc_t<NV> chain = anc_mask<NV>(m, i);
       while (chain) {
         const int j = pop_top(chain);
         LD[i * nv + j] -= a * LD[k * nv + j];
@@ -264,7 +264,7 @@ TK_DEV void factor_ldl(const DM& m, const double* A, double* LD, double* dinv, c
     g.sync();
     if (have0) LD[k * nv + g.gl] = a0;
     for (int i = g.gl + G; i < k; i += G)
-      if ((anck >> i) & 1ull) LD[k * nv + i] = LD[k * nv + i] / Mkk;
+      if ((anck >> i) & 1) LD[k * nv + i] = LD[k * nv + i] / Mkk;
     if (g.gl == 0) { LD[k * nv + k] = Mkk; dinv[k] = 1.0 / Mkk; }
     g.sync();
   }
@@ -281,7 +281,7 @@ TK_DEV void solve_ldl(const DM& m, const double* LD, const double* dinv, double*
     for (int t = 0; t < m.max_tree_dofs - 1; t++) {
       for (int j = g.gl; j < nv; j += G) {
         const int i = m.dof_treelast[j] - t;
-        if (i > j && ((anc_mask<NV>(m, i) >> j) & 1ull)) x[j] -= LD[i * nv + j] * x[i];
+        if (i > j && ((anc_mask<NV>(m, i) >> j) & 1)) x[j] -= LD[i * nv + j] * x[i];
       }
       g.sync();
     }
@@ -290,9 +290,9 @@ TK_DEV void solve_ldl(const DM& m, const double* LD, const double* dinv, double*
     for (int i = nv - 1; i > 0; i--) {
       double xi = x[i];
       if (xi != 0.0) {
-        const unsigned long long anci = anc_mask<NV>(m, i);
+        const anc_t<NV> anci = anc_mask<NV>(m, i);
         for (int j = g.gl; j < i; j += G)
-          if ((anci >> j) & 1ull) x[j] -= LD[i * nv + j] * xi;
+          if ((anci >> j) & 1) x[j] -= LD[i * nv + j] * xi;
       }
       g.sync();
     }
@@ -323,7 +323,7 @@ TK_DEV void solve_ldl(const DM& m, const double* LD, const double* dinv, double*
         if (depth[k] != d) continue;
         const int i = g.gl + k * G;
         double s = x[i];
-        unsigned long long chain = anc_mask<NV>(m, i) & ~(1ull << i);
+        anc_t<NV> chain = anc_mask<NV>(m, i) & ~(anc_t<NV>(1) << i);
         while (chain) {
           const int j = pop_top(chain);
           s -= LD[i * nv + j] * x[j];

@@ -88,6 +88,11 @@ const char* tokp_last_error(void);
 const char* tokp_version(void);
 
 /* ---- model (MuJoCoHelper::InitSimulator, src/PhysicsSimulators/MuJoCoHelper.cpp:877-923) ---------- */
+/* TOKP_ERR_MODEL for anything the step does not model and mj_loadXML would have accepted or rejected itself: collision
+ * pairs without a narrow-phase function, condim other than 1 / 3, joint frictionloss / stiffness, <tendon>, <equality>,
+ * OBJ face indices outside the vertex list, integrators / cones / solvers other than Euler / pyramidal / Newton.
+ * The handle is uploaded to the CUDA device that is current at its first device use and is valid on that device
+ * only: using it with another current device returns TOKP_ERR_STATE (compile the model once per device). */
 int tokp_model_compile(const char* mjcf_path, double timestep, tokp_model** out);
 int tokp_model_compile_string(const char* mjcf_xml, const char* base_dir, double timestep, tokp_model** out);
 void tokp_model_destroy(tokp_model* m);

@@ -241,3 +241,34 @@ def test_dump_trajectory_writes_the_reference_csv_files(built, tmp_path):
     assert np.allclose(A, A_dev, rtol=1e-5, atol=1e-9) and np.allclose(Bm, B_dev, rtol=1e-5, atol=1e-9)
     assert np.allclose(X, tr.get(0, "X_old").reshape(T + 1, nx)[:T - 1], rtol=1e-5, atol=1e-6)
     assert np.allclose(Uf, np.asarray(U).reshape(T, m)[:T - 1], rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("method,min_N,max_N", [(capi.KP_VELOCITY_CHANGE, 2, 20), (capi.KP_SET_INTERVAL, 5, 5)])
+def test_device_keypoint_statistics_equal_the_host_readback(built, method, min_N, max_N):
+    """k_kp_stats (the derivative phase no longer copies the key-point masks to the host): the average percentage of
+    derivatives in tokp_optimise's stats and the FD world / Jacobian counters equal what the host computes from
+    tokp_keypoints - including velocity_change's last row (every dof appended again, KeyPointGenerator.cpp:724-727)."""
+    T, B = 40, 3
+    tc = make("walker_run", kp_method=method, min_N=min_N, max_N=max_N)
+    if method == capi.KP_VELOCITY_CHANGE:
+        tc.vel_thr = np.full(tc.n, 0.5)
+    snaps = np.ascontiguousarray(np.stack([perturbed_start(tc, 30 + b) for b in range(B)]))
+    U = np.ascontiguousarray(np.stack([np.asarray(random_controls(tc, T, 40 + b)).reshape(T, tc.m) for b in range(B)]))
+    tr = capi.Traj(tc, T, B)
+    Uo, stats = np.zeros((B, T, tc.m)), np.zeros((B, 8))
+    capi.check(capi.lib().tokp_optimise(tr.h, capi._d(snaps), capi._d(U), 1, 1, None, capi._d(Uo), capi._d(stats)))
+    counters = tr.counters()
+    # the key-points of that iteration: the same generator on the same nominal trajectory, read back on the host
+    tr2 = capi.Traj(tc, T, B)
+    capi.check(capi.lib().tokp_rollout(tr2.h, capi._d(snaps), capi._d(U), None))
+    rows, pct = tr2.keypoints()
+    worlds = cols = 0
+    for b in range(B):
+        assert stats[b, 4] == pytest.approx(np.asarray(pct[b]).sum() / tc.n, rel=1e-14), (b, stats[b, 4], pct[b])
+        for row in rows[b]:
+            c = set(row)
+            if c:
+                worlds += 1 + 2 * len([j for j in c if j < tc.m]) + 4 * len(c)
+                cols += len(c)
+    assert counters[0] == worlds
+    assert counters[1] == int(cols / tc.n * 1e6)

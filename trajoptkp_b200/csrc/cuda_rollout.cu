@@ -179,6 +179,7 @@ int launch_rollout(tokp_traj* tr, int mode, const double* d_Uin, const double* d
     // the redo pass runs a sparse subset of the worlds: no block walk; neither for one-warp blocks
     a.bsync = (pass == 0 && (!a.spread || (warps > 1 && G == 32))) ? 2 : 0;
     if (tr->roll_blocksync >= 0 && a.bsync) a.bsync = tr->roll_blocksync;
+    if (a.spread && tr->spread_blocksync >= 0 && a.bsync) a.bsync = tr->spread_blocksync;
 #define LAUNCH(GG, NN)                                                                                              \
   TOKP_CUDA(cudaFuncSetAttribute(k_rollout<GG, NN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lp.smem));    \
   k_rollout<GG, NN><<<blocks, warps * 32, lp.smem, tr->stream>>>(dm, a, lp.wsd);

@@ -138,6 +138,7 @@ extern "C" int tokp_traj_create(const tokp_model* m, const tokp_task_desc* td, i
   if (!tr->kp_stats || !tr->h_kp_stats || !tr->h_fd_counts || !tr->h_wstatus) { set_error("tokp_traj_create: statistics buffers"); tokp_traj_destroy(tr); return TOKP_ERR_CUDA; }
   read_env_options(tr->dm);
   if (const char* e = getenv("TOKP_ROLL_BLOCKSYNC")) tr->roll_blocksync = atoi(e) > 3 ? 3 : (atoi(e) < 0 ? 0 : atoi(e));
+  if (const char* e = getenv("TOKP_SPREAD_BLOCKSYNC")) tr->spread_blocksync = atoi(e) > 3 ? 3 : (atoi(e) < 0 ? 0 : atoi(e));
   if (const char* e = getenv("TOKP_SPREAD_WARPS")) { int v = atoi(e); if (v >= 1 && v <= 4) tr->spread_warps = v; }
   if (getenv("TOKP_SPREAD_KEEP_LANES")) tr->spread_keep_lanes = 1;
   if (const char* e = getenv("TOKP_FD_SHARE_GIB")) { int v = atoi(e); if (v >= 1 && v <= 64) tr->fd_share_gib = v; }

@@ -6,16 +6,24 @@
 
 namespace tk {
 
-// mj_comVel (level-synchronous)
+// mj_comVel and the forward pass of mj_rne(flg_acc = 0) in ONE level-synchronous walk down the tree: a body's cvel and
+// cdof_dot, then its cacc = cacc[parent] + cdof_dot qvel and cfrc = I cacc + cvel x* (I cvel), all of which need only the
+// parent's values of the previous level.  Same operations per entry as two separate walks, one barrier per level less.
 template <int G, int NV>
 TK_DEV void com_vel(const DM& m, WS& w, const Grp<G, NV>& g) {
-  if (g.gl == 0) for (int k = 0; k < 6; k++) w.cvel[k] = 0.0;
+  if (g.gl == 0) {
+    for (int k = 0; k < 6; k++) w.cvel[k] = 0.0;
+    w.cacc[0] = w.cacc[1] = w.cacc[2] = 0.0;
+    w.cacc[3] = -m.gravity[0]; w.cacc[4] = -m.gravity[1]; w.cacc[5] = -m.gravity[2];
+    for (int k = 0; k < 6; k++) w.cfrc[k] = 0.0;
+  }
   g.sync();
   for (int depth = 1; depth <= m.treedepth; depth++) {
     for (int i = 1 + g.gl; i < m.nbody; i += G) {
       if (m.body_depth[i] != depth) continue;
+      const int pid = m.body_parentid[i];
       double cv[6];
-      for (int k = 0; k < 6; k++) cv[k] = w.cvel[6 * m.body_parentid[i] + k];
+      for (int k = 0; k < 6; k++) cv[k] = w.cvel[6 * pid + k];
       int bda = m.body_dofadr[i], dn = m.body_dofnum[i];
       int j = 0;
       while (j < dn) {
@@ -36,12 +44,23 @@ TK_DEV void com_vel(const DM& m, WS& w, const Grp<G, NV>& g) {
         }
       }
       for (int k = 0; k < 6; k++) w.cvel[6 * i + k] = cv[k];
+      // mj_rne forward pass for this body
+      double t[6] = {0, 0, 0, 0, 0, 0};
+      for (int jj = 0; jj < dn; jj++)
+        for (int c = 0; c < 6; c++) t[c] += w.cdof_dot[6 * (bda + jj) + c] * w.qvel[bda + jj];
+      double ca[6];
+      for (int c = 0; c < 6; c++) { ca[c] = w.cacc[6 * pid + c] + t[c]; w.cacc[6 * i + c] = ca[c]; }
+      double t1[6], t2[6], t3[6];
+      mul_inert_vec(t1, &w.cinert[10 * i], ca);
+      mul_inert_vec(t2, &w.cinert[10 * i], cv);
+      cross_force(t3, cv, t2);
+      for (int c = 0; c < 6; c++) w.cfrc[6 * i + c] = t1[c] + t3[c];
     }
     g.sync();
   }
 }
 
-// mj_passive (damping + gravity compensation) and mj_rne(flg_acc = 0)
+// mj_passive (damping + gravity compensation) and the backward pass of mj_rne (cacc / cfrc come from com_vel's walk)
 template <int G, int NV>
 TK_DEV void passive_and_bias(const DM& m, WS& w, const Grp<G, NV>& g) {
   const int nv = NV ? NV : m.nv;
@@ -58,30 +77,6 @@ TK_DEV void passive_and_bias(const DM& m, WS& w, const Grp<G, NV>& g) {
       }
     }
     w.frc_passive[i] = f;
-  }
-  // cacc: level-synchronous down the tree
-  if (g.gl == 0) {
-    w.cacc[0] = w.cacc[1] = w.cacc[2] = 0.0;
-    w.cacc[3] = -m.gravity[0]; w.cacc[4] = -m.gravity[1]; w.cacc[5] = -m.gravity[2];
-    for (int k = 0; k < 6; k++) w.cfrc[k] = 0.0;
-  }
-  g.sync();
-  for (int depth = 1; depth <= m.treedepth; depth++) {
-    for (int i = 1 + g.gl; i < m.nbody; i += G) {
-      if (m.body_depth[i] != depth) continue;
-      int bda = m.body_dofadr[i];
-      double t[6] = {0, 0, 0, 0, 0, 0};
-      for (int j = 0; j < m.body_dofnum[i]; j++)
-        for (int c = 0; c < 6; c++) t[c] += w.cdof_dot[6 * (bda + j) + c] * w.qvel[bda + j];
-      double ca[6];
-      for (int c = 0; c < 6; c++) { ca[c] = w.cacc[6 * m.body_parentid[i] + c] + t[c]; w.cacc[6 * i + c] = ca[c]; }
-      double t1[6], t2[6], t3[6];
-      mul_inert_vec(t1, &w.cinert[10 * i], ca);
-      mul_inert_vec(t2, &w.cinert[10 * i], &w.cvel[6 * i]);
-      cross_force(t3, &w.cvel[6 * i], t2);
-      for (int c = 0; c < 6; c++) w.cfrc[6 * i + c] = t1[c] + t3[c];
-    }
-    g.sync();
   }
   // bias[i] = cdof_i . (sum of body forces over the subtree of the dof's body)
   for (int i = g.gl; i < nv; i += G) {

@@ -105,6 +105,7 @@ struct tokp_traj {
   int fd_last_lane_mode = 0;
   // rollout tuning (TOKP_ROLL_BLOCKSYNC, TOKP_SPREAD_WARPS, TOKP_SPREAD_KEEP_LANES; read once at creation)
   int roll_blocksync = -1, spread_warps = 0, spread_keep_lanes = 0;
+  int spread_blocksync = -1;  // Grp::bsync level of the spread (one world per warp) rollouts; -1 = the default (2)
   // key-point statistics without a bulk readback: k_kp_stats leaves [B][3] (sum of per-dof percentages, FD worlds,
   // columns) in kp_stats; it, the FD list counters and the status words land in pinned host memory with the stream
   double* kp_stats = nullptr;
